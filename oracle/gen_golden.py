@@ -1,0 +1,170 @@
+"""Generate tests/golden/*.npz by running the REAL reference modules from /root/reference.
+
+Run in the build container only (the reference is not present on the GPU box):
+
+    python oracle/gen_golden.py
+
+The reference's ``models`` package imports ``segmentation_models_pytorch`` at module top
+(models/__init__.py:2), which is not installed; a stub is placed in ``sys.modules`` so that
+``models.unet`` / ``models.ducknet`` import unmodified.  ``core/loss.py`` is loaded by file path.
+Weights come from ``oracle.ref_models.synth_state_dict`` (numpy PCG64 - independent of the torch
+version) and are loaded into the reference modules through ``load_state_dict``; inputs are stored
+in the fixture, so the tests never need the reference again.
+"""
+import importlib.util
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.environ.get('MSX_REFERENCE', '/root/reference')
+sys.path.insert(0, ROOT)
+
+from oracle import ref_models  # noqa: E402
+
+
+def load_reference():
+    stub = types.ModuleType('segmentation_models_pytorch')
+    for n in ('DeepLabV3', 'DeepLabV3Plus', 'FPN', 'Linknet', 'MAnet', 'PAN', 'PSPNet', 'Unet', 'UnetPlusPlus'):
+        setattr(stub, n, None)
+    sys.modules['segmentation_models_pytorch'] = stub
+    sys.path.insert(0, REF)
+    from models.unet import UNet            # noqa
+    from models.ducknet import DuckNet      # noqa
+    spec = importlib.util.spec_from_file_location('ref_core_loss', os.path.join(REF, 'core', 'loss.py'))
+    loss_mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(loss_mod)
+    sys.path.remove(REF)
+    return UNet, DuckNet, loss_mod
+
+
+def synth_batch(rng, n, h, w, n_class=2, ignore_frac=0.0):
+    img = np.clip(rng.standard_normal((n, 3, h, w)), -2.12, 2.64).astype(np.float32)
+    yy, xx = np.mgrid[0:h, 0:w]
+    mask = np.zeros((n, h, w), dtype=np.int64)
+    for i in range(n):
+        cy, cx = rng.uniform(0.2, 0.8) * h, rng.uniform(0.2, 0.8) * w
+        ay, ax = rng.uniform(0.15, 0.35) * h, rng.uniform(0.15, 0.35) * w
+        mask[i] = (((yy - cy) / ay) ** 2 + ((xx - cx) / ax) ** 2 <= 1.0).astype(np.int64) * (n_class - 1)
+    if ignore_frac > 0:
+        mask[rng.uniform(size=mask.shape) < ignore_frac] = 255
+    return img, mask
+
+
+class Cfg:
+    pass
+
+
+def model_case(ref_cls, name, base, n, hw, seed, loss_mod, out):
+    rng = np.random.Generator(np.random.PCG64(seed))
+    img, mask = synth_batch(rng, n, hw, hw, 2, ignore_frac=0.03)
+    layout = ref_models.model_layout(name, num_class=2, n_channel=3, base_channel=base)
+    sd = ref_models.synth_state_dict(layout, seed + 100)
+    res = {'images': img, 'masks': mask, 'base_channel': np.int64(base), 'weight_seed': np.int64(seed + 100)}
+    cfg = Cfg()
+    cfg.class_weights, cfg.loss_type, cfg.ignore_index, cfg.reduction = None, 'ce', 255, 'mean'
+    for tag, dt in (('f32', torch.float32), ('f64', torch.float64)):
+        torch.manual_seed(0)
+        model = ref_cls(num_class=2, n_channel=3, base_channel=base)
+        assert list(model.state_dict().keys()) == list(layout.keys()), 'oracle layout != reference state_dict'
+        for k, v in model.state_dict().items():
+            assert tuple(v.shape) == tuple(layout[k]), (k, v.shape, layout[k])
+        model.load_state_dict(sd)
+        model = model.to(dt).train()
+        loss_fn = loss_mod.get_loss_fn(cfg, torch.device('cpu'))
+        x = torch.from_numpy(img).to(dt)
+        logits = model(x)
+        loss = loss_fn(logits, torch.from_numpy(mask))
+        loss.backward()
+        res[f'logits_{tag}'] = logits.detach().numpy()
+        res[f'loss_{tag}'] = loss.detach().numpy()
+        gn = []
+        for k, p in model.named_parameters():
+            gn.append(p.grad.norm().item())
+        res[f'grad_norms_{tag}'] = np.asarray(gn, dtype=np.float64)
+        named = dict(model.named_parameters())
+        keep = ['seg_head.weight', list(named.keys())[0], list(named.keys())[1], list(named.keys())[2]]
+        for k in keep:
+            res[f'grad_{tag}::{k}'] = named[k].grad.detach().numpy()
+        st = model.state_dict()
+        bn_keys = [k for k in st if k.endswith('running_var')]
+        for k in (bn_keys[0], bn_keys[len(bn_keys) // 2], bn_keys[-1]):
+            res[f'buf_{tag}::{k}'] = st[k].numpy().copy()
+            km = k.replace('running_var', 'running_mean')
+            res[f'buf_{tag}::{km}'] = st[km].numpy().copy()
+        # eval-mode forward with the updated running stats (validation path, core/seg_trainer.py:114)
+        model.eval()
+        with torch.no_grad():
+            res[f'eval_logits_{tag}'] = model(x).numpy()
+    res['param_names'] = np.asarray([k for k, _ in model.named_parameters()])
+    np.savez_compressed(out, **res)
+    print('wrote', out, {k: getattr(v, 'shape', None) for k, v in res.items() if k.startswith('logits')})
+
+
+def loss_case(loss_mod, out):
+    rng = np.random.Generator(np.random.PCG64(7))
+    n, c, h, w = 2, 3, 16, 24
+    z = (rng.standard_normal((n, c, h, w)) * 2.0).astype(np.float32)
+    zt = (rng.standard_normal((n, c, h, w)) * 2.0).astype(np.float32)
+    t = rng.integers(0, c, size=(n, h, w)).astype(np.int64)
+    t[rng.uniform(size=t.shape) < 0.1] = 255
+    res = {'logits': z, 'teacher': zt, 'labels': t}
+    cfg = Cfg()
+    cfg.ignore_index, cfg.reduction, cfg.loss_type = 255, 'mean', 'ce'
+
+    def run(fn, key):
+        zz = torch.from_numpy(z).double().requires_grad_(True)
+        val = fn(zz)
+        val.backward()
+        res[key] = val.detach().numpy()
+        res[key + '_grad'] = zz.grad.numpy()
+
+    cfg.class_weights = None
+    ce = loss_mod.get_loss_fn(cfg, torch.device('cpu'))
+    run(lambda zz: ce(zz, torch.from_numpy(t)), 'ce')
+    cfg.class_weights = [0.3, 1.0, 2.5]
+    res['class_weights'] = np.asarray(cfg.class_weights, dtype=np.float32)
+    cew = loss_mod.get_loss_fn(cfg, torch.device('cpu')).double()
+    run(lambda zz: cew(zz, torch.from_numpy(t)), 'ce_weighted')
+
+    # OHEM: the reference forward body, constructed without the .cuda() of core/loss.py:9
+    def make_ohem(thresh):
+        o = loss_mod.OhemCELoss.__new__(loss_mod.OhemCELoss)
+        torch.nn.Module.__init__(o)
+        o.thresh = -torch.log(torch.tensor(thresh, dtype=torch.float))
+        o.ignore_index = 255
+        o.criteria = torch.nn.CrossEntropyLoss(ignore_index=255, reduction='none')
+        return o
+    run(lambda zz: make_ohem(0.7)(zz, torch.from_numpy(t)), 'ohem_thresh_branch')       # many hard pixels
+    run(lambda zz: make_ohem(1e-4)(zz, torch.from_numpy(t)), 'ohem_topk_branch')        # thresh ~9.2: top-k
+    res['ohem_topk_thresh'] = np.float64(1e-4)
+
+    cfg.kd_temperature = 4.0
+    for kind in ('kl_div', 'mse'):
+        cfg.kd_loss_type = kind
+        run(lambda zz: loss_mod.kd_loss_fn(cfg, zz, torch.from_numpy(zt).double()), 'kd_' + kind)
+    np.savez_compressed(out, **res)
+    print('wrote', out)
+
+
+def main():
+    torch.set_num_threads(1)
+    UNet, DuckNet, loss_mod = load_reference()
+    g = os.path.join(ROOT, 'tests', 'golden')
+    os.makedirs(g, exist_ok=True)
+    model_case(UNet, 'unet', 8, 2, 32, 11, loss_mod, os.path.join(g, 'unet_b8_32.npz'))
+    model_case(DuckNet, 'ducknet', 3, 2, 64, 12, loss_mod, os.path.join(g, 'ducknet_b3_64.npz'))
+    loss_case(loss_mod, os.path.join(g, 'losses.npz'))
+    # parameter-count pins from README.md:110-112
+    counts = {}
+    for name, cls, b in (('unet32', UNet, 32), ('ducknet17', DuckNet, 17), ('ducknet34', DuckNet, 34)):
+        counts[name] = sum(p.numel() for p in cls(num_class=2, n_channel=3, base_channel=b).parameters())
+    np.savez(os.path.join(g, 'param_counts.npz'), **{k: np.int64(v) for k, v in counts.items()})
+    print(counts)
+
+
+if __name__ == '__main__':
+    main()
