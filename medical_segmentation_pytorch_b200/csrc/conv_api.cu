@@ -1,0 +1,122 @@
+// extern "C" convolution entry points: engine selection + the ConvBNAct composites.
+#include "common.cuh"
+
+namespace msx {
+struct GatherGeom;
+int validate_desc(const msx_conv_desc* d);
+size_t conv_packed_elems(const msx_conv_desc* d);
+int conv_pack_launch(const msx_conv_desc* d, int mode, const float* w, void* packed, cudaStream_t st);
+int conv_gather_simt(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
+                     void* dst, cudaStream_t st);
+size_t conv_wgrad_ws_bytes(const msx_conv_desc* d);
+int conv_wgrad_simt(const msx_conv_desc* d, const void* x, const void* dy, float* dw, void* ws, size_t ws_bytes,
+                    cudaStream_t st);
+// tcgen05 engine (conv_tc.cu)
+bool conv_tc_supported(const msx_conv_desc* d, bool fwd_pass);
+int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
+                   void* dst, cudaStream_t st);
+
+static int conv_gather(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
+                       void* dst, cudaStream_t st) {
+    const bool want_tc = d->engine == MSX_ENGINE_TCGEN05 || (d->engine == MSX_ENGINE_AUTO && d->dtype == MSX_BF16);
+    if (want_tc && conv_tc_supported(d, fwd_pass)) return conv_gather_tc(d, fwd_pass, src, packed, bias, dst, st);
+    if (d->engine == MSX_ENGINE_TCGEN05)
+        return set_error(MSX_ERR_UNSUPPORTED, "conv: tcgen05 engine requested for a shape/dtype it does not support");
+    return conv_gather_simt(d, fwd_pass, src, packed, bias, dst, st);
+}
+
+static size_t ws_conv_bytes(const msx_conv_desc* d) {
+    const size_t a = conv_wgrad_ws_bytes(d);
+    const int cmax = d->cin > d->cout ? d->cin : d->cout;
+    const size_t b = bn_partials_bytes(cmax);
+    return (a > b ? a : b) + 256;
+}
+}  // namespace msx
+
+using namespace msx;
+
+extern "C" {
+
+size_t msx_conv_packed_bytes(const msx_conv_desc* d) {
+    if (!d) return 0;
+    return conv_packed_elems(d) * (d->dtype == MSX_BF16 ? 2 : 4);
+}
+size_t msx_ws_bytes_conv(const msx_conv_desc* d) { return d ? ws_conv_bytes(d) : 0; }
+
+int msx_conv_pack_weights(const msx_conv_desc* d, int mode, const float* w_master, void* packed, void* stream) {
+    MSX_TRY(validate_desc(d));
+    MSX_REQUIRE(w_master && packed, "pack_weights: null pointer");
+    MSX_REQUIRE(mode == MSX_PACK_FPROP || mode == MSX_PACK_DGRAD, "pack_weights: bad mode %d", mode);
+    return conv_pack_launch(d, mode, w_master, packed, as_stream(stream));
+}
+
+int msx_conv2d_fwd(const msx_conv_desc* d, const void* x, const float* w_master, const float* bias, void* w_packed,
+                   void* y, void* stream) {
+    MSX_TRY(validate_desc(d));
+    MSX_REQUIRE(x && w_master && w_packed && y, "conv2d_fwd: null pointer");
+    cudaStream_t st = as_stream(stream);
+    MSX_TRY(conv_pack_launch(d, MSX_PACK_FPROP, w_master, w_packed, st));
+    return conv_gather(d, true, x, w_packed, bias, y, st);
+}
+
+int msx_conv2d_bwd(const msx_conv_desc* d, const void* x, const float* w_master, const void* dy, void* w_packed,
+                   void* dx, float* dw, float* dbias, void* ws, size_t ws_bytes, void* stream) {
+    MSX_TRY(validate_desc(d));
+    MSX_REQUIRE(x && w_master && dy && w_packed, "conv2d_bwd: null pointer");
+    cudaStream_t st = as_stream(stream);
+    if (dx) {
+        MSX_TRY(conv_pack_launch(d, MSX_PACK_DGRAD, w_master, w_packed, st));
+        MSX_TRY(conv_gather(d, false, dy, w_packed, nullptr, dx, st));
+    }
+    if (dw) MSX_TRY(conv_wgrad_simt(d, x, dy, dw, ws, ws_bytes, st));
+    if (dbias)
+        MSX_TRY(channel_sum_launch(d->dtype, dy, d->ldy, (int64_t)d->n * d->oh * d->ow, d->cout, dbias, ws, ws_bytes, st));
+    return MSX_OK;
+}
+
+int msx_conv_bn_act_fwd(const msx_conv_desc* d, const void* x, const float* w_master, const float* bias,
+                        const float* gamma, const float* beta, float* running_mean, float* running_var,
+                        int64_t* num_batches_tracked, float eps, float momentum, int training, int relu,
+                        void* w_packed, void* y_raw, void* z, int32_t ldz, float* save_mean, float* save_invstd,
+                        void* ws, size_t ws_bytes, void* stream) {
+    MSX_TRY(validate_desc(d));
+    MSX_REQUIRE(x && w_master && gamma && beta && w_packed && y_raw && z && save_mean && save_invstd, "conv_bn_act_fwd: null pointer");
+    MSX_REQUIRE(training || (running_mean && running_var), "conv_bn_act_fwd: eval mode needs running statistics");
+    if (ws_bytes < bn_partials_bytes(d->cout)) return set_error(MSX_ERR_WORKSPACE, "conv_bn_act_fwd: workspace %zu < %zu", ws_bytes, bn_partials_bytes(d->cout));
+    cudaStream_t st = as_stream(stream);
+    const int64_t pixels = (int64_t)d->n * d->oh * d->ow;
+    MSX_TRY(conv_pack_launch(d, MSX_PACK_FPROP, w_master, w_packed, st));
+    MSX_TRY(conv_gather(d, true, x, w_packed, bias, y_raw, st));
+    if (training) {
+        int nblk = 0;
+        MSX_TRY(bn_stats_launch(d->dtype, y_raw, d->ldy, pixels, d->cout, static_cast<double*>(ws), &nblk, st));
+        MSX_TRY(bn_finalize_launch(static_cast<double*>(ws), nblk, d->cout, pixels, eps, momentum, save_mean, save_invstd,
+                                   running_mean, running_var, num_batches_tracked, st));
+    } else {
+        MSX_TRY(bn_eval_stats_launch(d->cout, running_mean, running_var, eps, save_mean, save_invstd, st));
+    }
+    return bn_apply_launch(d->dtype, y_raw, d->ldy, z, ldz, pixels, d->cout, save_mean, save_invstd, gamma, beta, relu, st);
+}
+
+int msx_conv_bn_act_bwd(const msx_conv_desc* d, const void* x, const float* w_master, const void* y_raw,
+                        const void* dz, int32_t lddz, const float* gamma, const float* beta, const float* save_mean,
+                        const float* save_invstd, int relu, void* w_packed, void* dy_scratch, void* dx, float* dw,
+                        float* dbias, float* dgamma, float* dbeta, void* ws, size_t ws_bytes, void* stream) {
+    MSX_TRY(validate_desc(d));
+    MSX_REQUIRE(x && w_master && y_raw && dz && gamma && beta && save_mean && save_invstd && w_packed && dy_scratch,
+                "conv_bn_act_bwd: null pointer");
+    if (ws_bytes < ws_conv_bytes(d)) return set_error(MSX_ERR_WORKSPACE, "conv_bn_act_bwd: workspace %zu < %zu", ws_bytes, ws_conv_bytes(d));
+    cudaStream_t st = as_stream(stream);
+    const int64_t pixels = (int64_t)d->n * d->oh * d->ow;
+    MSX_TRY(bn_bwd_launch(d->dtype, y_raw, d->ldy, dz, lddz, pixels, d->cout, gamma, beta, save_mean, save_invstd, relu,
+                          dy_scratch, d->ldy, dgamma, dbeta, ws, ws_bytes, st));
+    if (dx) {
+        MSX_TRY(conv_pack_launch(d, MSX_PACK_DGRAD, w_master, w_packed, st));
+        MSX_TRY(conv_gather(d, false, dy_scratch, w_packed, nullptr, dx, st));
+    }
+    if (dw) MSX_TRY(conv_wgrad_simt(d, x, dy_scratch, dw, ws, ws_bytes, st));
+    if (dbias) MSX_TRY(channel_sum_launch(d->dtype, dy_scratch, d->ldy, pixels, d->cout, dbias, ws, ws_bytes, st));
+    return MSX_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,708 @@
+// Bandwidth-bound NHWC kernels: BatchNorm statistics / apply / backward, n-way sum (+nearest-2x
+// upsample) with fused statistics, MaxPool2d(3,2,1), layout conversion.
+//
+// Thread mapping shared by all of them ("channel-fixed"): a thread owns one 16-byte channel
+// vector (4 floats / 8 bf16) and walks over pixels, so per-channel parameters and accumulators
+// stay in registers and every warp access is a run of whole 16 B vectors along the contiguous
+// channel axis.  A CTA of 256 threads = `lanes` pixels x `vch` vectors; blockIdx.y selects a
+// chunk of <= 64 vectors when the tensor has more channels than that.
+#include "common.cuh"
+
+namespace msx {
+
+namespace {
+
+struct ChanCfg {
+    int cp, vch, nchunk, lanes;
+};
+template <int VEC>
+ChanCfg chan_cfg(int channels) {
+    ChanCfg c;
+    c.cp = round_up(channels, 8);
+    const int V = c.cp / VEC;
+    c.vch = V < 64 ? V : 64;
+    c.nchunk = (V + c.vch - 1) / c.vch;
+    c.lanes = 256 / c.vch;
+    return c;
+}
+
+struct ChanThread {
+    int c0, lane, lanes;
+    bool active;
+};
+template <int VEC>
+__device__ inline ChanThread chan_thread(int cp, int vch) {
+    ChanThread t;
+    t.lanes = blockDim.x / vch;
+    t.lane = threadIdx.x / vch;
+    const int v = blockIdx.y * vch + threadIdx.x % vch;
+    t.c0 = v * VEC;
+    t.active = t.lane < t.lanes && t.c0 < cp;
+    return t;
+}
+
+// Sum v[j] over the pixel lanes of the CTA (threads that share threadIdx.x % vch); result valid
+// in lane 0.  sh: 256 doubles.
+template <int NV>
+__device__ inline void lane_reduce(double (&v)[NV], double* sh, int vch, int lane, int lanes) {
+    int p2 = 1;
+    while (p2 < lanes) p2 <<= 1;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+        sh[threadIdx.x] = v[j];
+        __syncthreads();
+        for (int off = p2 >> 1; off > 0; off >>= 1) {
+            if (lane < off && lane + off < lanes) sh[threadIdx.x] += sh[threadIdx.x + off * vch];
+            __syncthreads();
+        }
+        v[j] = sh[threadIdx.x];
+        __syncthreads();
+    }
+}
+
+inline int reduce_grid(int64_t pixels, int lanes) {
+    int64_t g = cdiv64(pixels, (int64_t)lanes * 8);
+    if (g < 1) g = 1;
+    if (g > kMaxPartialBlocks) g = kMaxPartialBlocks;
+    return (int)g;
+}
+inline int stream_grid(int64_t pixels, int lanes) {
+    int64_t g = cdiv64(pixels, (int64_t)lanes * 4);
+    if (g < 1) g = 1;
+    if (g > kNumSMs * 16) g = kNumSMs * 16;
+    return (int)g;
+}
+
+// ---- statistics ---------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) bn_stats_kernel(const T* __restrict__ x, int ld, int64_t pixels, int cp, int vch,
+                                                       double* __restrict__ partials) {
+    constexpr int VEC = Vec<T>::N;
+    __shared__ double sh[256];
+    const ChanThread t = chan_thread<VEC>(cp, vch);
+    double acc[2 * VEC];
+#pragma unroll
+    for (int j = 0; j < 2 * VEC; ++j) acc[j] = 0.0;
+    if (t.active) {
+        for (int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane; p < pixels; p += (int64_t)gridDim.x * t.lanes) {
+            float v[VEC];
+            Vec<T>::load(x + p * ld + t.c0, v);
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) {
+                acc[j] += (double)v[j];
+                acc[VEC + j] += (double)v[j] * (double)v[j];
+            }
+        }
+    }
+    lane_reduce<2 * VEC>(acc, sh, vch, t.lane, t.lanes);
+    if (t.active && t.lane == 0) {
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            partials[((int64_t)blockIdx.x * 2 + 0) * cp + t.c0 + j] = acc[j];
+            partials[((int64_t)blockIdx.x * 2 + 1) * cp + t.c0 + j] = acc[VEC + j];
+        }
+    }
+}
+
+__global__ void bn_finalize_kernel(const double* __restrict__ partials, int nblk, int cp, int channels, int64_t count,
+                                   float eps, float momentum, float* __restrict__ mean, float* __restrict__ invstd,
+                                   float* running_mean, float* running_var, int64_t* nbt) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c == 0 && nbt) *nbt += 1;
+    if (c >= cp) return;
+    if (c >= channels) { mean[c] = 0.f; invstd[c] = 0.f; return; }
+    double s = 0.0, q = 0.0;
+    for (int b = 0; b < nblk; ++b) {
+        s += partials[((int64_t)b * 2 + 0) * cp + c];
+        q += partials[((int64_t)b * 2 + 1) * cp + c];
+    }
+    const double m = s / (double)count;
+    double var = q / (double)count - m * m;
+    if (var < 0.0) var = 0.0;
+    mean[c] = (float)m;
+    invstd[c] = (float)(1.0 / sqrt(var + (double)eps));
+    if (running_mean) {
+        const double unb = count > 1 ? var * ((double)count / (double)(count - 1)) : var;
+        running_mean[c] = (float)((1.0 - momentum) * (double)running_mean[c] + (double)momentum * m);
+        running_var[c] = (float)((1.0 - momentum) * (double)running_var[c] + (double)momentum * unb);
+    }
+}
+
+__global__ void bn_eval_stats_kernel(int cp, int channels, const float* rm, const float* rv, float eps,
+                                     float* mean, float* invstd) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= cp) return;
+    if (c >= channels) { mean[c] = 0.f; invstd[c] = 0.f; return; }
+    mean[c] = rm[c];
+    invstd[c] = (float)(1.0 / sqrt((double)rv[c] + (double)eps));
+}
+
+// ---- apply --------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) bn_apply_kernel(const T* __restrict__ x, int ldx, T* __restrict__ z, int ldz,
+                                                       int64_t pixels, int cp, int vch, int channels,
+                                                       const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                       const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                       int relu) {
+    constexpr int VEC = Vec<T>::N;
+    const ChanThread t = chan_thread<VEC>(cp, vch);
+    if (!t.active) return;
+    float mu[VEC], sc[VEC], sh[VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+        const int c = t.c0 + j;
+        const bool ok = c < channels;
+        mu[j] = ok ? mean[c] : 0.f;
+        sc[j] = ok ? invstd[c] * gamma[c] : 0.f;
+        sh[j] = ok ? beta[c] : 0.f;
+    }
+    for (int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane; p < pixels; p += (int64_t)gridDim.x * t.lanes) {
+        float v[VEC];
+        Vec<T>::load(x + p * ldx + t.c0, v);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            float r = (v[j] - mu[j]) * sc[j] + sh[j];
+            v[j] = relu ? fmaxf(r, 0.f) : r;
+        }
+        Vec<T>::store(z + p * ldz + t.c0, v);
+    }
+}
+
+// ---- backward -----------------------------------------------------------------------------
+// g = dz * [relu mask];  partial sums of g and g*xhat.
+template <typename T>
+__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const T* __restrict__ x, int ldx, const T* __restrict__ dz, int lddz,
+                                                            int64_t pixels, int cp, int vch, int channels,
+                                                            const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                            const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                            int relu, double* __restrict__ partials) {
+    constexpr int VEC = Vec<T>::N;
+    __shared__ double shm[256];
+    const ChanThread t = chan_thread<VEC>(cp, vch);
+    float mu[VEC], is[VEC], ga[VEC], be[VEC];
+    double acc[2 * VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+        const int c = t.c0 + j;
+        const bool ok = t.active && c < channels;
+        mu[j] = ok ? mean[c] : 0.f;
+        is[j] = ok ? invstd[c] : 0.f;
+        ga[j] = ok ? gamma[c] : 0.f;
+        be[j] = ok ? beta[c] : 0.f;
+        acc[j] = 0.0; acc[VEC + j] = 0.0;
+    }
+    if (t.active) {
+        for (int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane; p < pixels; p += (int64_t)gridDim.x * t.lanes) {
+            float v[VEC], g[VEC];
+            Vec<T>::load(x + p * ldx + t.c0, v);
+            Vec<T>::load(dz + p * lddz + t.c0, g);
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) {
+                const float xh = (v[j] - mu[j]) * is[j];
+                const float out = (v[j] - mu[j]) * (is[j] * ga[j]) + be[j];
+                const float gg = (relu && !(out > 0.f)) ? 0.f : g[j];
+                acc[j] += (double)gg;
+                acc[VEC + j] += (double)gg * (double)xh;
+            }
+        }
+    }
+    lane_reduce<2 * VEC>(acc, shm, vch, t.lane, t.lanes);
+    if (t.active && t.lane == 0) {
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            partials[((int64_t)blockIdx.x * 2 + 0) * cp + t.c0 + j] = acc[j];
+            partials[((int64_t)blockIdx.x * 2 + 1) * cp + t.c0 + j] = acc[VEC + j];
+        }
+    }
+}
+
+__global__ void bn_bwd_finalize_kernel(const double* __restrict__ partials, int nblk, int cp, int channels, int64_t count,
+                                       float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                       float* __restrict__ c1, float* __restrict__ c2) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= cp) return;
+    if (c >= channels) { c1[c] = 0.f; c2[c] = 0.f; return; }
+    double s = 0.0, q = 0.0;
+    for (int b = 0; b < nblk; ++b) {
+        s += partials[((int64_t)b * 2 + 0) * cp + c];
+        q += partials[((int64_t)b * 2 + 1) * cp + c];
+    }
+    if (dbeta) dbeta[c] = (float)s;
+    if (dgamma) dgamma[c] = (float)q;
+    c1[c] = (float)(s / (double)count);
+    c2[c] = (float)(q / (double)count);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const T* __restrict__ x, int ldx, const T* __restrict__ dz, int lddz,
+                                                           T* __restrict__ dx, int lddx, int64_t pixels, int cp, int vch, int channels,
+                                                           const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                           const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                           const float* __restrict__ c1, const float* __restrict__ c2, int relu) {
+    constexpr int VEC = Vec<T>::N;
+    const ChanThread t = chan_thread<VEC>(cp, vch);
+    if (!t.active) return;
+    float mu[VEC], is[VEC], ga[VEC], be[VEC], k1[VEC], k2[VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+        const int c = t.c0 + j;
+        const bool ok = c < channels;
+        mu[j] = ok ? mean[c] : 0.f;
+        is[j] = ok ? invstd[c] : 0.f;
+        ga[j] = ok ? gamma[c] : 0.f;
+        be[j] = ok ? beta[c] : 0.f;
+        k1[j] = ok ? c1[c] : 0.f;
+        k2[j] = ok ? c2[c] : 0.f;
+    }
+    for (int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane; p < pixels; p += (int64_t)gridDim.x * t.lanes) {
+        float v[VEC], g[VEC];
+        Vec<T>::load(x + p * ldx + t.c0, v);
+        Vec<T>::load(dz + p * lddz + t.c0, g);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            const float xh = (v[j] - mu[j]) * is[j];
+            const float out = (v[j] - mu[j]) * (is[j] * ga[j]) + be[j];
+            const float gg = (relu && !(out > 0.f)) ? 0.f : g[j];
+            v[j] = (ga[j] * is[j]) * (gg - k1[j] - xh * k2[j]);
+        }
+        Vec<T>::store(dx + p * lddx + t.c0, v);
+    }
+}
+
+// ---- n-way sum (+ nearest 2x upsample of input 0) with fused statistics --------------------
+struct SumArgs {
+    const void* x[8];
+    int ld[8];
+    int n;
+};
+template <typename T>
+__global__ void __launch_bounds__(256) sum_stats_kernel(SumArgs a, int up2x, int H, int W, T* __restrict__ s, int lds,
+                                                        int64_t pixels, int cp, int vch, double* __restrict__ partials) {
+    constexpr int VEC = Vec<T>::N;
+    __shared__ double sh[256];
+    const ChanThread t = chan_thread<VEC>(cp, vch);
+    double acc[2 * VEC];
+#pragma unroll
+    for (int j = 0; j < 2 * VEC; ++j) acc[j] = 0.0;
+    if (t.active) {
+        for (int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane; p < pixels; p += (int64_t)gridDim.x * t.lanes) {
+            int64_t p0 = p;
+            if (up2x) {
+                const int xw = (int)(p % W);
+                const int64_t r = p / W;
+                const int yh = (int)(r % H);
+                const int64_t nn = r / H;
+                p0 = (nn * (H >> 1) + (yh >> 1)) * (W >> 1) + (xw >> 1);
+            }
+            float v[VEC];
+            Vec<T>::load(static_cast<const T*>(a.x[0]) + p0 * a.ld[0] + t.c0, v);
+            for (int i = 1; i < a.n; ++i) {
+                float u[VEC];
+                Vec<T>::load(static_cast<const T*>(a.x[i]) + p * a.ld[i] + t.c0, u);
+#pragma unroll
+                for (int j = 0; j < VEC; ++j) v[j] += u[j];
+            }
+            Vec<T>::store(s + p * lds + t.c0, v);
+            // statistics of the value as stored (bf16 rounding included), so that apply/backward,
+            // which re-read s, see the same numbers
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) {
+                const double w = (double)to_float(from_float<T>(v[j]));
+                acc[j] += w;
+                acc[VEC + j] += w * w;
+            }
+        }
+    }
+    lane_reduce<2 * VEC>(acc, sh, vch, t.lane, t.lanes);
+    if (t.active && t.lane == 0 && partials) {
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            partials[((int64_t)blockIdx.x * 2 + 0) * cp + t.c0 + j] = acc[j];
+            partials[((int64_t)blockIdx.x * 2 + 1) * cp + t.c0 + j] = acc[VEC + j];
+        }
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) upsample2x_bwd_kernel(const T* __restrict__ ds, int ldds, int H, int W,
+                                                             T* __restrict__ da, int ldda, int64_t pixels_lo, int cp, int vch) {
+    constexpr int VEC = Vec<T>::N;
+    const ChanThread t = chan_thread<VEC>(cp, vch);
+    if (!t.active) return;
+    const int h2 = H >> 1, w2 = W >> 1;
+    for (int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane; p < pixels_lo; p += (int64_t)gridDim.x * t.lanes) {
+        const int xw = (int)(p % w2);
+        const int64_t r = p / w2;
+        const int yh = (int)(r % h2);
+        const int64_t nn = r / h2;
+        const int64_t base = (nn * H + 2 * yh) * W + 2 * xw;
+        float v[VEC], u[VEC];
+        Vec<T>::load(ds + base * ldds + t.c0, v);
+        Vec<T>::load(ds + (base + 1) * ldds + t.c0, u);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) v[j] += u[j];
+        Vec<T>::load(ds + (base + W) * ldds + t.c0, u);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) v[j] += u[j];
+        Vec<T>::load(ds + (base + W + 1) * ldds + t.c0, u);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) v[j] += u[j];
+        Vec<T>::store(da + p * ldda + t.c0, v);
+    }
+}
+
+// ---- MaxPool2d(3, 2, 1) -------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) maxpool_fwd_kernel(const T* __restrict__ x, int ldx, int H, int W, int OH, int OW,
+                                                          T* __restrict__ z, int ldz, int8_t* __restrict__ idx, int ldidx,
+                                                          int64_t opix, int cp, int vch) {
+    constexpr int VEC = Vec<T>::N;
+    const ChanThread t = chan_thread<VEC>(cp, vch);
+    if (!t.active) return;
+    for (int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane; p < opix; p += (int64_t)gridDim.x * t.lanes) {
+        const int ox = (int)(p % OW);
+        const int64_t r = p / OW;
+        const int oy = (int)(r % OH);
+        const int64_t nn = r / OH;
+        float best[VEC];
+        int bi[VEC];
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) { best[j] = -INFINITY; bi[j] = -1; }
+#pragma unroll
+        for (int ky = 0; ky < 3; ++ky) {
+            const int iy = 2 * oy - 1 + ky;
+            if (iy < 0 || iy >= H) continue;
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx) {
+                const int ix = 2 * ox - 1 + kx;
+                if (ix < 0 || ix >= W) continue;
+                float v[VEC];
+                Vec<T>::load(x + ((nn * H + iy) * W + ix) * ldx + t.c0, v);
+#pragma unroll
+                for (int j = 0; j < VEC; ++j)
+                    if (bi[j] < 0 || v[j] > best[j]) { best[j] = v[j]; bi[j] = ky * 3 + kx; }
+            }
+        }
+        Vec<T>::store(z + p * ldz + t.c0, best);
+        int8_t* ip = idx + p * ldidx + t.c0;
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) ip[j] = (int8_t)bi[j];
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) maxpool_bwd_kernel(const T* __restrict__ dz, int lddz, const int8_t* __restrict__ idx, int ldidx,
+                                                          int H, int W, int OH, int OW, T* __restrict__ dx, int lddx,
+                                                          int64_t ipix, int cp, int vch) {
+    constexpr int VEC = Vec<T>::N;
+    const ChanThread t = chan_thread<VEC>(cp, vch);
+    if (!t.active) return;
+    for (int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane; p < ipix; p += (int64_t)gridDim.x * t.lanes) {
+        const int ix = (int)(p % W);
+        const int64_t r = p / W;
+        const int iy = (int)(r % H);
+        const int64_t nn = r / H;
+        float acc[VEC];
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) acc[j] = 0.f;
+        const int oy0 = iy >> 1, oy1 = (iy + 1) >> 1;     // windows 2*oy-1 .. 2*oy+1 containing iy
+        const int ox0 = ix >> 1, ox1 = (ix + 1) >> 1;
+        for (int oy = oy0; oy <= oy1; ++oy) {
+            if (oy >= OH) continue;
+            const int ky = iy - (2 * oy - 1);
+            for (int ox = ox0; ox <= ox1; ++ox) {
+                if (ox >= OW) continue;
+                const int pos = ky * 3 + (ix - (2 * ox - 1));
+                const int64_t op = (nn * OH + oy) * OW + ox;
+                float g[VEC];
+                Vec<T>::load(dz + op * lddz + t.c0, g);
+                const int8_t* ip = idx + op * ldidx + t.c0;
+#pragma unroll
+                for (int j = 0; j < VEC; ++j)
+                    if (ip[j] == pos) acc[j] += g[j];
+            }
+        }
+        Vec<T>::store(dx + p * lddx + t.c0, acc);
+    }
+}
+
+// ---- layout boundary ----------------------------------------------------------------------
+template <typename T>
+__global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, int C, int64_t hw, int64_t pixels, T* __restrict__ dst, int ld, int cp) {
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < pixels; p += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t nn = p / hw, q = p % hw;
+        for (int c0 = 0; c0 < cp; c0 += 4) {
+            float v[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) v[j] = (c0 + j < C) ? src[(nn * C + c0 + j) * hw + q] : 0.f;
+            store4(dst + p * ld + c0, v);
+        }
+    }
+}
+template <typename T>
+__global__ void nhwc_to_nchw_kernel(const T* __restrict__ src, int ld, int C, int64_t hw, int64_t pixels, float* __restrict__ dst) {
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < pixels; p += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t nn = p / hw, q = p % hw;
+        for (int c = 0; c < C; ++c) dst[(nn * C + c) * hw + q] = to_float(src[p * ld + c]);
+    }
+}
+
+// per-channel plain sum -> float (ConvTranspose bias gradient)
+__global__ void channel_sum_finalize_kernel(const double* __restrict__ partials, int nblk, int cp, int channels, float* out) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= channels) return;
+    double s = 0.0;
+    for (int b = 0; b < nblk; ++b) s += partials[((int64_t)b * 2 + 0) * cp + c];
+    out[c] = (float)s;
+}
+
+inline int check_ld(int ld, int channels, const char* what) {
+    if (ld % 8 != 0 || ld < round_up(channels, 8))
+        return set_error(MSX_ERR_INVALID, "%s: pixel stride %d must be a multiple of 8 and >= round_up(%d, 8)", what, ld, channels);
+    return MSX_OK;
+}
+
+}  // namespace
+
+// ---- launchers (internal) -------------------------------------------------------------------
+size_t bn_partials_bytes(int channels) {
+    const int cp = round_up(channels, 8);
+    return (size_t)kMaxPartialBlocks * 2 * cp * sizeof(double) + 2 * (size_t)cp * sizeof(float) + 256;
+}
+
+int bn_stats_launch(int dtype, const void* x, int ld, int64_t pixels, int channels, double* partials, int* nblk_out,
+                    cudaStream_t st) {
+    MSX_TRY(check_ld(ld, channels, "bn_stats"));
+    MSX_DISPATCH_DTYPE(dtype, T, {
+        const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
+        const int g = reduce_grid(pixels, c.lanes);
+        { ProfScope ps__(K_BN_STATS, st, (double)pixels * channels * (double)sizeof(T), 0); bn_stats_kernel<T><<<dim3(g, c.nchunk), 256, 0, st>>>(static_cast<const T*>(x), ld, pixels, c.cp, c.vch, partials); }
+        *nblk_out = g;
+    });
+    MSX_LAUNCH_CHECK();
+    return MSX_OK;
+}
+
+int bn_finalize_launch(const double* partials, int nblk, int channels, int64_t count, float eps, float momentum,
+                       float* mean, float* invstd, float* running_mean, float* running_var, int64_t* nbt,
+                       cudaStream_t st) {
+    const int cp = round_up(channels, 8);
+    { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_finalize_kernel<<<(cp + 127) / 128, 128, 0, st>>>(partials, nblk, cp, channels, count, eps, momentum, mean, invstd,
+                                                         running_mean, running_var, nbt); }
+    MSX_LAUNCH_CHECK();
+    return MSX_OK;
+}
+
+int bn_eval_stats_launch(int channels, const float* rm, const float* rv, float eps, float* mean, float* invstd,
+                         cudaStream_t st) {
+    const int cp = round_up(channels, 8);
+    { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_eval_stats_kernel<<<(cp + 127) / 128, 128, 0, st>>>(cp, channels, rm, rv, eps, mean, invstd); }
+    MSX_LAUNCH_CHECK();
+    return MSX_OK;
+}
+
+int bn_apply_launch(int dtype, const void* x, int ldx, void* z, int ldz, int64_t pixels, int channels,
+                    const float* mean, const float* invstd, const float* gamma, const float* beta, int relu,
+                    cudaStream_t st) {
+    MSX_TRY(check_ld(ldx, channels, "bn_apply x"));
+    MSX_TRY(check_ld(ldz, channels, "bn_apply z"));
+    MSX_DISPATCH_DTYPE(dtype, T, {
+        const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
+        { ProfScope ps__(K_BN_APPLY, st, 2.0 * (double)pixels * channels * (double)sizeof(T), 0); bn_apply_kernel<T><<<dim3(stream_grid(pixels, c.lanes), c.nchunk), 256, 0, st>>>(
+            static_cast<const T*>(x), ldx, static_cast<T*>(z), ldz, pixels, c.cp, c.vch, channels, mean, invstd, gamma, beta, relu); }
+    });
+    MSX_LAUNCH_CHECK();
+    return MSX_OK;
+}
+
+int bn_bwd_launch(int dtype, const void* x, int ldx, const void* dz, int lddz, int64_t pixels, int channels,
+                  const float* gamma, const float* beta, const float* mean, const float* invstd, int relu,
+                  void* dx, int lddx, float* dgamma, float* dbeta, void* ws, size_t ws_bytes, cudaStream_t st) {
+    MSX_TRY(check_ld(ldx, channels, "bn_bwd x"));
+    MSX_TRY(check_ld(lddz, channels, "bn_bwd dz"));
+    MSX_TRY(check_ld(lddx, channels, "bn_bwd dx"));
+    if (ws_bytes < bn_partials_bytes(channels)) return set_error(MSX_ERR_WORKSPACE, "bn_bwd: workspace %zu < %zu", ws_bytes, bn_partials_bytes(channels));
+    const int cp = round_up(channels, 8);
+    double* partials = static_cast<double*>(ws);
+    float* c1 = reinterpret_cast<float*>(partials + (size_t)kMaxPartialBlocks * 2 * cp);
+    float* c2 = c1 + cp;
+    MSX_DISPATCH_DTYPE(dtype, T, {
+        const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
+        const int g = reduce_grid(pixels, c.lanes);
+        { ProfScope ps__(K_BN_BWD_REDUCE, st, 2.0 * (double)pixels * channels * (double)sizeof(T), 0); bn_bwd_reduce_kernel<T><<<dim3(g, c.nchunk), 256, 0, st>>>(static_cast<const T*>(x), ldx, static_cast<const T*>(dz), lddz,
+                                                                 pixels, c.cp, c.vch, channels, mean, invstd, gamma, beta, relu, partials); }
+        { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_bwd_finalize_kernel<<<(cp + 127) / 128, 128, 0, st>>>(partials, g, cp, channels, pixels, dgamma, dbeta, c1, c2); }
+        { ProfScope ps__(K_BN_BWD_APPLY, st, 3.0 * (double)pixels * channels * (double)sizeof(T), 0); bn_bwd_apply_kernel<T><<<dim3(stream_grid(pixels, c.lanes), c.nchunk), 256, 0, st>>>(
+            static_cast<const T*>(x), ldx, static_cast<const T*>(dz), lddz, static_cast<T*>(dx), lddx, pixels, c.cp, c.vch, channels,
+            mean, invstd, gamma, beta, c1, c2, relu); }
+    });
+    MSX_LAUNCH_CHECK();
+    return MSX_OK;
+}
+
+int channel_sum_launch(int dtype, const void* x, int ld, int64_t pixels, int channels, float* out, void* ws,
+                       size_t ws_bytes, cudaStream_t st) {
+    if (ws_bytes < bn_partials_bytes(channels)) return set_error(MSX_ERR_WORKSPACE, "channel_sum: workspace too small");
+    int nblk = 0;
+    MSX_TRY(bn_stats_launch(dtype, x, ld, pixels, channels, static_cast<double*>(ws), &nblk, st));
+    { ProfScope ps__(K_MISC, st, 0, 0); channel_sum_finalize_kernel<<<(channels + 127) / 128, 128, 0, st>>>(static_cast<double*>(ws), nblk, round_up(channels, 8), channels, out); }
+    MSX_LAUNCH_CHECK();
+    return MSX_OK;
+}
+
+}  // namespace msx
+
+using namespace msx;
+
+// ============================================================================================
+extern "C" {
+
+size_t msx_ws_bytes_bn(int32_t channels) { return bn_partials_bytes(channels); }
+
+int msx_sum_bn_act_fwd(int dtype, int n_in, const void* const* host_xs, const int32_t* host_ldxs, int up2x_first,
+                       int32_t n, int32_t h, int32_t w, int32_t channels, void* s, int32_t lds,
+                       const float* gamma, const float* beta, float* running_mean, float* running_var,
+                       int64_t* num_batches_tracked, float eps, float momentum, int training, int relu,
+                       void* z, int32_t ldz, float* save_mean, float* save_invstd, void* ws, size_t ws_bytes, void* stream) {
+    cudaStream_t st = as_stream(stream);
+    MSX_REQUIRE(n_in >= 1 && n_in <= 8, "sum_bn_act: n_in=%d not in [1,8]", n_in);
+    MSX_REQUIRE(host_xs && host_ldxs && gamma && beta && z && save_mean && save_invstd, "sum_bn_act: null pointer");
+    MSX_REQUIRE(!up2x_first || (h % 2 == 0 && w % 2 == 0), "sum_bn_act: nearest-2x needs even h, w (got %dx%d)", h, w);
+    if (ws_bytes < bn_partials_bytes(channels)) return set_error(MSX_ERR_WORKSPACE, "sum_bn_act: workspace %zu < %zu", ws_bytes, bn_partials_bytes(channels));
+    const int64_t pixels = (int64_t)n * h * w;
+    double* partials = static_cast<double*>(ws);
+    const void* src = host_xs[0];
+    int ldsrc = host_ldxs[0];
+    int nblk = 0;
+    const bool need_sum = n_in > 1 || up2x_first;
+    if (need_sum) {
+        MSX_REQUIRE(s != nullptr, "sum_bn_act: sum buffer required for n_in>1 or upsampling");
+        MSX_TRY(check_ld(lds, channels, "sum_bn_act s"));
+        SumArgs a;
+        a.n = n_in;
+        for (int i = 0; i < n_in; ++i) {
+            MSX_TRY(check_ld(host_ldxs[i], channels, "sum_bn_act x"));
+            a.x[i] = host_xs[i];
+            a.ld[i] = host_ldxs[i];
+        }
+        MSX_DISPATCH_DTYPE(dtype, T, {
+            const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
+            nblk = reduce_grid(pixels, c.lanes);
+            { ProfScope ps__(K_SUM, st, (double)pixels * channels * (double)sizeof(T) * (n_in + 1.0), 0); sum_stats_kernel<T><<<dim3(nblk, c.nchunk), 256, 0, st>>>(a, up2x_first, h, w, static_cast<T*>(s), lds, pixels, c.cp, c.vch,
+                                                                     training ? partials : nullptr); }
+        });
+        MSX_LAUNCH_CHECK();
+        src = s;
+        ldsrc = lds;
+    } else if (training) {
+        MSX_TRY(bn_stats_launch(dtype, src, ldsrc, pixels, channels, partials, &nblk, st));
+    }
+    if (training)
+        MSX_TRY(bn_finalize_launch(partials, nblk, channels, pixels, eps, momentum, save_mean, save_invstd, running_mean,
+                                   running_var, num_batches_tracked, st));
+    else
+        MSX_TRY(bn_eval_stats_launch(channels, running_mean, running_var, eps, save_mean, save_invstd, st));
+    return bn_apply_launch(dtype, src, ldsrc, z, ldz, pixels, channels, save_mean, save_invstd, gamma, beta, relu, st);
+}
+
+int msx_sum_n(int dtype, int n_in, const void* const* host_xs, const int32_t* host_ldxs, int64_t pixels, int32_t channels,
+              void* out, int32_t ldout, void* stream) {
+    MSX_REQUIRE(n_in >= 1 && n_in <= 8 && host_xs && host_ldxs && out, "sum_n: bad arguments");
+    MSX_TRY(check_ld(ldout, channels, "sum_n out"));
+    SumArgs a;
+    a.n = n_in;
+    for (int i = 0; i < n_in; ++i) {
+        MSX_TRY(check_ld(host_ldxs[i], channels, "sum_n x"));
+        a.x[i] = host_xs[i];
+        a.ld[i] = host_ldxs[i];
+    }
+    MSX_DISPATCH_DTYPE(dtype, T, {
+        const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
+        { ProfScope ps__(K_SUM, as_stream(stream), (double)pixels * channels * (double)sizeof(T) * (n_in + 1.0), 0); sum_stats_kernel<T><<<dim3(stream_grid(pixels, c.lanes), c.nchunk), 256, 0, as_stream(stream)>>>(
+            a, 0, 1, 1, static_cast<T*>(out), ldout, pixels, c.cp, c.vch, nullptr); }
+    });
+    MSX_LAUNCH_CHECK();
+    return MSX_OK;
+}
+
+int msx_bn_act_bwd(int dtype, const void* s, int32_t lds, const void* dz, int32_t lddz, int64_t pixels, int32_t channels,
+                   const float* gamma, const float* beta, const float* save_mean, const float* save_invstd, int relu,
+                   void* ds, int32_t ldds, float* dgamma, float* dbeta, void* ws, size_t ws_bytes, void* stream) {
+    MSX_REQUIRE(s && dz && ds && gamma && beta && save_mean && save_invstd, "bn_act_bwd: null pointer");
+    return bn_bwd_launch(dtype, s, lds, dz, lddz, pixels, channels, gamma, beta, save_mean, save_invstd, relu, ds, ldds,
+                         dgamma, dbeta, ws, ws_bytes, as_stream(stream));
+}
+
+int msx_upsample2x_bwd(int dtype, const void* ds, int32_t ldds, int32_t n, int32_t h, int32_t w, int32_t channels,
+                       void* da, int32_t ldda, void* stream) {
+    MSX_REQUIRE(ds && da, "upsample2x_bwd: null pointer");
+    MSX_REQUIRE(h % 2 == 0 && w % 2 == 0, "upsample2x_bwd: odd size %dx%d", h, w);
+    MSX_TRY(check_ld(ldds, channels, "upsample2x_bwd ds"));
+    MSX_TRY(check_ld(ldda, channels, "upsample2x_bwd da"));
+    const int64_t plo = (int64_t)n * (h / 2) * (w / 2);
+    MSX_DISPATCH_DTYPE(dtype, T, {
+        const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
+        { ProfScope ps__(K_UPSAMPLE_BWD, as_stream(stream), (double)plo * channels * (double)sizeof(T) * 5.0, 0); upsample2x_bwd_kernel<T><<<dim3(stream_grid(plo, c.lanes), c.nchunk), 256, 0, as_stream(stream)>>>(
+            static_cast<const T*>(ds), ldds, h, w, static_cast<T*>(da), ldda, plo, c.cp, c.vch); }
+    });
+    MSX_LAUNCH_CHECK();
+    return MSX_OK;
+}
+
+int msx_maxpool3s2_fwd(int dtype, const void* x, int32_t ldx, int32_t n, int32_t h, int32_t w, int32_t channels,
+                       void* z, int32_t ldz, int8_t* idx, int32_t ldidx, void* stream) {
+    MSX_REQUIRE(x && z && idx, "maxpool_fwd: null pointer");
+    MSX_TRY(check_ld(ldx, channels, "maxpool x"));
+    MSX_TRY(check_ld(ldz, channels, "maxpool z"));
+    MSX_TRY(check_ld(ldidx, channels, "maxpool idx"));
+    const int oh = (h - 1) / 2 + 1, ow = (w - 1) / 2 + 1;
+    const int64_t opix = (int64_t)n * oh * ow;
+    MSX_DISPATCH_DTYPE(dtype, T, {
+        const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
+        { ProfScope ps__(K_MAXPOOL, as_stream(stream), (double)opix * channels * ((double)sizeof(T) * 5.0 + 1.0), 0); maxpool_fwd_kernel<T><<<dim3(stream_grid(opix, c.lanes), c.nchunk), 256, 0, as_stream(stream)>>>(
+            static_cast<const T*>(x), ldx, h, w, oh, ow, static_cast<T*>(z), ldz, idx, ldidx, opix, c.cp, c.vch); }
+    });
+    MSX_LAUNCH_CHECK();
+    return MSX_OK;
+}
+
+int msx_maxpool3s2_bwd(int dtype, const void* dz, int32_t lddz, const int8_t* idx, int32_t ldidx, int32_t n, int32_t h,
+                       int32_t w, int32_t channels, void* dx, int32_t lddx, void* stream) {
+    MSX_REQUIRE(dz && dx && idx, "maxpool_bwd: null pointer");
+    MSX_TRY(check_ld(lddz, channels, "maxpool dz"));
+    MSX_TRY(check_ld(lddx, channels, "maxpool dx"));
+    const int oh = (h - 1) / 2 + 1, ow = (w - 1) / 2 + 1;
+    const int64_t ipix = (int64_t)n * h * w;
+    MSX_DISPATCH_DTYPE(dtype, T, {
+        const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
+        { ProfScope ps__(K_MAXPOOL, as_stream(stream), (double)ipix * channels * ((double)sizeof(T) * 1.25 + 0.25 + (double)sizeof(T)), 0); maxpool_bwd_kernel<T><<<dim3(stream_grid(ipix, c.lanes), c.nchunk), 256, 0, as_stream(stream)>>>(
+            static_cast<const T*>(dz), lddz, idx, ldidx, h, w, oh, ow, static_cast<T*>(dx), lddx, ipix, c.cp, c.vch); }
+    });
+    MSX_LAUNCH_CHECK();
+    return MSX_OK;
+}
+
+int msx_nchw_to_nhwc(int dtype, const float* src, int32_t n, int32_t c, int32_t h, int32_t w, void* dst, int32_t ld, void* stream) {
+    MSX_REQUIRE(src && dst, "nchw_to_nhwc: null pointer");
+    MSX_TRY(check_ld(ld, c, "nchw_to_nhwc"));
+    const int64_t hw = (int64_t)h * w, pixels = hw * n;
+    const int grid = (int)((pixels + 255) / 256 < kNumSMs * 8 ? (pixels + 255) / 256 : kNumSMs * 8);
+    MSX_DISPATCH_DTYPE(dtype, T, {
+        { ProfScope ps__(K_LAYOUT, as_stream(stream), (double)pixels * (c * 4.0 + round_up(c, 8) * (double)sizeof(T)), 0); nchw_to_nhwc_kernel<T><<<grid, 256, 0, as_stream(stream)>>>(src, c, hw, pixels, static_cast<T*>(dst), ld, round_up(c, 8)); }
+    });
+    MSX_LAUNCH_CHECK();
+    return MSX_OK;
+}
+
+int msx_nhwc_to_nchw(int dtype, const void* src, int32_t ld, int32_t n, int32_t c, int32_t h, int32_t w, float* dst, void* stream) {
+    MSX_REQUIRE(src && dst, "nhwc_to_nchw: null pointer");
+    const int64_t hw = (int64_t)h * w, pixels = hw * n;
+    const int grid = (int)((pixels + 255) / 256 < kNumSMs * 8 ? (pixels + 255) / 256 : kNumSMs * 8);
+    MSX_DISPATCH_DTYPE(dtype, T, {
+        { ProfScope ps__(K_LAYOUT, as_stream(stream), (double)pixels * c * (4.0 + (double)sizeof(T)), 0); nhwc_to_nchw_kernel<T><<<grid, 256, 0, as_stream(stream)>>>(static_cast<const T*>(src), ld, c, hw, pixels, dst); }
+    });
+    MSX_LAUNCH_CHECK();
+    return MSX_OK;
+}
+
+}  // extern "C"

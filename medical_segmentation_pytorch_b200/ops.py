@@ -1,0 +1,418 @@
+"""Autograd bindings: each Function is a thin shim over one C-ABI composite of libmsx.so.
+
+Activations travel between modules as :class:`Act` - an NHWC tensor ``[N, H, W, round_up(C, 8)]``
+(fp32 or bf16; padded channels hold zeros) plus the logical channel count.  A tensor may alias a
+channel slice of a wider buffer (pixel stride ``ld`` > its own width), which is how UNet's
+``torch.cat`` (models/unet.py:66) becomes zero-copy.
+
+No op here has a PyTorch-eager or CPU implementation: everything calls the CUDA library.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib as L
+from ._lib import lib
+
+
+def rup(x, m=8):
+    return (x + m - 1) // m * m
+
+
+class Act:
+    """NHWC activation: tensor ``t`` [N,H,W,cp] (stride(3) == 1) and logical channels ``c``."""
+    __slots__ = ('t', 'c')
+
+    def __init__(self, t, c):
+        self.t, self.c = t, c
+
+    @property
+    def shape(self):
+        return self.t.shape
+
+    def nchw(self):
+        """Debug/test helper: fp32 NCHW copy of the logical channels."""
+        n, h, w, _ = self.t.shape
+        out = torch.empty(n, self.c, h, w, dtype=torch.float32, device=self.t.device)
+        L.check(lib.msx_nhwc_to_nchw(L.dtype_code(self.t.dtype), L.ptr(self.t), ld_of(self.t), n, self.c, h, w,
+                                     L.ptr(out), L.stream()))
+        return out
+
+
+def ld_of(t):
+    """Pixel stride of an NHWC tensor; validates that it is a dense-pixel layout."""
+    n, h, w, c = t.shape
+    s = t.stride()
+    ld = s[2]
+    if s[3] != 1 or ld % 8 or ld < c or s[1] != w * ld or s[0] != h * w * ld or (t.data_ptr() % 16):
+        raise L.MsxError(f'tensor with shape {tuple(t.shape)} stride {s} is not an NHWC activation layout')
+    return ld
+
+
+def as_act_layout(t):
+    """Return ``t`` if it is a valid NHWC layout, else a contiguous copy (rare: autograd-made grads)."""
+    n, h, w, c = t.shape
+    s = t.stride()
+    ok = s[3] == 1 and s[2] % 8 == 0 and s[2] >= c and s[1] == w * s[2] and s[0] == h * w * s[2] and t.data_ptr() % 16 == 0
+    return t if ok else t.contiguous()
+
+
+def alias_slice(buf, off, c):
+    """Tensor aliasing channels [off, off+c) of NHWC ``buf`` WITHOUT being an autograd view of it."""
+    n, h, w, ld = buf.shape
+    return torch.empty(0, dtype=buf.dtype, device=buf.device).set_(
+        buf.untyped_storage(), buf.storage_offset() + off, (n, h, w, c), (h * w * ld, w * ld, ld, 1))
+
+
+def alias(t):
+    """Tensor aliasing all of ``t`` (same size/stride) WITHOUT being an autograd view of it."""
+    return torch.empty(0, dtype=t.dtype, device=t.device).set_(t.untyped_storage(), t.storage_offset(), t.shape, t.stride())
+
+
+class OutSlot:
+    """Destination for a producer's output: channels [off, off+cp) of a preallocated NHWC buffer."""
+    __slots__ = ('buf', 'off')
+
+    def __init__(self, buf, off):
+        self.buf, self.off = buf, off
+
+
+def _out_tensor(slot, n, h, w, cp, dtype, device):
+    if slot is None:
+        return torch.empty(n, h, w, cp, dtype=dtype, device=device)
+    assert slot.buf.shape[:3] == (n, h, w) and slot.buf.dtype == dtype
+    return alias_slice(slot.buf, slot.off, cp)
+
+
+class ConvGeom:
+    """Static geometry of a conv module (mirrors nn.Conv2d / nn.ConvTranspose2d arguments)."""
+    __slots__ = ('cin', 'cout', 'kh', 'kw', 'stride', 'dil', 'pad_h', 'pad_w', 'transposed', 'out_pad', 'engine')
+
+    def __init__(self, cin, cout, kh, kw, stride=1, dil=1, pad_h=0, pad_w=0, transposed=False, out_pad=0, engine=L.ENGINE_AUTO):
+        self.cin, self.cout, self.kh, self.kw = cin, cout, kh, kw
+        self.stride, self.dil, self.pad_h, self.pad_w = stride, dil, pad_h, pad_w
+        self.transposed, self.out_pad, self.engine = transposed, out_pad, engine
+
+    def out_hw(self, h, w):
+        if not self.transposed:
+            return ((h + 2 * self.pad_h - self.dil * (self.kh - 1) - 1) // self.stride + 1,
+                    (w + 2 * self.pad_w - self.dil * (self.kw - 1) - 1) // self.stride + 1)
+        return ((h - 1) * self.stride - 2 * self.pad_h + self.dil * (self.kh - 1) + self.out_pad + 1,
+                (w - 1) * self.stride - 2 * self.pad_w + self.dil * (self.kw - 1) + self.out_pad + 1)
+
+    def desc(self, x, ldy, oh, ow):
+        n, h, w, _ = x.shape
+        return L.ConvDesc(n, h, w, self.cin, oh, ow, self.cout, self.kh, self.kw, self.stride, self.dil,
+                          self.pad_h, self.pad_w, ld_of(x), ldy, int(self.transposed), L.dtype_code(x.dtype), self.engine)
+
+
+_DEFAULT_ENGINE = [L.ENGINE_AUTO]
+
+
+def set_conv_engine(engine):
+    """Force the conv engine for subsequently built descriptors (tests: SIMT as comparator)."""
+    _DEFAULT_ENGINE[0] = {'auto': L.ENGINE_AUTO, 'simt': L.ENGINE_SIMT, 'tcgen05': L.ENGINE_TCGEN05}[engine]
+
+
+def _desc(g, x, ldy, oh, ow):
+    d = g.desc(x, ldy, oh, ow)
+    if d.engine == L.ENGINE_AUTO:
+        d.engine = _DEFAULT_ENGINE[0]
+    return d
+
+
+def _f32(t):
+    if t is not None and (t.dtype != torch.float32 or not t.is_contiguous()):
+        raise L.MsxError('parameters / statistics must be contiguous fp32')
+    return t
+
+
+def _pgrad(p):
+    """Destination of a parameter gradient: its slot in the flat gradient arena when the model has
+    been flattened (flat.py), else a fresh tensor handed back to autograd."""
+    g = getattr(p, '_msx_grad', None)
+    return g if g is not None else torch.empty_like(p)
+
+
+def _pdone(p, g):
+    """After the kernel writing ``g`` was enqueued: notify DDP bucket bookkeeping; arena-resident
+    gradients are not returned to autograd (it would copy them)."""
+    if g is not None and getattr(p, '_msx_grad', None) is g:
+        ready = getattr(p, '_msx_ready', None)
+        if ready is not None:
+            ready()
+        return None
+    return g
+
+
+def _grad_like_input(x):
+    """dx buffer with the SAME pixel stride as x (the C-ABI uses desc.ldx for both)."""
+    n, h, w, cp = x.shape
+    ld = ld_of(x)
+    if ld == cp:
+        return torch.empty(n, h, w, cp, dtype=x.dtype, device=x.device)
+    return alias_slice(torch.empty(n, h, w, ld, dtype=x.dtype, device=x.device), 0, cp)
+
+
+class AddFn(torch.autograd.Function):
+    """Plain n-way add (DuckNet `x5 + x` before mid_stage, models/ducknet.py:43) -> msx_sum_n."""
+
+    @staticmethod
+    def forward(ctx, c, *xs):
+        ctx.n = len(xs)
+        return sum_n(list(xs), c)
+
+    @staticmethod
+    def backward(ctx, g):
+        return (None,) + (g,) * ctx.n
+
+
+# ---------------------------------------------------------------------------------------------
+class ConvBNActFn(torch.autograd.Function):
+    """ConvBNAct / DeConvBNAct (models/modules.py:73-108) -> msx_conv_bn_act_{fwd,bwd}."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, gamma, beta, rm, rv, nbt, g, eps, momentum, training, relu, slot):
+        n, h, w, _ = x.shape
+        oh, ow = g.out_hw(h, w)
+        cp = rup(g.cout)
+        dev = x.device
+        y = torch.empty(n, oh, ow, cp, dtype=x.dtype, device=dev)
+        z = _out_tensor(slot, n, oh, ow, cp, x.dtype, dev)
+        mean = torch.empty(cp, dtype=torch.float32, device=dev)
+        invstd = torch.empty(cp, dtype=torch.float32, device=dev)
+        d = _desc(g, x, cp, oh, ow)
+        wsb = lib.msx_ws_bytes_conv(C.byref(d))
+        ws = L.workspace(wsb, dev)
+        pk = L.scratch('pack', lib.msx_conv_packed_bytes(C.byref(d)), dev)
+        L.check(lib.msx_conv_bn_act_fwd(
+            C.byref(d), L.ptr(x), L.ptr(_f32(weight)), L.ptr(_f32(bias)), L.ptr(_f32(gamma)), L.ptr(_f32(beta)),
+            L.ptr(rm), L.ptr(rv), L.ptr(nbt), eps, momentum, int(training), int(relu),
+            L.ptr(pk), L.ptr(y), L.ptr(z), ld_of(z), L.ptr(mean), L.ptr(invstd), L.ptr(ws), ws.numel(), L.stream()))
+        ctx.g, ctx.relu, ctx.d = g, relu, d
+        ctx.bias = bias                      # leaf parameter (or None); only its identity is needed
+        ctx.save_for_backward(x, weight, gamma, beta, y, mean, invstd)
+        return z
+
+    @staticmethod
+    def backward(ctx, dz):
+        x, weight, gamma, beta, y, mean, invstd = ctx.saved_tensors
+        dz = as_act_layout(dz)
+        d, dev = ctx.d, x.device
+        dy = torch.empty_like(y)
+        dx = _grad_like_input(x) if ctx.needs_input_grad[0] else None
+        bias = ctx.bias
+        dw = _pgrad(weight)
+        db = _pgrad(bias) if bias is not None else None
+        dgamma, dbeta = _pgrad(gamma), _pgrad(beta)
+        ws = L.workspace(lib.msx_ws_bytes_conv(C.byref(d)), dev)
+        pk = L.scratch('pack', lib.msx_conv_packed_bytes(C.byref(d)), dev)
+        L.check(lib.msx_conv_bn_act_bwd(
+            C.byref(d), L.ptr(x), L.ptr(weight), L.ptr(y), L.ptr(dz), ld_of(dz), L.ptr(gamma), L.ptr(beta),
+            L.ptr(mean), L.ptr(invstd), int(ctx.relu), L.ptr(pk), L.ptr(dy), L.ptr(dx), L.ptr(dw), L.ptr(db),
+            L.ptr(dgamma), L.ptr(dbeta), L.ptr(ws), ws.numel(), L.stream()))
+        # notify in arena order (reverse registration): bn.bias, bn.weight, conv.bias, conv.weight
+        dbeta, dgamma = _pdone(beta, dbeta), _pdone(gamma, dgamma)
+        db = _pdone(bias, db) if bias is not None else None
+        dw = _pdone(weight, dw)
+        return (dx, dw, db, dgamma, dbeta) + (None,) * 9
+
+
+class Conv2dFn(torch.autograd.Function):
+    """Bias-free conv without BN (ResidualBlock.upper_branch, models/ducknet.py:93) -> msx_conv2d_{fwd,bwd}."""
+
+    @staticmethod
+    def forward(ctx, x, weight, g):
+        n, h, w, _ = x.shape
+        oh, ow = g.out_hw(h, w)
+        cp = rup(g.cout)
+        y = torch.empty(n, oh, ow, cp, dtype=x.dtype, device=x.device)
+        d = _desc(g, x, cp, oh, ow)
+        pk = L.scratch('pack', lib.msx_conv_packed_bytes(C.byref(d)), x.device)
+        L.check(lib.msx_conv2d_fwd(C.byref(d), L.ptr(x), L.ptr(_f32(weight)), None, L.ptr(pk), L.ptr(y), L.stream()))
+        ctx.d = d
+        ctx.save_for_backward(x, weight)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, weight = ctx.saved_tensors
+        d = ctx.d
+        dy = as_act_layout(dy)
+        if ld_of(dy) != d.ldy:
+            d = L.ConvDesc.from_buffer_copy(d)
+            d.ldy = ld_of(dy)
+        dx = _grad_like_input(x) if ctx.needs_input_grad[0] else None
+        dw = _pgrad(weight)
+        ws = L.workspace(lib.msx_ws_bytes_conv(C.byref(d)), x.device)
+        pk = L.scratch('pack', lib.msx_conv_packed_bytes(C.byref(d)), x.device)
+        L.check(lib.msx_conv2d_bwd(C.byref(d), L.ptr(x), L.ptr(weight), L.ptr(dy), L.ptr(pk), L.ptr(dx), L.ptr(dw), None,
+                                   L.ptr(ws), ws.numel(), L.stream()))
+        return dx, _pdone(weight, dw), None
+
+
+def _ptr_arrays(ts):
+    n = len(ts)
+    ptrs = (C.c_void_p * n)(*[t.data_ptr() for t in ts])
+    lds = (C.c_int32 * n)(*[ld_of(t) for t in ts])
+    return ptrs, lds
+
+
+class SumBNActFn(torch.autograd.Function):
+    """(sum of inputs, first optionally nearest-2x upsampled) -> BN -> ReLU -> msx_sum_bn_act_fwd / msx_bn_act_bwd."""
+
+    @staticmethod
+    def forward(ctx, gamma, beta, rm, rv, nbt, c, eps, momentum, training, relu, up2x, slot, *xs):
+        ref = xs[1] if up2x else xs[0]
+        n, h, w, cp = ref.shape
+        dev, dt = ref.device, ref.dtype
+        need_sum = len(xs) > 1 or up2x
+        s = torch.empty(n, h, w, cp, dtype=dt, device=dev) if need_sum else None
+        z = _out_tensor(slot, n, h, w, cp, dt, dev)
+        mean = torch.empty(cp, dtype=torch.float32, device=dev)
+        invstd = torch.empty(cp, dtype=torch.float32, device=dev)
+        ptrs, lds = _ptr_arrays(xs)
+        ws = L.workspace(lib.msx_ws_bytes_bn(c), dev)
+        L.check(lib.msx_sum_bn_act_fwd(
+            L.dtype_code(dt), len(xs), ptrs, lds, int(up2x), n, h, w, c, L.ptr(s), cp if need_sum else 0,
+            L.ptr(_f32(gamma)), L.ptr(_f32(beta)), L.ptr(rm), L.ptr(rv), L.ptr(nbt), eps, momentum, int(training), int(relu),
+            L.ptr(z), ld_of(z), L.ptr(mean), L.ptr(invstd), L.ptr(ws), ws.numel(), L.stream()))
+        ctx.c, ctx.relu, ctx.up2x, ctx.nx = c, relu, up2x, len(xs)
+        ctx.x0_shape = xs[0].shape
+        ctx.save_for_backward(s if need_sum else xs[0], gamma, beta, mean, invstd)
+        return z
+
+    @staticmethod
+    def backward(ctx, dz):
+        s, gamma, beta, mean, invstd = ctx.saved_tensors
+        dz = as_act_layout(dz)
+        n, h, w, cp = s.shape
+        dev = s.device
+        ds = torch.empty(n, h, w, cp, dtype=s.dtype, device=dev)
+        dgamma, dbeta = _pgrad(gamma), _pgrad(beta)
+        ws = L.workspace(lib.msx_ws_bytes_bn(ctx.c), dev)
+        code = L.dtype_code(s.dtype)
+        L.check(lib.msx_bn_act_bwd(code, L.ptr(s), ld_of(s), L.ptr(dz), ld_of(dz), n * h * w, ctx.c, L.ptr(gamma), L.ptr(beta),
+                                   L.ptr(mean), L.ptr(invstd), int(ctx.relu), L.ptr(ds), cp, L.ptr(dgamma), L.ptr(dbeta),
+                                   L.ptr(ws), ws.numel(), L.stream()))
+        grads = [ds] * ctx.nx
+        if ctx.up2x:
+            da = torch.empty(ctx.x0_shape, dtype=s.dtype, device=dev)
+            L.check(lib.msx_upsample2x_bwd(code, L.ptr(ds), cp, n, h, w, ctx.c, L.ptr(da), ld_of(da), L.stream()))
+            grads[0] = da
+        for i in range(ctx.nx):
+            if not ctx.needs_input_grad[12 + i]:
+                grads[i] = None
+        dbeta, dgamma = _pdone(beta, dbeta), _pdone(gamma, dgamma)
+        return (dgamma, dbeta) + (None,) * 10 + tuple(grads)
+
+
+def sum_n(ts, c):
+    """out = sum(ts) with the library's n-way sum kernel (<= 8 inputs per launch)."""
+    ts = [as_act_layout(t) for t in ts]
+    out = torch.empty(ts[0].shape, dtype=ts[0].dtype, device=ts[0].device)
+    n, h, w, cp = out.shape
+    code = L.dtype_code(out.dtype)
+    first = True
+    while ts:
+        chunk = ts[:8] if first else [out] + ts[:7]
+        ts = ts[8:] if first else ts[7:]
+        first = False
+        ptrs, lds = _ptr_arrays(chunk)
+        L.check(lib.msx_sum_n(code, len(chunk), ptrs, lds, n * h * w, c, L.ptr(out), cp, L.stream()))
+    return out
+
+
+class FanoutFn(torch.autograd.Function):
+    """Identity with k outputs; backward adds the k gradients in ONE pass (msx_sum_n) instead of the
+    k-1 pairwise adds autograd would issue (DUCK.in_bn output feeds nine convs, models/ducknet.py:144-149)."""
+
+    @staticmethod
+    def forward(ctx, x, k, c):
+        ctx.c = c
+        return tuple(alias(x) for _ in range(k))
+
+    @staticmethod
+    def backward(ctx, *gs):
+        gs = [g for g in gs if g is not None]
+        if len(gs) == 1:
+            return gs[0], None, None
+        return sum_n(gs, ctx.c), None, None
+
+
+class MaxPoolFn(torch.autograd.Function):
+    """nn.MaxPool2d(3, 2, 1) (models/unet.py:49) -> msx_maxpool3s2_{fwd,bwd}."""
+
+    @staticmethod
+    def forward(ctx, x, c):
+        n, h, w, cp = x.shape
+        oh, ow = (h - 1) // 2 + 1, (w - 1) // 2 + 1
+        z = torch.empty(n, oh, ow, cp, dtype=x.dtype, device=x.device)
+        idx = torch.empty(n, oh, ow, cp, dtype=torch.int8, device=x.device)
+        L.check(lib.msx_maxpool3s2_fwd(L.dtype_code(x.dtype), L.ptr(x), ld_of(x), n, h, w, c, L.ptr(z), cp, L.ptr(idx), cp, L.stream()))
+        ctx.c, ctx.xshape = c, x.shape
+        ctx.save_for_backward(idx)
+        return z
+
+    @staticmethod
+    def backward(ctx, dz):
+        idx, = ctx.saved_tensors
+        dz = as_act_layout(dz)
+        n, h, w, cp = ctx.xshape
+        dx = torch.empty(ctx.xshape, dtype=dz.dtype, device=dz.device)
+        L.check(lib.msx_maxpool3s2_bwd(L.dtype_code(dz.dtype), L.ptr(dz), ld_of(dz), L.ptr(idx), cp, n, h, w, ctx.c, L.ptr(dx), cp, L.stream()))
+        return dx, None
+
+
+class ConcatFn(torch.autograd.Function):
+    """torch.cat([a, b], dim=1) (models/unet.py:66) with zero copies: both producers already wrote
+    their channels into ``buf``; backward hands out channel slices of the incoming gradient."""
+
+    @staticmethod
+    def forward(ctx, a, b, buf, ca):
+        assert a.data_ptr() == buf.data_ptr() and b.data_ptr() == buf.data_ptr() + ca * buf.element_size()
+        ctx.ca = ca
+        return alias_slice(buf, 0, buf.shape[3])
+
+    @staticmethod
+    def backward(ctx, g):
+        g = as_act_layout(g)
+        ca = ctx.ca
+        return alias_slice(g, 0, ca), alias_slice(g, ca, g.shape[3] - ca), None, None
+
+
+class HeadFn(torch.autograd.Function):
+    """seg_head conv1x1 (models/unet.py:27,41) -> msx_head_{fwd,bwd}; returns NCHW fp32 logits."""
+
+    @staticmethod
+    def forward(ctx, x, weight, c):
+        n, h, w, _ = x.shape
+        nc = weight.shape[0]
+        logits = torch.empty(n, nc, h, w, dtype=torch.float32, device=x.device)
+        L.check(lib.msx_head_fwd(L.dtype_code(x.dtype), L.ptr(x), ld_of(x), n, h, w, c, L.ptr(_f32(weight)), nc, L.ptr(logits), L.stream()))
+        ctx.c = c
+        ctx.save_for_backward(x, weight)
+        return logits
+
+    @staticmethod
+    def backward(ctx, dl):
+        x, weight = ctx.saved_tensors
+        n, h, w, cp = x.shape
+        dl = dl.contiguous().float()
+        dx = torch.empty(n, h, w, cp, dtype=x.dtype, device=x.device) if ctx.needs_input_grad[0] else None
+        dw = _pgrad(weight)
+        ws = L.workspace(lib.msx_ws_bytes_bn(ctx.c), x.device)
+        L.check(lib.msx_head_bwd(L.dtype_code(x.dtype), L.ptr(x), ld_of(x), n, h, w, ctx.c, L.ptr(weight), weight.shape[0],
+                                 L.ptr(dl), L.ptr(dx), cp, L.ptr(dw), L.ptr(ws), ws.numel(), L.stream()))
+        return dx, _pdone(weight, dw), None
+
+
+def to_nhwc(images, dtype):
+    """NCHW fp32 images (core/seg_trainer.py:35) -> NHWC activation (no gradient to the images)."""
+    if images.dtype != torch.float32:
+        images = images.float()
+    images = images.contiguous()
+    n, c, h, w = images.shape
+    out = torch.empty(n, h, w, rup(c), dtype=dtype, device=images.device)
+    L.check(lib.msx_nchw_to_nhwc(L.dtype_code(dtype), L.ptr(images), n, c, h, w, L.ptr(out), rup(c), L.stream()))
+    return Act(out, c)

@@ -1,0 +1,310 @@
+"""-m gpu: per-kernel parity of the CUDA path (through the package's public ops -> C-ABI) against
+CPU float64 PyTorch restatements of the same op.  Tolerances: fp32 path 1e-5 rel-L2 per op
+(north_star: fp32 within 1e-4); bf16 path 2e-2 rel-L2 with bf16-rounded inputs; integer work bit-exact."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+from gpu_util import DEV, Cfg, from_act, rel, to_act  # noqa: E402
+
+
+def _ops():
+    from medical_segmentation_pytorch_b200 import ops
+    return ops
+
+
+CONV_CASES = [
+    # cin, cout, kh, kw, stride, dil, H, W
+    (3, 17, 3, 3, 1, 1, 20, 24),
+    (17, 17, 3, 3, 1, 2, 16, 16),
+    (17, 34, 3, 3, 1, 3, 16, 12),
+    (34, 68, 3, 3, 2, 1, 16, 16),
+    (3, 34, 2, 2, 2, 1, 16, 16),
+    (24, 40, 1, 1, 1, 1, 9, 11),
+    (17, 17, 1, 7, 1, 1, 12, 20),
+    (17, 17, 7, 1, 1, 1, 20, 12),
+    (64, 96, 3, 3, 1, 1, 11, 11),
+    (136, 72, 3, 3, 1, 1, 8, 8),
+]
+
+
+@pytest.mark.parametrize('case', CONV_CASES)
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_conv2d_fwd_bwd(case, dtype):
+    ops = _ops()
+    cin, cout, kh, kw, stride, dil, H, W = case
+    torch.manual_seed(sum(case))
+    n = 2
+    x = torch.randn(n, cin, H, W)
+    w = torch.randn(cout, cin, kh, kw) / (cin * kh * kw) ** 0.5
+    if dtype == torch.bfloat16:
+        x, w = x.bfloat16().float(), w.bfloat16().float()
+    pad = ((kh - 1) // 2 * dil, (kw - 1) // 2 * dil)
+    xd, wd = x.double().requires_grad_(True), w.double().requires_grad_(True)
+    yref = F.conv2d(xd, wd, None, stride, pad, dil)
+    dy = torch.randn(yref.shape)
+    if dtype == torch.bfloat16:
+        dy = dy.bfloat16().float()
+    yref.backward(dy.double())
+
+    g = ops.ConvGeom(cin, cout, kh, kw, stride, dil, pad[0], pad[1], engine=1)     # SIMT engine
+    a = to_act(x, dtype, requires_grad=True)
+    wp = torch.nn.Parameter(w.to(DEV))
+    y = ops.Conv2dFn.apply(a.t, wp, g)
+    assert y.shape[3] == ops.rup(cout) and float(y[..., cout:].abs().sum()) == 0.0     # padded channels stay zero
+    y.backward(to_act(dy, dtype).t)
+    tol = 1e-5 if dtype == torch.float32 else 2e-2
+    assert rel(from_act(y, cout), yref) < tol
+    assert rel(from_act(a.t.grad, cin), xd.grad) < tol
+    assert rel(wp.grad, wd.grad) < tol
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_conv_transpose_bn_relu(dtype):
+    """DeConvBNAct: ConvTranspose2d(3, s2, p1, op1, bias) -> BN(train) -> ReLU, forward and all gradients."""
+    import medical_segmentation_pytorch_b200 as msx
+    torch.manual_seed(3)
+    cin, cout, n, H = 16, 8, 2, 6
+    m = msx.modules.DeConvBNAct(cin, cout).to(DEV)
+    ref = torch.nn.Sequential(torch.nn.ConvTranspose2d(cin, cout, 3, 2, 1, 1), torch.nn.BatchNorm2d(cout), torch.nn.ReLU()).double()
+    with torch.no_grad():
+        m.up_conv[1].weight.uniform_(0.5, 1.5)
+        m.up_conv[1].bias.uniform_(-0.3, 0.3)
+        if dtype == torch.bfloat16:
+            m.up_conv[0].weight.copy_(m.up_conv[0].weight.bfloat16().float())
+    ref.load_state_dict({k.replace('up_conv.', ''): v.double().cpu() for k, v in m.state_dict().items()})
+    x = torch.randn(n, cin, H, H)
+    if dtype == torch.bfloat16:
+        x = x.bfloat16().float()
+    xd = x.double().requires_grad_(True)
+    yref = ref(xd)
+    dy = torch.randn(yref.shape)
+    yref.backward(dy.double())
+    a = to_act(x, dtype, requires_grad=True)
+    z = m(a)
+    z.t.backward(to_act(dy, dtype).t)
+    tol = 2e-5 if dtype == torch.float32 else 3e-2
+    assert rel(from_act(z.t, cout), yref) < tol
+    assert rel(from_act(a.t.grad, cin), xd.grad) < tol * 5
+    assert rel(m.up_conv[0].weight.grad, ref[0].weight.grad) < tol * 5
+    assert rel(m.up_conv[1].weight.grad, ref[1].weight.grad) < tol * 5
+    assert rel(m.up_conv[1].bias.grad, ref[1].bias.grad) < tol * 5
+    # conv bias gradient is analytically zero when BN follows
+    assert float(m.up_conv[0].bias.grad.abs().max()) < 1e-3 * float(m.up_conv[1].bias.grad.abs().max() + 1e-6) + 1e-4
+    if dtype == torch.float32:
+        assert rel(m.up_conv[1].running_mean, ref[1].running_mean) < 1e-5
+        assert rel(m.up_conv[1].running_var, ref[1].running_var) < 1e-5
+        assert int(m.up_conv[1].num_batches_tracked) == 1
+
+
+@pytest.mark.parametrize('c', [3, 17, 40, 272])
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_sum_bn_relu_and_upsample(c, dtype):
+    """(nearest-2x(a) + b) -> BN(train) -> ReLU vs F.interpolate/+/batch_norm/relu in float64."""
+    import medical_segmentation_pytorch_b200 as msx
+    torch.manual_seed(c)
+    n, h, w = 2, 6, 10
+    bn = torch.nn.BatchNorm2d(c).to(DEV)
+    with torch.no_grad():
+        bn.weight.uniform_(0.5, 1.5)
+        bn.bias.uniform_(-0.3, 0.3)
+    a, b = torch.randn(n, c, h // 2, w // 2) + 0.5, torch.randn(n, c, h, w)
+    if dtype == torch.bfloat16:
+        a, b = a.bfloat16().float(), b.bfloat16().float()
+    ad, bd = a.double().requires_grad_(True), b.double().requires_grad_(True)
+    gd, btd = bn.weight.detach().double().cpu().requires_grad_(True), bn.bias.detach().double().cpu().requires_grad_(True)
+    s = F.interpolate(ad, (h, w), mode='nearest') + bd
+    if dtype == torch.bfloat16:
+        s = s + (s.detach().float().bfloat16().double() - s.detach())        # stored sum is bf16-rounded
+    zref = F.relu(F.batch_norm(s, None, None, gd, btd, True, 0.1, 1e-5))
+    dz = torch.randn(zref.shape)
+    zref.backward(dz.double())
+    aa, ba = to_act(a, dtype, True), to_act(b, dtype, True)
+    z = msx.modules.sum_bn_act([aa, ba], bn, 1, up2x=True)
+    z.t.backward(to_act(dz, dtype).t)
+    tol = 1e-5 if dtype == torch.float32 else 2e-2
+    assert rel(from_act(z.t, c), zref) < tol
+    assert rel(from_act(aa.t.grad, c), ad.grad) < tol * 3
+    assert rel(from_act(ba.t.grad, c), bd.grad) < tol * 3
+    assert rel(bn.weight.grad, gd.grad) < tol * 3
+    assert rel(bn.bias.grad, btd.grad) < tol * 3
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_maxpool_3s2(dtype):
+    ops = _ops()
+    torch.manual_seed(0)
+    x = torch.randn(2, 24, 10, 14)
+    if dtype == torch.bfloat16:
+        x = x.bfloat16().float()
+    xd = x.double().requires_grad_(True)
+    zref = F.max_pool2d(xd, 3, 2, 1)
+    dz = torch.randn(zref.shape)
+    zref.backward(dz.double())
+    a = to_act(x, dtype, True)
+    z = ops.MaxPoolFn.apply(a.t, 24)
+    z.backward(to_act(dz, dtype).t)
+    assert rel(from_act(z, 24), zref) < (1e-7 if dtype == torch.float32 else 1e-7)
+    assert rel(from_act(a.t.grad, 24), xd.grad) < (1e-6 if dtype == torch.float32 else 1e-2)
+
+
+@pytest.mark.parametrize('nc', [1, 2, 5])
+def test_head(nc):
+    ops = _ops()
+    torch.manual_seed(nc)
+    c, n, h, w = 17, 2, 8, 12
+    x, wt = torch.randn(n, c, h, w), torch.randn(nc, c, 1, 1)
+    xd, wd = x.double().requires_grad_(True), wt.double().requires_grad_(True)
+    ref = F.conv2d(xd, wd)
+    dl = torch.randn(ref.shape)
+    ref.backward(dl.double())
+    a = to_act(x, torch.float32, True)
+    wp = torch.nn.Parameter(wt.to(DEV))
+    out = ops.HeadFn.apply(a.t, wp, c)
+    out.backward(dl.to(DEV))
+    assert rel(out, ref) < 1e-6 and rel(from_act(a.t.grad, c), xd.grad) < 1e-6 and rel(wp.grad, wd.grad) < 1e-6
+
+
+# ---- losses ------------------------------------------------------------------------------------
+def _loss_and_grad(fn, z):
+    zz = z.clone().to(DEV).requires_grad_(True)
+    v = fn(zz)
+    v.backward()
+    return float(v), zz.grad.cpu()
+
+
+def test_losses_match_golden(golden_dir):
+    """CUDA losses vs outputs of the REAL reference (tests/golden/losses.npz)."""
+    import os
+    import medical_segmentation_pytorch_b200 as msx
+    g = np.load(os.path.join(golden_dir, 'losses.npz'))
+    z, zt, t = torch.from_numpy(g['logits']), torch.from_numpy(g['teacher']).to(DEV), torch.from_numpy(g['labels']).to(DEV)
+    cases = {
+        'ce': msx.get_loss_fn(Cfg(), DEV),
+        'ce_weighted': msx.get_loss_fn(Cfg(class_weights=g['class_weights'].tolist()), DEV),
+        'ohem_thresh_branch': msx.get_loss_fn(Cfg(loss_type='ohem', ohem_thrs=0.7), DEV),
+        'ohem_topk_branch': msx.get_loss_fn(Cfg(loss_type='ohem', ohem_thrs=float(g['ohem_topk_thresh'])), DEV),
+    }
+    for key, fn in cases.items():
+        v, gr = _loss_and_grad(lambda zz: fn(zz, t), z)
+        assert abs(v - float(g[key])) < 1e-5 * max(1.0, abs(float(g[key]))), key
+        assert rel(gr, g[key + '_grad']) < 1e-5, key
+    for kind in ('kl_div', 'mse'):
+        cfg = Cfg(kd_loss_type=kind)
+        v, gr = _loss_and_grad(lambda zz: msx.kd_loss_fn(cfg, zz, zt), z)
+        assert abs(v - float(g['kd_' + kind])) < 1e-5 * max(1.0, abs(float(g['kd_' + kind]))), kind
+        assert rel(gr, g['kd_' + kind + '_grad']) < 1e-5, kind
+
+
+@pytest.mark.parametrize('shape', [(2, 2, 16, 20), (3, 2, 7, 9), (1, 5, 8, 8), (2, 11, 6, 6)])
+def test_ce_vs_oracle_shapes(shape):
+    """vector (hw%4==0) and scalar paths, register-resident and generic class counts, 'sum', upstream scale."""
+    import medical_segmentation_pytorch_b200 as msx
+    from oracle import ref_loss
+    torch.manual_seed(shape[1])
+    n, c, h, w = shape
+    z = torch.randn(shape) * 3
+    t = torch.randint(0, c, (n, h, w))
+    t[torch.rand(n, h, w) < 0.2] = 255
+    for red in ('mean', 'sum'):
+        fn = msx.get_loss_fn(Cfg(reduction=red), DEV)
+        v, gr = _loss_and_grad(lambda zz: fn(zz, t.to(DEV)) * 0.5, z)
+        zd = z.double().requires_grad_(True)
+        ref = ref_loss.ce_loss(zd, t, None, 255, red) * 0.5
+        ref.backward()
+        assert abs(v - ref.item()) < 2e-6 * max(1, abs(ref.item()))
+        assert rel(gr, zd.grad) < 1e-5
+    fn = msx.get_loss_fn(Cfg(reduction='none'), DEV)
+    zz = z.clone().to(DEV).requires_grad_(True)
+    per = fn(zz, t.to(DEV))
+    coef = torch.rand(n, h, w)
+    (per * coef.to(DEV)).sum().backward()
+    zd = z.double().requires_grad_(True)
+    refp = ref_loss.ce_loss(zd, t, None, 255, 'none')
+    (refp * coef.double()).sum().backward()
+    assert rel(per, refp) < 1e-6 and rel(zz.grad, zd.grad) < 1e-5
+
+
+def test_ce_all_ignored_is_nan_with_zero_grad():
+    import medical_segmentation_pytorch_b200 as msx
+    fn = msx.get_loss_fn(Cfg(), DEV)
+    z = torch.randn(1, 2, 4, 4, device=DEV, requires_grad=True)
+    t = torch.full((1, 4, 4), 255, dtype=torch.int64, device=DEV)
+    v = fn(z, t)
+    v.backward()
+    assert torch.isnan(v) and float(z.grad.abs().sum()) == 0.0
+
+
+def test_dice_bce_vs_oracle():
+    import medical_segmentation_pytorch_b200 as msx
+    from oracle import ref_loss
+    torch.manual_seed(1)
+    z = torch.randn(2, 1, 12, 10) * 2
+    for t in ((torch.rand(2, 12, 10) > 0.7).long(), (torch.rand(2, 1, 12, 10) > 0.7).float()):
+        fn = msx.get_loss_fn(Cfg(loss_type='dice_bce'), DEV)
+        v, gr = _loss_and_grad(lambda zz: fn(zz, t.to(DEV)), z)
+        zd = z.double().requires_grad_(True)
+        ref = ref_loss.dice_bce_loss(zd, t.double())
+        ref.backward()
+        assert abs(v - ref.item()) < 2e-6 and rel(gr, zd.grad) < 1e-5
+
+
+# ---- metrics -----------------------------------------------------------------------------------
+def test_confmat_bit_exact_with_ties_nan_ignore():
+    import medical_segmentation_pytorch_b200 as msx
+    from oracle import ref_metrics
+    rng = np.random.default_rng(5)
+    for c, shape in ((2, (3, 2, 16, 20)), (2, (1, 2, 7, 9)), (4, (2, 4, 8, 8)), (7, (2, 7, 8, 12))):
+        z = rng.standard_normal(shape).astype(np.float32)
+        z[rng.uniform(size=shape) < 0.1] = 0.5                  # many exact ties
+        z[rng.uniform(size=shape) < 0.02] = np.nan
+        t = rng.integers(0, c, size=(shape[0],) + shape[2:])
+        t[rng.uniform(size=t.shape) < 0.1] = 255
+        cfg = Cfg(num_class=c)
+        m = msx.get_seg_metrics(cfg, 'iou').to(DEV)
+        for _ in range(2):
+            m.update(torch.from_numpy(z).to(DEV), torch.from_numpy(t).to(DEV))
+        want = 2 * ref_metrics.confusion_matrix(z, t, c, 255)
+        assert np.array_equal(m.confmat.cpu().numpy(), want)
+        got = m.compute().cpu().numpy()
+        assert np.array_equal(got, ref_metrics.iou_per_class(want))          # float32 ratios, same cast order
+        m.reset()
+        assert int(m.confmat.sum()) == 0
+        # Dice has no ignore_index: a 255 label must raise at compute(), like torchmetrics' validation
+        d = msx.get_seg_metrics(cfg, 'dice').to(DEV)
+        d.update(torch.from_numpy(z).to(DEV), torch.from_numpy(t).to(DEV))
+        with pytest.raises(ValueError):
+            d.compute()
+        d.reset()
+        t2 = np.where(t == 255, 0, t)
+        d.update(torch.from_numpy(z).to(DEV), torch.from_numpy(t2).to(DEV))
+        cm2 = ref_metrics.confusion_matrix(z, t2, c, None)
+        assert np.array_equal(d.confmat.cpu().numpy(), cm2)
+        assert float(d.compute()) == float(ref_metrics.dice_macro(cm2))
+    with pytest.raises(ValueError):
+        msx.get_seg_metrics(Cfg(), 'f1')
+
+
+def test_full_size_properties():
+    """BASELINE config-2 size (16x2x352x352): size-independent properties instead of a CPU oracle."""
+    import medical_segmentation_pytorch_b200 as msx
+    from medical_segmentation_pytorch_b200.synth import synth_batch
+    n, h = 16, 352
+    _, mask = synth_batch(n, h, h, seed=1, ignore_band=0.05)
+    torch.manual_seed(0)
+    z = torch.randn(n, 2, h, h, device=DEV, requires_grad=True)
+    mask = mask.to(DEV)
+    m = msx.get_seg_metrics(Cfg(), 'iou').to(DEV)
+    m.update(z, mask)
+    assert int(m.confmat.sum()) == int((mask != 255).sum())                        # every valid pixel counted once
+    assert torch.equal(m.confmat.sum(1), torch.stack([(mask == 0).sum(), (mask == 1).sum()]))   # row sums = label histogram
+    loss = msx.get_loss_fn(Cfg(), DEV)(z, mask)
+    loss.backward()
+    g = z.grad
+    assert float(g.sum(1).abs().max()) < 1e-9                                       # softmax - onehot sums to 0 over classes
+    assert float(g[:, 0][mask == 255].abs().max()) == 0.0                            # ignored pixels get no gradient
+    want = torch.nn.functional.cross_entropy(z.detach(), mask, ignore_index=255)     # same-device library check of the scalar
+    assert abs(float(loss) - float(want)) < 1e-5

@@ -1,0 +1,136 @@
+"""-m gpu: whole-model parity of the CUDA path against vectors from the REAL reference modules
+(tests/golden/*.npz; fp64 run = ground truth, fp32 run = the reference's own noise floor).
+
+Protocol: an error of the new path against fp64 truth must not exceed
+max(3 x the reference-fp32 error against the same truth, floor).  Loss within 1e-4 relative
+(north_star fp32 tolerance).  bf16 (autocast) tolerance, stated: loss within 5e-2 relative, logits
+rel-L2 < 0.35 on these random-init nets (the reference's own CPU bf16 autocast shows 0.14 on UNet-32)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from gpu_util import DEV, Cfg, rel  # noqa: E402
+
+
+def _build(name, base):
+    import medical_segmentation_pytorch_b200 as msx
+    from oracle import ref_models
+    cls = msx.UNet if name == 'unet' else msx.DuckNet
+    return cls(num_class=2, n_channel=3, base_channel=base).to(DEV), ref_models
+
+
+@pytest.mark.parametrize('name,fname', [('unet', 'unet_b8_32.npz'), ('ducknet', 'ducknet_b3_64.npz')])
+def test_model_fp32_vs_reference_golden(golden_dir, name, fname):
+    import medical_segmentation_pytorch_b200 as msx
+    g = np.load(os.path.join(golden_dir, fname))
+    base = int(g['base_channel'])
+    model, ref_models = _build(name, base)
+    sd = ref_models.synth_state_dict(ref_models.model_layout(name, num_class=2, n_channel=3, base_channel=base), int(g['weight_seed']))
+    model.load_state_dict(sd)                               # reference key layout loads unchanged
+    model.train()
+    x, t = torch.from_numpy(g['images']).to(DEV), torch.from_numpy(g['masks']).to(DEV)
+    logits = model(x)
+    loss = msx.get_loss_fn(Cfg(), DEV)(logits, t)
+    loss.backward()
+    floor = 2e-5
+    e_ref = rel(g['logits_f32'], g['logits_f64'])
+    e_new = rel(logits, g['logits_f64'])
+    print(f'{name}: logits err new {e_new:.2e} ref-fp32 {e_ref:.2e}')
+    assert e_new <= max(3 * e_ref, floor)
+    assert abs(float(loss) - float(g['loss_f64'])) <= 1e-4 * abs(float(g['loss_f64']))
+    names = [str(s) for s in g['param_names']]
+    params = dict(model.named_parameters())
+    assert names == list(params.keys())
+    gn = np.array([float(params[k].grad.norm()) for k in names])
+    t64, r32 = g['grad_norms_f64'], g['grad_norms_f32']
+    big = t64 > 1e-9 * t64.max()
+    e_gn_new = np.abs(gn[big] / t64[big] - 1)
+    e_gn_ref = np.abs(r32[big] / t64[big] - 1)
+    print(f'{name}: grad-norm err median new {np.median(e_gn_new):.2e} ref {np.median(e_gn_ref):.2e}; max new {e_gn_new.max():.2e} ref {e_gn_ref.max():.2e}')
+    assert np.median(e_gn_new) <= max(3 * np.median(e_gn_ref), 1e-4)
+    assert e_gn_new.max() <= max(3 * e_gn_ref.max(), 1e-3)
+    for k in g.files:
+        if k.startswith('grad_f64::'):
+            pn = k.split('::')[1]
+            e_r = rel(g['grad_f32::' + pn], g[k])
+            assert rel(params[pn].grad, g[k]) <= max(3 * e_r, 1e-4), pn
+        if k.startswith('buf_f64::'):
+            bn = k.split('::')[1]
+            assert rel(model.state_dict()[bn], g[k]) <= max(3 * rel(g['buf_f32::' + bn], g[k]), 1e-5), bn
+    assert int(model.state_dict()[[k for k in model.state_dict() if k.endswith('num_batches_tracked')][0]]) == 1
+    # validation path: eval-mode BN with the just-updated running statistics, no autograd
+    model.eval()
+    with torch.no_grad():
+        ev = model(x)
+    assert rel(ev, g['eval_logits_f64']) <= max(3 * rel(g['eval_logits_f32'], g['eval_logits_f64']), floor)
+    # state_dict round trip back into the reference layout
+    out = model.state_dict()
+    assert list(out.keys()) == list(sd.keys()) and all(tuple(out[k].shape) == tuple(sd[k].shape) for k in sd)
+
+
+@pytest.mark.parametrize('name,fname', [('unet', 'unet_b8_32.npz'), ('ducknet', 'ducknet_b3_64.npz')])
+def test_model_bf16_autocast(golden_dir, name, fname):
+    import medical_segmentation_pytorch_b200 as msx
+    g = np.load(os.path.join(golden_dir, fname))
+    base = int(g['base_channel'])
+    model, ref_models = _build(name, base)
+    model.load_state_dict(ref_models.synth_state_dict(ref_models.model_layout(name, num_class=2, n_channel=3, base_channel=base), int(g['weight_seed'])))
+    model.train()
+    x, t = torch.from_numpy(g['images']).to(DEV), torch.from_numpy(g['masks']).to(DEV)
+    with torch.autocast('cuda', dtype=torch.bfloat16):          # the reference's AMP switch (core/seg_trainer.py:61)
+        logits = model(x)
+        loss = msx.get_loss_fn(Cfg(), DEV)(logits, t)
+    loss.backward()
+    assert logits.dtype == torch.float32
+    e = rel(logits, g['logits_f64'])
+    print(f'{name} bf16: logits rel-L2 {e:.3e}, loss {float(loss):.5f} vs {float(g["loss_f64"]):.5f}')
+    assert e < 0.35
+    assert abs(float(loss) - float(g['loss_f64'])) <= 5e-2 * abs(float(g['loss_f64']))
+    assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in model.parameters())
+
+
+def test_train_step_flat_arena_matches_autograd_path():
+    """FlatParams + fused Adam + EMA copy: same gradients as the plain autograd path, parameters move
+    exactly like torch.optim.Adam, EMA model equals the model (use_ema=False copies, utils/model_ema.py:39-40)."""
+    import medical_segmentation_pytorch_b200 as msx
+    from medical_segmentation_pytorch_b200.flat import FlatParams
+    from medical_segmentation_pytorch_b200.synth import synth_batch
+    torch.manual_seed(1)
+    a = msx.DuckNet(2, 3, 2).to(DEV)
+    b = msx.DuckNet(2, 3, 2).to(DEV)
+    b.load_state_dict(a.state_dict())
+    x, t = synth_batch(2, 32, 32, seed=3)
+    x, t = x.to(DEV), t.to(DEV)
+    lf = msx.get_loss_fn(Cfg(), DEV)
+    lf(a(x), t).backward()
+    ref_grads = [p.grad.clone() for p in a.parameters()]
+    opt_ref = torch.optim.Adam(a.parameters(), lr=1e-3)
+    opt_ref.step()
+    FlatParams(b)
+    opt = msx.FusedOptimizer(b, 'adam', lr=1e-3)
+    ema = msx.ModelEma(b)
+    lf(b(x), t).backward()
+    for p, gr in zip(b.parameters(), ref_grads):
+        assert torch.equal(p.grad, gr)                       # same kernels, same order: bit-identical
+    opt.step()
+    ema.update(b, 1)
+    for pa, pb in zip(a.parameters(), b.parameters()):
+        assert rel(pb, pa) < 1e-6
+    for (ka, va), (kb, vb) in zip(b.state_dict().items(), ema.ema.state_dict().items()):
+        assert ka == kb and torch.equal(va, vb)
+
+
+def test_unknown_names_raise_like_the_reference():
+    import medical_segmentation_pytorch_b200 as msx
+    with pytest.raises(NotImplementedError):
+        msx.get_model(Cfg(model='resnet'))
+    with pytest.raises(NotImplementedError):
+        msx.get_loss_fn(Cfg(loss_type='focal'), DEV)
+    with pytest.raises(ValueError):
+        msx.get_model(Cfg(model='unet', use_aux=True))
+    with pytest.raises(NotImplementedError):
+        msx.modules.Activation('swishh')
