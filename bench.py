@@ -1,0 +1,276 @@
+#!/usr/bin/env python
+"""Headline benchmark: DUCKNet-17 training step at 352x352 (BASELINE.json metric "train imgs/sec").
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --steps K --warmup W     # the reference's CPU step (oracle port)
+
+One "step" = zero_grad -> forward -> CrossEntropyLoss -> backward (+ bucketed gradient all-reduce
+when N > 1) -> Adam -> EMA state copy, the body of core/seg_trainer.py:38-87, on one synthetic batch
+per GPU.  Prints ONE JSON line on rank 0 (see the contract in the task statement):
+  value      img/s with inputs already resident in HBM (CUDA events, max over ranks)
+  e2e        same step driven from pinned HOST buffers (H2D of images+masks and D2H of the loss inside
+             the timed region)
+  roofline   the dominant kernel class of a profiled pass (live CUDA-event timings per launch,
+             algorithmic bytes/flops booked by the library) against MEASURED_PEAKS.json
+  cpu_baseline  the oracle port of the reference step timed on this box's host cores (rank 0, N=1)
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+MODELS = {  # name -> (arch, base_channel, train GFLOP/img @352 (2*MAC*3), conv activation GB/img bf16)  SURVEY.md §8d
+    'ducknet17': ('ducknet', 17, 279.7, 2.197),
+    'ducknet34': ('ducknet', 34, 1114.3, 4.370),
+    'unet32': ('unet', 32, 144.6, 0.467),
+}
+
+
+def peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {'hbm_gbs': d['hbm_gbs'], 'tf': d.get('bf16_tflops_sustained', d['bf16_tflops']), 'tf_burst': d['bf16_tflops'], 'src': 'measured'}
+    return {'hbm_gbs': 6650.0, 'tf': 1400.0, 'tf_burst': 1590.0, 'src': 'fallback'}
+
+
+class ClockSampler:
+    """nvidia-smi clock / throttle sampling DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = 'index,clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,' \
+        'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap'
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', f'--query-gpu={self.Q}', '--format=csv,noheader,nounits', '-lms', '200',
+                                          '-i', str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(',')])
+
+    def stop(self):
+        if not self.proc:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.25)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1]))
+                mx = float(r[2])
+                for name, v in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'), r[3:7]):
+                    if v.lower().startswith('active'):
+                        reasons.add(name)
+            except Exception:
+                pass
+        sm.sort()
+        return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': mx, 'reasons': sorted(reasons), 'samples': len(sm)}
+
+
+def cpu_reference_leg(name, steps, warmup, batch=2, hw=352):
+    """The reference's CPU training step (oracle port) on this box's host cores."""
+    import torch
+    from medical_segmentation_pytorch_b200.synth import synth_batch
+    from oracle.ref_step import CpuTrainer
+    arch, base, _, _ = MODELS[name]
+    cores = os.cpu_count() or 1
+    threads = max(1, cores // 2) if cores > 16 else cores          # physical cores on SMT hosts
+    tr = CpuTrainer(arch, base, 2, seed=1, lr=1e-3, threads=threads)
+    x, t = synth_batch(batch, hw, hw, seed=1)
+    sec = tr.time_steps(x, t, steps, warmup)
+    return {'value': batch / sec, 'unit': 'img/s', 'cores': threads, 'kind': 'port',
+            'sample': f'{steps} timed step(s) after {warmup} warm-up of {name} batch {batch} at {hw}x{hw} fp32 '
+                      f'(oracle/ref_step.py: forward+CE+backward+Adam+EMA copy), {sec:.2f} s/step'}, sec
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', 0))
+    if rank != 0:
+        return
+    cb, sec = cpu_reference_leg(args.model, args.steps, args.warmup, batch=2, hw=args.size)
+    arch, base, _, _ = MODELS[args.model]
+    line = {'impl': 'reference', 'metric': 'train_imgs_per_sec', 'value': cb['value'], 'unit': 'img/s', 'n_gpus': args.gpus,
+            'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': sec * 1e3, 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': {'workload': f'{args.model} training step {args.size}x{args.size}, CPU host cores, bounded sample: batch 2 per step',
+                       'timing': 'host wall clock'},
+            'cpu_baseline': cb, 'e2e': {'value': cb['value'], 'unit': 'img/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+            'gpu_launches': 0}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--model', default='ducknet17', choices=sorted(MODELS))
+    ap.add_argument('--batch', type=int, default=16, help='images per GPU')
+    ap.add_argument('--size', type=int, default=352)
+    ap.add_argument('--dtype', default='bf16', choices=['bf16', 'fp32'])
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--profile-steps', type=int, default=2)
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == 'b200' else args.warmup
+    if args.impl == 'reference':
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    import medical_segmentation_pytorch_b200 as msx
+    from medical_segmentation_pytorch_b200 import _lib
+    from medical_segmentation_pytorch_b200.flat import FlatBuffers, FlatParams
+    from medical_segmentation_pytorch_b200.synth import synth_batch
+
+    rank, world = int(os.environ.get('RANK', 0)), int(os.environ.get('WORLD_SIZE', 1))
+    local = int(os.environ.get('LOCAL_RANK', 0))
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    arch, base, gflop_img, gb_img = MODELS[args.model]
+    B, S = args.batch, args.size
+    bf16 = args.dtype == 'bf16'
+
+    class Cfg:
+        num_class, ignore_index, class_weights, loss_type, reduction = 2, 255, None, 'ce', 'mean'
+
+    torch.manual_seed(1)                                           # configs/base_config.py:75 random_seed = 1
+    model = (msx.DuckNet if arch == 'ducknet' else msx.UNet)(num_class=2, n_channel=3, base_channel=base).to(dev)
+    model.train()
+    FlatParams(model)
+    FlatBuffers(model)
+    net = msx.DistributedDataParallelB200(model) if world > 1 else model
+    opt = msx.FusedOptimizer(model, 'adam', lr=0.1 * 0.01 * world)  # utils/optimizer.py:15 with my_config.py:23
+    ema = msx.ModelEma(model)
+    loss_fn = msx.get_loss_fn(Cfg, dev)
+    xh, th = synth_batch(B, S, S, seed=1 + rank)
+    xh, th = xh.pin_memory(), th.pin_memory()
+    xd, td = xh.to(dev), th.to(dev)
+    it = [0]
+
+    def step(x, t):
+        opt.zero_grad()
+        with torch.autocast('cuda', dtype=torch.bfloat16, enabled=bf16):
+            loss = loss_fn(net(x), t)
+        loss.backward()
+        opt.step()
+        it[0] += 1
+        ema.update(model, it[0])
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms)
+
+    for _ in range(args.warmup):
+        loss = step(xd, td)
+    torch.cuda.synchronize()
+    assert torch.isfinite(loss).item(), 'non-finite loss in warm-up'
+
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = _lib.lib.msx_launch_count()
+    ms = timed(lambda: step(xd, td), args.steps)
+    launches = _lib.lib.msx_launch_count() - l0
+    clocks = sampler.stop() if rank == 0 else None
+
+    # end to end: pinned host buffers -> device every step, loss read back every step
+    def e2e_step():
+        x = xh.to(dev, non_blocking=True)
+        t = th.to(dev, non_blocking=True)
+        return float(step(x, t))
+    e2e_step()
+    ms_e2e = timed(e2e_step, args.steps)
+
+    # profiled pass: per-launch CUDA events on the launching stream, algorithmic bytes/flops per launch
+    prof = {}
+    if rank == 0 and args.profile_steps > 0:
+        _lib.lib.msx_profile_enable(1)
+        for _ in range(args.profile_steps):
+            step(xd, td)
+        prof = _lib.profile_collect()
+        _lib.lib.msx_profile_enable(0)
+    barrier()
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    pk = peaks()
+    imgs = B * world * args.steps
+    value = imgs / (ms / 1e3)
+    tot_ms = sum(v['ms'] for v in prof.values()) or 1.0
+    kernels = {k: {'ms_per_step': v['ms'] / args.profile_steps, 'share': v['ms'] / tot_ms, 'launches_per_step': v['launches'] // args.profile_steps,
+                   'GBps': v['bytes'] / v['ms'] / 1e6 if v['ms'] else 0.0, 'TFLOPs': v['flops'] / v['ms'] / 1e9 if v['ms'] else 0.0}
+               for k, v in sorted(prof.items(), key=lambda kv: -kv[1]['ms'])}
+    roofline = None
+    if prof:
+        top, tv = max(prof.items(), key=lambda kv: kv[1]['ms'])
+        t_tensor, t_hbm = tv['flops'] / (pk['tf'] * 1e12), tv['bytes'] / (pk['hbm_gbs'] * 1e9)
+        if t_tensor >= t_hbm:
+            ach = tv['flops'] / tv['ms'] / 1e9
+            roofline = {'kernel': top, 'bound': 'tensor', 'achieved': ach, 'peak': pk['tf'], 'unit': 'TFLOP/s', 'frac': ach / pk['tf']}
+        else:
+            ach = tv['bytes'] / tv['ms'] / 1e6
+            roofline = {'kernel': top, 'bound': 'hbm', 'achieved': ach, 'peak': pk['hbm_gbs'], 'unit': 'GB/s', 'frac': ach / pk['hbm_gbs']}
+        roofline.update({'traffic': None, 'peak_source': pk['src'] + (' (sustained bf16)' if roofline['bound'] == 'tensor' else ''),
+                         'avg_launch_us': tv['ms'] / tv['launches'] * 1e3, 'launches_per_step': tv['launches'] // args.profile_steps,
+                         'share_of_step': tv['ms'] / tot_ms,
+                         'how': f'{args.profile_steps} extra step(s) after the timed region with per-launch CUDA events (msx_profile_*)'})
+    cpu_baseline = None
+    if world == 1 and not args.no_cpu_baseline:
+        cpu_baseline, _ = cpu_reference_leg(args.model, 2, 1, batch=2, hw=S)
+    line = {
+        'metric': 'train_imgs_per_sec', 'value': value, 'unit': 'img/s', 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
+        'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
+        'dtype': 'bf16' if bf16 else 'f32', 'data': 'synthetic',
+        'config': {'workload': f'{args.model} training step (fwd+CE+bwd+Adam+EMA copy), {S}x{S}, batch {B}/GPU, num_class 2, per-GPU BN',
+                   'global_batch': B * world, 'parallelism': f'dp{world}', 'l2': 'per-step working set >> 126 MB L2 (no flush needed)',
+                   'seed': 'weights manual_seed(1); data PCG64(1+rank)'},
+        'clocks': clocks,
+        'e2e': {'value': imgs / (ms_e2e / 1e3), 'unit': 'img/s', 'h2d_bytes_per_step': xh.numel() * 4 + th.numel() * 8, 'd2h_bytes_per_step': 4},
+        'gpu_launches': int(launches),
+        'roofline': roofline,
+        'cpu_baseline': cpu_baseline,
+        'model_roofline': {'train_gflop_per_img': gflop_img, 'conv_act_gb_per_img_bf16': gb_img,
+                           'tensor_frac': value / world * gflop_img / 1e3 / pk['tf'],
+                           'hbm_frac': value / world * gb_img * (1 if bf16 else 2) / pk['hbm_gbs']},
+        'kernels': kernels,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()
