@@ -104,18 +104,29 @@ __global__ void __launch_bounds__(256) bn_stats_kernel(const T* __restrict__ x, 
     }
 }
 
-__global__ void bn_finalize_kernel(const double* __restrict__ partials, int nblk, int cp, int channels, int64_t count,
-                                   float eps, float momentum, float* __restrict__ mean, float* __restrict__ invstd,
-                                   float* running_mean, float* running_var, int64_t* nbt) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c == 0 && nbt) *nbt += 1;
-    if (c >= cp) return;
-    if (c >= channels) { mean[c] = 0.f; invstd[c] = 0.f; return; }
-    double s = 0.0, q = 0.0;
-    for (int b = 0; b < nblk; ++b) {
+// One warp per channel: lanes stride over the (<= 592) per-CTA partials, then shuffle-reduce.
+__device__ inline void reduce_partials(const double* __restrict__ partials, int nblk, int cp, int c, double& s, double& q) {
+    const int lane = threadIdx.x & 31;
+    s = 0.0; q = 0.0;
+    for (int b = lane; b < nblk; b += 32) {
         s += partials[((int64_t)b * 2 + 0) * cp + c];
         q += partials[((int64_t)b * 2 + 1) * cp + c];
     }
+    s = warp_sum(s);
+    q = warp_sum(q);
+}
+
+__global__ void bn_finalize_kernel(const double* __restrict__ partials, int nblk, int cp, int channels, int64_t count,
+                                   float eps, float momentum, float* __restrict__ mean, float* __restrict__ invstd,
+                                   float* running_mean, float* running_var, int64_t* nbt) {
+    const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (c == 0 && lane == 0 && nbt) *nbt += 1;
+    if (c >= cp) return;
+    if (c >= channels) { if (lane == 0) { mean[c] = 0.f; invstd[c] = 0.f; } return; }
+    double s, q;
+    reduce_partials(partials, nblk, cp, c, s, q);
+    if (lane != 0) return;
     const double m = s / (double)count;
     double var = q / (double)count - m * m;
     if (var < 0.0) var = 0.0;
@@ -219,14 +230,13 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const T* __restrict_
 __global__ void bn_bwd_finalize_kernel(const double* __restrict__ partials, int nblk, int cp, int channels, int64_t count,
                                        float* __restrict__ dgamma, float* __restrict__ dbeta,
                                        float* __restrict__ c1, float* __restrict__ c2) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
     if (c >= cp) return;
-    if (c >= channels) { c1[c] = 0.f; c2[c] = 0.f; return; }
-    double s = 0.0, q = 0.0;
-    for (int b = 0; b < nblk; ++b) {
-        s += partials[((int64_t)b * 2 + 0) * cp + c];
-        q += partials[((int64_t)b * 2 + 1) * cp + c];
-    }
+    if (c >= channels) { if (lane == 0) { c1[c] = 0.f; c2[c] = 0.f; } return; }
+    double s, q;
+    reduce_partials(partials, nblk, cp, c, s, q);
+    if (lane != 0) return;
     if (dbeta) dbeta[c] = (float)s;
     if (dgamma) dgamma[c] = (float)q;
     c1[c] = (float)(s / (double)count);
@@ -449,11 +459,11 @@ __global__ void nhwc_to_nchw_kernel(const T* __restrict__ src, int ld, int C, in
 
 // per-channel plain sum -> float (ConvTranspose bias gradient)
 __global__ void channel_sum_finalize_kernel(const double* __restrict__ partials, int nblk, int cp, int channels, float* out) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (c >= channels) return;
-    double s = 0.0;
-    for (int b = 0; b < nblk; ++b) s += partials[((int64_t)b * 2 + 0) * cp + c];
-    out[c] = (float)s;
+    double s, q;
+    reduce_partials(partials, nblk, cp, c, s, q);
+    if ((threadIdx.x & 31) == 0) out[c] = (float)s;
 }
 
 inline int check_ld(int ld, int channels, const char* what) {
@@ -487,7 +497,7 @@ int bn_finalize_launch(const double* partials, int nblk, int channels, int64_t c
                        float* mean, float* invstd, float* running_mean, float* running_var, int64_t* nbt,
                        cudaStream_t st) {
     const int cp = round_up(channels, 8);
-    { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_finalize_kernel<<<(cp + 127) / 128, 128, 0, st>>>(partials, nblk, cp, channels, count, eps, momentum, mean, invstd,
+    { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_finalize_kernel<<<(cp * 32 + 127) / 128, 128, 0, st>>>(partials, nblk, cp, channels, count, eps, momentum, mean, invstd,
                                                          running_mean, running_var, nbt); }
     MSX_LAUNCH_CHECK();
     return MSX_OK;
@@ -531,7 +541,7 @@ int bn_bwd_launch(int dtype, const void* x, int ldx, const void* dz, int lddz, i
         const int g = reduce_grid(pixels, c.lanes);
         { ProfScope ps__(K_BN_BWD_REDUCE, st, 2.0 * (double)pixels * channels * (double)sizeof(T), 0); bn_bwd_reduce_kernel<T><<<dim3(g, c.nchunk), 256, 0, st>>>(static_cast<const T*>(x), ldx, static_cast<const T*>(dz), lddz,
                                                                  pixels, c.cp, c.vch, channels, mean, invstd, gamma, beta, relu, partials); }
-        { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_bwd_finalize_kernel<<<(cp + 127) / 128, 128, 0, st>>>(partials, g, cp, channels, pixels, dgamma, dbeta, c1, c2); }
+        { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_bwd_finalize_kernel<<<(cp * 32 + 127) / 128, 128, 0, st>>>(partials, g, cp, channels, pixels, dgamma, dbeta, c1, c2); }
         { ProfScope ps__(K_BN_BWD_APPLY, st, 3.0 * (double)pixels * channels * (double)sizeof(T), 0); bn_bwd_apply_kernel<T><<<dim3(stream_grid(pixels, c.lanes), c.nchunk), 256, 0, st>>>(
             static_cast<const T*>(x), ldx, static_cast<const T*>(dz), lddz, static_cast<T*>(dx), lddx, pixels, c.cp, c.vch, channels,
             mean, invstd, gamma, beta, c1, c2, relu); }
@@ -545,7 +555,7 @@ int channel_sum_launch(int dtype, const void* x, int ld, int64_t pixels, int cha
     if (ws_bytes < bn_partials_bytes(channels)) return set_error(MSX_ERR_WORKSPACE, "channel_sum: workspace too small");
     int nblk = 0;
     MSX_TRY(bn_stats_launch(dtype, x, ld, pixels, channels, static_cast<double*>(ws), &nblk, st));
-    { ProfScope ps__(K_MISC, st, 0, 0); channel_sum_finalize_kernel<<<(channels + 127) / 128, 128, 0, st>>>(static_cast<double*>(ws), nblk, round_up(channels, 8), channels, out); }
+    { ProfScope ps__(K_MISC, st, 0, 0); channel_sum_finalize_kernel<<<(channels * 32 + 127) / 128, 128, 0, st>>>(static_cast<double*>(ws), nblk, round_up(channels, 8), channels, out); }
     MSX_LAUNCH_CHECK();
     return MSX_OK;
 }

@@ -99,6 +99,17 @@ def model_case(ref_cls, name, base, n, hw, seed, loss_mod, out):
         model.eval()
         with torch.no_grad():
             res[f'eval_logits_{tag}'] = model(x).numpy()
+    # the reference's AMP switch (core/seg_trainer.py:61) with dtype=bfloat16 on CPU: the bf16 noise floor
+    torch.manual_seed(0)
+    model = ref_cls(num_class=2, n_channel=3, base_channel=base)
+    model.load_state_dict(sd)
+    model.train()
+    loss_fn = loss_mod.get_loss_fn(cfg, torch.device('cpu'))
+    with torch.autocast('cpu', dtype=torch.bfloat16):
+        lg = model(torch.from_numpy(img))
+        ls = loss_fn(lg, torch.from_numpy(mask))
+    res['logits_bf16'] = lg.detach().float().numpy()
+    res['loss_bf16'] = ls.detach().float().numpy()
     res['param_names'] = np.asarray([k for k, _ in model.named_parameters()])
     np.savez_compressed(out, **res)
     print('wrote', out, {k: getattr(v, 'shape', None) for k, v in res.items() if k.startswith('logits')})

@@ -54,7 +54,7 @@ def test_conv2d_fwd_bwd(case, dtype):
     a = to_act(x, dtype, requires_grad=True)
     wp = torch.nn.Parameter(w.to(DEV))
     y = ops.Conv2dFn.apply(a.t, wp, g)
-    assert y.shape[3] == ops.rup(cout) and float(y[..., cout:].abs().sum()) == 0.0     # padded channels stay zero
+    assert y.shape[3] == ops.rup(cout) and float(y.detach()[..., cout:].abs().sum()) == 0.0     # padded channels stay zero
     y.backward(to_act(dy, dtype).t)
     tol = 1e-5 if dtype == torch.float32 else 2e-2
     assert rel(from_act(y, cout), yref) < tol
@@ -93,7 +93,8 @@ def test_conv_transpose_bn_relu(dtype):
     assert rel(m.up_conv[1].weight.grad, ref[1].weight.grad) < tol * 5
     assert rel(m.up_conv[1].bias.grad, ref[1].bias.grad) < tol * 5
     # conv bias gradient is analytically zero when BN follows
-    assert float(m.up_conv[0].bias.grad.abs().max()) < 1e-3 * float(m.up_conv[1].bias.grad.abs().max() + 1e-6) + 1e-4
+    zero_tol = 1e-5 if dtype == torch.float32 else 1e-2        # bf16: dy is rounded before it is summed
+    assert float(m.up_conv[0].bias.grad.abs().max()) < zero_tol * float(m.up_conv[1].bias.grad.abs().max()) + 1e-5
     if dtype == torch.float32:
         assert rel(m.up_conv[1].running_mean, ref[1].running_mean) < 1e-5
         assert rel(m.up_conv[1].running_var, ref[1].running_var) < 1e-5

@@ -3,8 +3,10 @@
 
 Protocol: an error of the new path against fp64 truth must not exceed
 max(3 x the reference-fp32 error against the same truth, floor).  Loss within 1e-4 relative
-(north_star fp32 tolerance).  bf16 (autocast) tolerance, stated: loss within 5e-2 relative, logits
-rel-L2 < 0.35 on these random-init nets (the reference's own CPU bf16 autocast shows 0.14 on UNet-32)."""
+(north_star fp32 tolerance).  bf16 (autocast) tolerance, stated: loss within 5e-2 relative; logits
+rel-L2 against fp64 truth at most 1.5 x what the reference itself shows under
+torch.autocast(dtype=bfloat16) on the same inputs (golden 'logits_bf16'; 0.06 on the UNet case, 0.77 on
+the tiny DuckNet whose 2x2-pixel BatchNorms are ill-conditioned in any precision)."""
 import os
 
 import numpy as np
@@ -87,8 +89,9 @@ def test_model_bf16_autocast(golden_dir, name, fname):
     loss.backward()
     assert logits.dtype == torch.float32
     e = rel(logits, g['logits_f64'])
-    print(f'{name} bf16: logits rel-L2 {e:.3e}, loss {float(loss):.5f} vs {float(g["loss_f64"]):.5f}')
-    assert e < 0.35
+    e_ref = rel(g['logits_bf16'], g['logits_f64'])           # the reference itself under bf16 autocast (CPU)
+    print(f'{name} bf16: logits rel-L2 {e:.3e} (reference bf16 autocast {e_ref:.3e}), loss {float(loss):.5f} vs {float(g["loss_f64"]):.5f}')
+    assert e <= max(1.5 * e_ref, 0.05)
     assert abs(float(loss) - float(g['loss_f64'])) <= 5e-2 * abs(float(g['loss_f64']))
     assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in model.parameters())
 
