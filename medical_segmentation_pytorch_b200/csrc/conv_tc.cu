@@ -1,8 +1,367 @@
-// tcgen05 / TMEM / TMA implicit-GEMM convolution engine (bf16).  Placeholder until the kernel lands.
+// tcgen05 / TMEM / TMA implicit-GEMM convolution engine for sm_100a (bf16 in, fp32 accumulate).
+//
+// One kernel serves every stride-1 "gather" pass of the reference's convolutions (Conv2d fprop and
+// dgrad for 3x3 d1/d2/d3, 1x1, 1x7, 7x1):   dst[p][n] = sum_{tap,k} src[p + off(tap)][k] * Wp[tap][n][k]
+//
+//   GEMM view     M = 128 output pixels (a th x tw patch of one image), N = BN <= 256 output channels,
+//                 K = taps x channels, walked tap by tap in chunks of 64 (or 32) channels.
+//   A operand     NHWC activations through a 4-D TMA tensor map {C, W, H, N}; the box {chunk, tw, th, 1}
+//                 at (k0, x0 + dx(tap), y0 + dy(tap), img) lands in shared memory as 128 pixel rows of
+//                 128 B (64 B) with the 128B (64B) swizzle = the canonical K-major UMMA layout.  Image
+//                 borders (zero padding), ragged tiles and the channel tail are all TMA out-of-bounds
+//                 zero fill: no im2col buffer, no predication.
+//   B operand     packed weights [tap][Np][Kp] through a 3-D tensor map, box {chunk, BN, 1}.
+//   D accumulator TMEM, 128 lanes x BN fp32 columns, double buffered (2 x BN <= 512 columns) so the
+//                 epilogue of tile i overlaps the MMAs of tile i+1.
+//   Warp roles    warp 0: TMA producer (one lane) - warp 1: TMEM alloc + tcgen05.mma issue (one lane) -
+//                 warps 2..5: epilogue (tcgen05.ld -> +bias -> bf16 -> 16 B global stores).
+//   Pipelines     smem ring of S stages (full/empty mbarriers, tcgen05.commit frees a stage);
+//                 TMEM ring of 2 accumulators (tmem_full / tmem_empty mbarriers).
+//   Scheduling    persistent: grid = min(#tiles, 148), static round-robin over (pixel tile, n tile).
+#include <cuda.h>
+
 #include "common.cuh"
+
 namespace msx {
-bool conv_tc_supported(const msx_conv_desc*, bool) { return false; }
-int conv_gather_tc(const msx_conv_desc*, bool, const void*, const void*, const float*, void*, cudaStream_t) {
-    return set_error(MSX_ERR_UNSUPPORTED, "tcgen05 conv engine not built");
+
+namespace {
+
+constexpr int kThreads = 192;
+constexpr int kMaxStages = 8;
+constexpr uint32_t kSmemBudget = 200 * 1024;
+
+struct TcParams {
+    int N, H, W;          // destination == source spatial size (stride 1)
+    int tw, th, tiles_x, tiles_y;
+    int n_tiles, BN;      // tiling of the output-channel axis
+    int kh, kw, mul_t, off_h, off_w;
+    int kchunks, chunk;   // K chunks per tap, channels per chunk (64 or 32)
+    int Kp;               // padded reduction channels (multiple of 8)
+    int Nc, ncp, ldd;     // output channels, round_up(Nc, 8), destination pixel stride
+    int stages;
+    uint32_t a_bytes, b_bytes, a_stage, b_stage;   // TMA box bytes and smem stage pitch
+    int tmem_cols;
+    int64_t total_tiles;
+};
+
+// ---- PTX wrappers -----------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
 }
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n" : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+// Bounded spin: a protocol bug traps (reported as a CUDA error) instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t spins = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        if (++spins > 50000000u) __trap();
+    }
+}
+__device__ __forceinline__ void tma_load_4d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+                 ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// K-major operand descriptor for a tile of rows x (64|32) bf16, rows `row_bytes` apart, 8-row swizzle
+// atoms packed densely (SBO = 8 * row_bytes).  cute::UMMA::SmemDescriptor bit layout.
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t row_bytes) {
+    const uint64_t layout = row_bytes == 128 ? 2ull : 4ull;       // SWIZZLE_128B : SWIZZLE_64B
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)((8 * row_bytes) >> 4) << 32) | (1ull << 46) | (layout << 61);
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               bf16* __restrict__ dst, const float* __restrict__ bias, const TcParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;             // swizzle atoms need 1024 B alignment
+    const uint32_t sA = base, sB = base + p.stages * p.a_stage;
+    const uint32_t bars = sB + p.stages * p.b_stage;                         // 8 B each
+    const uint32_t bar_full = bars, bar_empty = bars + 8 * kMaxStages;
+    const uint32_t bar_tfull = bars + 16 * kMaxStages, bar_tempty = bar_tfull + 16;
+    const uint32_t tmem_slot = bar_tempty + 16;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < p.stages; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(bar_tfull + 8 * a, 1); mbar_init(bar_tempty + 8 * a, 4); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"((uint32_t)p.tmem_cols));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+    const int taps = p.kh * p.kw;
+    const int64_t tiles_per_img = (int64_t)p.tiles_x * p.tiles_y;
+    const int64_t m_tiles = tiles_per_img * p.N;
+
+    if (warp == 0) {
+        // ================= TMA producer =================
+        if (lane == 0) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int64_t t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
+                const int nt = (int)(t / m_tiles);
+                const int64_t mt = t % m_tiles;
+                const int img = (int)(mt / tiles_per_img);
+                const int rem = (int)(mt % tiles_per_img);
+                const int y0 = (rem / p.tiles_x) * p.th, x0 = (rem % p.tiles_x) * p.tw;
+                for (int tap = 0; tap < taps; ++tap) {
+                    const int r = tap / p.kw, s = tap % p.kw;
+                    const int sy = y0 + r * p.mul_t + p.off_h, sx = x0 + s * p.mul_t + p.off_w;
+                    for (int kc = 0; kc < p.kchunks; ++kc) {
+                        mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+                        mbar_expect_tx(bar_full + 8 * stage, p.a_bytes + p.b_bytes);
+                        tma_load_4d(sA + stage * p.a_stage, &tmA, bar_full + 8 * stage, kc * p.chunk, sx, sy, img);
+                        tma_load_3d(sB + stage * p.b_stage, &tmB, bar_full + 8 * stage, kc * p.chunk, nt * p.BN, tap);
+                        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================= MMA issuer =================
+        if (lane == 0) {
+            // cute::UMMA::InstrDescriptor: c=F32 (bit 4), a=b=BF16 (bits 7, 10), K-major A and B, N>>3 @17, M>>4 @24
+            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((128u >> 4) << 24);
+            const uint32_t row_bytes = p.chunk * 2;
+            int stage = 0;
+            uint32_t phase = 0;
+            int it = 0;
+            for (int64_t t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
+                const int as = it & 1;
+                mbar_wait(bar_tempty + 8 * as, ((it >> 1) & 1) ^ 1);         // epilogue has drained this accumulator
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + as * p.BN;
+                uint32_t acc = 0;
+                for (int tap = 0; tap < taps; ++tap) {
+                    for (int kc = 0; kc < p.kchunks; ++kc) {
+                        mbar_wait(bar_full + 8 * stage, phase);              // TMA bytes have landed
+                        tc_fence_after();
+                        const int kleft = p.Kp - kc * p.chunk;
+                        const int ksteps = kleft >= p.chunk ? p.chunk / 16 : (kleft + 15) / 16;
+                        const uint64_t da = umma_desc(sA + stage * p.a_stage, row_bytes);
+                        const uint64_t db = umma_desc(sB + stage * p.b_stage, row_bytes);
+                        for (int k = 0; k < ksteps; ++k) {
+                            umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, acc);   // +32 B per K=16 step
+                            acc = 1;
+                        }
+                        umma_commit(bar_empty + 8 * stage);                  // frees the smem stage when the MMAs retire
+                        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                    }
+                }
+                umma_commit(bar_tfull + 8 * as);                             // accumulator complete -> epilogue
+            }
+        }
+    } else {
+        // ================= epilogue (warps 2..5) =================
+        const int quad = warp & 3;                                           // TMEM lane quadrant this warp may read
+        const int m = quad * 32 + lane;
+        const int dy = m / p.tw, dx = m % p.tw;
+        int it = 0;
+        for (int64_t t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
+            const int as = it & 1;
+            const int nt = (int)(t / m_tiles);
+            const int64_t mt = t % m_tiles;
+            const int img = (int)(mt / tiles_per_img);
+            const int rem = (int)(mt % tiles_per_img);
+            const int y = (rem / p.tiles_x) * p.th + dy, x = (rem % p.tiles_x) * p.tw + dx;
+            const bool valid = dy < p.th && y < p.H && x < p.W;
+            const int n0 = nt * p.BN;
+            const int ncols = min(p.BN, p.ncp - n0);                         // multiple of 8
+            bf16* out = dst + ((int64_t)(img * p.H + y) * p.W + x) * p.ldd + n0;
+            mbar_wait(bar_tfull + 8 * as, (it >> 1) & 1);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + as * p.BN;
+            for (int c0 = 0; c0 < ncols; c0 += 16) {
+                uint32_t v[16];
+                tmem_ld16(taddr + c0, v);
+                tmem_ld_wait();
+                if (valid) {
+                    uint32_t w[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        float a = __uint_as_float(v[2 * j]), b = __uint_as_float(v[2 * j + 1]);
+                        if (bias) {
+                            const int c = n0 + c0 + 2 * j;
+                            a += c < p.Nc ? bias[c] : 0.f;
+                            b += c + 1 < p.Nc ? bias[c + 1] : 0.f;
+                        }
+                        __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+                        w[j] = *reinterpret_cast<uint32_t*>(&h);
+                    }
+                    *reinterpret_cast<uint4*>(out + c0) = make_uint4(w[0], w[1], w[2], w[3]);
+                    if (c0 + 8 < ncols) *reinterpret_cast<uint4*>(out + c0 + 8) = make_uint4(w[4], w[5], w[6], w[7]);
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)p.tmem_cols));
+    }
+}
+
+// ---- host side ----------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = []() -> EncodeTiledFn {
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            return nullptr;
+        return reinterpret_cast<EncodeTiledFn>(f);
+    }();
+    return fn;
+}
+
+int make_map(CUtensorMap* m, int rank, const void* ptr, const cuuint64_t* dims, const cuuint64_t* strides_bytes,
+             const cuuint32_t* box, CUtensorMapSwizzle sw) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) return set_error(MSX_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
+    cuuint32_t es[5] = {1, 1, 1, 1, 1};
+    CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(ptr), dims, strides_bytes, box, es,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return set_error(MSX_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    return MSX_OK;
+}
+
+void pick_tile(int H, int W, int& tw, int& th) {
+    double best = -1;
+    tw = 1; th = 1;
+    for (int w = 1; w <= (W < 128 ? W : 128); ++w) {
+        int h = 128 / w;
+        if (h > H) h = H;
+        if (h < 1) continue;
+        const double tiles = (double)((W + w - 1) / w) * ((H + h - 1) / h);
+        const double eff = (double)W * H / (tiles * 128.0);
+        if (eff > best + 1e-9 || (eff > best - 1e-9 && w > tw)) { best = eff; tw = w; th = h; }
+    }
+}
+
+}  // namespace
+
+bool conv_tc_supported(const msx_conv_desc* d, bool fwd_pass) {
+    (void)fwd_pass;
+    if (d->dtype != MSX_BF16 || d->transposed || d->stride != 1) return false;
+    if (d->oh != d->h || d->ow != d->w) return false;          // 'same' geometry (all stride-1 convs of the reference)
+    return encode_fn() != nullptr;
+}
+
+int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
+                   void* dst, cudaStream_t st) {
+    TcParams p;
+    const int K = fwd_pass ? d->cin : d->cout, Nc = fwd_pass ? d->cout : d->cin;
+    const int lds = fwd_pass ? d->ldx : d->ldy;
+    p.N = d->n; p.H = d->h; p.W = d->w;
+    p.kh = d->kh; p.kw = d->kw;
+    if (fwd_pass) { p.mul_t = d->dil; p.off_h = -d->pad_h; p.off_w = -d->pad_w; }
+    else          { p.mul_t = -d->dil; p.off_h = d->pad_h; p.off_w = d->pad_w; }
+    p.Kp = round_up(K, 8);
+    p.Nc = Nc; p.ncp = round_up(Nc, 8); p.ldd = fwd_pass ? d->ldy : d->ldx;
+    const int Np = round_up(Nc, 16);
+    p.n_tiles = (Np + 255) / 256;
+    p.BN = round_up((Np + p.n_tiles - 1) / p.n_tiles, 16);
+    p.chunk = p.Kp <= 32 ? 32 : 64;
+    p.kchunks = (p.Kp + p.chunk - 1) / p.chunk;
+    pick_tile(p.H, p.W, p.tw, p.th);
+    p.tiles_x = (p.W + p.tw - 1) / p.tw;
+    p.tiles_y = (p.H + p.th - 1) / p.th;
+    p.total_tiles = (int64_t)p.tiles_x * p.tiles_y * p.N * p.n_tiles;
+    const uint32_t row_bytes = p.chunk * 2;
+    p.a_bytes = (uint32_t)p.tw * p.th * row_bytes;
+    p.b_bytes = (uint32_t)p.BN * row_bytes;
+    p.a_stage = 128 * row_bytes;                                 // full 128-row operand tile
+    p.b_stage = (p.b_bytes + 1023u) & ~1023u;
+    int stages = (int)(kSmemBudget / (p.a_stage + p.b_stage));
+    p.stages = stages > kMaxStages ? kMaxStages : (stages < 2 ? 2 : stages);
+    int cols = 32;
+    while (cols < 2 * p.BN) cols <<= 1;
+    p.tmem_cols = cols;
+    const size_t smem = 1024 + (size_t)p.stages * (p.a_stage + p.b_stage) + 16 * kMaxStages + 64;
+
+    const CUtensorMapSwizzle sw = p.chunk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+    CUtensorMap tmA, tmB;
+    {
+        cuuint64_t dims[4] = {(cuuint64_t)p.Kp, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.N};
+        cuuint64_t strides[3] = {(cuuint64_t)lds * 2, (cuuint64_t)lds * 2 * p.W, (cuuint64_t)lds * 2 * p.W * p.H};
+        cuuint32_t box[4] = {(cuuint32_t)p.chunk, (cuuint32_t)p.tw, (cuuint32_t)p.th, 1};
+        MSX_TRY(make_map(&tmA, 4, src, dims, strides, box, sw));
+    }
+    {
+        cuuint64_t dims[3] = {(cuuint64_t)p.Kp, (cuuint64_t)Np, (cuuint64_t)(p.kh * p.kw)};
+        cuuint64_t strides[2] = {(cuuint64_t)p.Kp * 2, (cuuint64_t)p.Kp * 2 * Np};
+        cuuint32_t box[3] = {(cuuint32_t)p.chunk, (cuuint32_t)p.BN, 1};
+        MSX_TRY(make_map(&tmB, 3, packed, dims, strides, box, sw));
+    }
+    static bool attr_set = false;
+    if (!attr_set) {
+        MSX_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr_set = true;
+    }
+    const int grid = (int)(p.total_tiles < kNumSMs ? p.total_tiles : kNumSMs);
+    const double M = (double)p.N * p.H * p.W;
+    {
+        ProfScope ps__(K_CONV_TC, st, M * (K + Nc) * 2.0, 2.0 * M * Nc * K * p.kh * p.kw);
+        conv_tc_kernel<<<grid, kThreads, smem, st>>>(tmA, tmB, static_cast<bf16*>(dst), bias, p);
+    }
+    MSX_LAUNCH_CHECK();
+    note_conv_engine(MSX_ENGINE_TCGEN05);
+    return MSX_OK;
+}
+
 }  // namespace msx

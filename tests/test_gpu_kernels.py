@@ -62,6 +62,51 @@ def test_conv2d_fwd_bwd(case, dtype):
     assert rel(wp.grad, wd.grad) < tol
 
 
+TC_CASES = [
+    # cin, cout, kh, kw, dil, H, W, n     (stride 1: the tcgen05 engine's domain, 97.7 % of DUCKNet MACs)
+    (17, 17, 3, 3, 1, 32, 48, 2),       # Kp=24 -> 64 B swizzle rows, BN=32
+    (3, 17, 3, 3, 1, 32, 32, 2),        # stem: Kp=8
+    (34, 34, 3, 3, 2, 24, 24, 2),       # Kp=40 -> one 64-channel chunk, 3 k-steps
+    (68, 68, 3, 3, 3, 16, 16, 2),       # two chunks (64 + 8)
+    (136, 136, 3, 3, 1, 44, 44, 1),     # 11x11-friendly tiling
+    (272, 136, 3, 3, 1, 22, 22, 2),
+    (544, 272, 3, 3, 1, 11, 11, 2),     # BN=256+..: two n tiles, 121-row tiles
+    (272, 544, 1, 1, 1, 11, 11, 3),     # 1x1, three n tiles
+    (17, 17, 1, 7, 1, 20, 40, 2),
+    (34, 34, 7, 1, 1, 40, 20, 2),
+    (32, 32, 3, 3, 1, 64, 64, 1),
+    (64, 32, 3, 3, 1, 40, 40, 2),       # UNet-style, 40x40 (ragged tiles)
+    (128, 256, 3, 3, 1, 20, 20, 2),
+]
+
+
+@pytest.mark.parametrize('case', TC_CASES)
+def test_conv_tcgen05_fwd_dgrad(case):
+    """tcgen05/TMEM/TMA implicit GEMM (engine forced) vs float64 conv on bf16-rounded operands."""
+    ops = _ops()
+    from medical_segmentation_pytorch_b200 import _lib
+    cin, cout, kh, kw, dil, H, W, n = case
+    torch.manual_seed(sum(case))
+    x = torch.randn(n, cin, H, W).bfloat16().float()
+    w = (torch.randn(cout, cin, kh, kw) / (cin * kh * kw) ** 0.5).bfloat16().float()
+    pad = ((kh - 1) // 2 * dil, (kw - 1) // 2 * dil)
+    xd, wd = x.double().requires_grad_(True), w.double().requires_grad_(True)
+    yref = F.conv2d(xd, wd, None, 1, pad, dil)
+    dy = torch.randn(yref.shape).bfloat16().float()
+    yref.backward(dy.double())
+    g = ops.ConvGeom(cin, cout, kh, kw, 1, dil, pad[0], pad[1], engine=2)
+    a = to_act(x, torch.bfloat16, requires_grad=True)
+    wp = torch.nn.Parameter(w.to(DEV))
+    y = ops.Conv2dFn.apply(a.t, wp, g)
+    assert _lib.lib.msx_last_conv_engine() == 2
+    assert float(y.detach()[..., cout:].float().abs().sum()) == 0.0
+    y.backward(to_act(dy, torch.bfloat16).t)
+    torch.cuda.synchronize()
+    e_y, e_dx, e_dw = rel(from_act(y, cout), yref), rel(from_act(a.t.grad, cin), xd.grad), rel(wp.grad, wd.grad)
+    print(f'tc {case}: y {e_y:.2e} dx {e_dx:.2e} dw {e_dw:.2e}')
+    assert e_y < 6e-3 and e_dx < 6e-3 and e_dw < 6e-3          # output rounding to bf16: ~2^-9 per element
+
+
 @pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
 def test_conv_transpose_bn_relu(dtype):
     """DeConvBNAct: ConvTranspose2d(3, s2, p1, op1, bias) -> BN(train) -> ReLU, forward and all gradients."""
