@@ -16,6 +16,18 @@ bool conv_tc_supported(const msx_conv_desc* d, bool fwd_pass);
 int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
                    void* dst, cudaStream_t st);
 
+size_t conv_wgrad_tc_ws_bytes(const msx_conv_desc* d);
+int conv_wgrad_tc(const msx_conv_desc* d, const void* x, const void* dy, float* dw, void* ws, size_t ws_bytes, cudaStream_t st);
+
+static bool want_tc(const msx_conv_desc* d) {
+    return d->engine == MSX_ENGINE_TCGEN05 || (d->engine == MSX_ENGINE_AUTO && d->dtype == MSX_BF16);
+}
+
+static int conv_wgrad(const msx_conv_desc* d, const void* x, const void* dy, float* dw, void* ws, size_t ws_bytes, cudaStream_t st) {
+    if (want_tc(d) && conv_tc_supported(d, true)) return conv_wgrad_tc(d, x, dy, dw, ws, ws_bytes, st);
+    return conv_wgrad_simt(d, x, dy, dw, ws, ws_bytes, st);
+}
+
 static int conv_gather(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
                        void* dst, cudaStream_t st) {
     const bool want_tc = d->engine == MSX_ENGINE_TCGEN05 || (d->engine == MSX_ENGINE_AUTO && d->dtype == MSX_BF16);
@@ -26,7 +38,11 @@ static int conv_gather(const msx_conv_desc* d, bool fwd_pass, const void* src, c
 }
 
 static size_t ws_conv_bytes(const msx_conv_desc* d) {
-    const size_t a = conv_wgrad_ws_bytes(d);
+    size_t a = conv_wgrad_ws_bytes(d);
+    if (d->dtype == MSX_BF16 && conv_tc_supported(d, true)) {
+        const size_t t = conv_wgrad_tc_ws_bytes(d);
+        if (t > a) a = t;
+    }
     const int cmax = d->cin > d->cout ? d->cin : d->cout;
     const size_t b = bn_partials_bytes(cmax);
     return (a > b ? a : b) + 256;
@@ -68,7 +84,7 @@ int msx_conv2d_bwd(const msx_conv_desc* d, const void* x, const float* w_master,
         MSX_TRY(conv_pack_launch(d, MSX_PACK_DGRAD, w_master, w_packed, st));
         MSX_TRY(conv_gather(d, false, dy, w_packed, nullptr, dx, st));
     }
-    if (dw) MSX_TRY(conv_wgrad_simt(d, x, dy, dw, ws, ws_bytes, st));
+    if (dw) MSX_TRY(conv_wgrad(d, x, dy, dw, ws, ws_bytes, st));
     if (dbias)
         MSX_TRY(channel_sum_launch(d->dtype, dy, d->ldy, (int64_t)d->n * d->oh * d->ow, d->cout, dbias, ws, ws_bytes, st));
     return MSX_OK;
@@ -114,7 +130,7 @@ int msx_conv_bn_act_bwd(const msx_conv_desc* d, const void* x, const float* w_ma
         MSX_TRY(conv_pack_launch(d, MSX_PACK_DGRAD, w_master, w_packed, st));
         MSX_TRY(conv_gather(d, false, dy_scratch, w_packed, nullptr, dx, st));
     }
-    if (dw) MSX_TRY(conv_wgrad_simt(d, x, dy_scratch, dw, ws, ws_bytes, st));
+    if (dw) MSX_TRY(conv_wgrad(d, x, dy_scratch, dw, ws, ws_bytes, st));
     if (dbias) MSX_TRY(channel_sum_launch(d->dtype, dy_scratch, d->ldy, pixels, d->cout, dbias, ws, ws_bytes, st));
     return MSX_OK;
 }

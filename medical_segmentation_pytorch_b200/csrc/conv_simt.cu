@@ -377,4 +377,15 @@ int conv_wgrad_simt(const msx_conv_desc* d, const void* x, const void* dy, float
     return MSX_OK;
 }
 
+int wgrad_reduce_launch(const float* partial, int splits, int taps, int A, int B, int Apad, int Bpad, float* dw, cudaStream_t st) {
+    const int64_t total = (int64_t)A * B * taps;
+    const int rg = (int)((total + 255) / 256 < 2048 ? (total + 255) / 256 : 2048);
+    {
+        ProfScope ps__(K_WGRAD_REDUCE, st, (double)total * 4 * (splits + 1), 0);
+        wgrad_reduce_kernel<<<rg, 256, 0, st>>>(partial, splits, taps, A, B, Apad, Bpad, dw);
+    }
+    MSX_LAUNCH_CHECK();
+    return MSX_OK;
+}
+
 }  // namespace msx

@@ -293,6 +293,209 @@ void pick_tile(int H, int W, int& tw, int& th) {
     }
 }
 
+
+// =================================================================================================
+// Weight gradient on tcgen05:  dW[a][b][tap] = sum_p small[p][a] * big[p + off(tap)][b]
+//   (Conv2d stride 1: small = dy (a = cout), big = x (b = cin)).
+// GEMM view: M = 128 a-channels, N = TN <= 256 b-channels, K = pixels.  Both operands are the NHWC
+// tiles themselves ([128 pixel rows][64|32 channels], TMA + swizzle) used as MN-MAJOR UMMA operands:
+// channels run along the 128 B (64 B) row, pixels along K, so no transpose is ever materialised.
+// The box of a tile is always a full 128-pixel rectangle (tw*th == 128); whatever hangs over the image
+// is TMA zero fill, so out-of-image pixels add exactly 0 to the sums.
+// A CTA owns one (a tile, b tile, tap group, pixel split): it keeps tg taps x TN fp32 columns in TMEM
+// (<= 512), streams its pixel tiles through two smem rings (A: dy tile, reused by all taps of the
+// group; B: one shifted x tile per tap) and finally dumps TMEM to the split-K workspace that
+// wgrad_reduce_kernel folds into the reference OIHW layout.
+struct WgParams {
+    int N, H, W, tw, th, tiles_x, tiles_y;
+    int kh, kw, dil, pad_h, pad_w;
+    int a_tiles, b_tiles, TN, tg, tap_groups, splits;
+    int chunkA, chunkB, groupsB;      // channels per MN group, groups per B tile
+    int Ap, Bp;                       // round_up(A, 8), round_up(B, 8): tensor-map channel extents
+    int Apad, Bpad;                   // workspace leading dims (a_tiles*128, b_tiles*TN)
+    int stagesB, tmem_cols;
+    uint32_t a_stage, b_stage;
+    int64_t pix_tiles;
+};
+
+// MN-major operand descriptor: MN groups `lbo` bytes apart, 8-row (K) groups 8*row_bytes apart.
+__device__ __forceinline__ uint64_t umma_desc_mn(uint32_t saddr, uint32_t row_bytes, uint32_t lbo) {
+    const uint64_t layout = row_bytes == 128 ? 2ull : 4ull;
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)((lbo >> 4) & 0x3FFFu) << 16) |
+           ((uint64_t)((8 * row_bytes) >> 4) << 32) | (1ull << 46) | (layout << 61);
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CUtensorMap tmG,
+                float* __restrict__ partial, const WgParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    constexpr int SA = 2;
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t sA = base, sB = base + SA * p.a_stage;
+    const uint32_t bars = sB + p.stagesB * p.b_stage;
+    const uint32_t barA_full = bars, barA_empty = bars + 16, barB_full = bars + 32, barB_empty = barB_full + 8 * kMaxStages;
+    const uint32_t bar_done = barB_empty + 8 * kMaxStages, tmem_slot = bar_done + 8;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    // unit decode: blockIdx.x = ((split * tap_groups + tgi) * b_tiles + bt) * a_tiles + at
+    int u = blockIdx.x;
+    const int at = u % p.a_tiles; u /= p.a_tiles;
+    const int bt = u % p.b_tiles; u /= p.b_tiles;
+    const int tgi = u % p.tap_groups; u /= p.tap_groups;
+    const int split = u;
+    const int taps = p.kh * p.kw;
+    const int tap0 = tgi * p.tg, ntap = min(p.tg, taps - tap0);
+    const int64_t per = (p.pix_tiles + p.splits - 1) / p.splits;
+    const int64_t t_beg = (int64_t)split * per, t_end = min(t_beg + per, p.pix_tiles);
+    const int a0 = at * 128, b0 = bt * p.TN;
+    const int groupsA = min((min(p.Ap - a0, 128) + p.chunkA - 1) / p.chunkA, 128 / p.chunkA);
+    const uint32_t rbA = p.chunkA * 2, rbB = p.chunkB * 2;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < SA; ++s) { mbar_init(barA_full + 8 * s, 1); mbar_init(barA_empty + 8 * s, 1); }
+        for (int s = 0; s < p.stagesB; ++s) { mbar_init(barB_full + 8 * s, 1); mbar_init(barB_empty + 8 * s, 1); }
+        mbar_init(bar_done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"((uint32_t)p.tmem_cols));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+    const int64_t tiles_per_img = (int64_t)p.tiles_x * p.tiles_y;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int stA = 0, stB = 0;
+            uint32_t phA = 0, phB = 0;
+            for (int64_t t = t_beg; t < t_end; ++t) {
+                const int img = (int)(t / tiles_per_img), rem = (int)(t % tiles_per_img);
+                const int y0 = (rem / p.tiles_x) * p.th, x0 = (rem % p.tiles_x) * p.tw;
+                mbar_wait(barA_empty + 8 * stA, phA ^ 1);
+                mbar_expect_tx(barA_full + 8 * stA, groupsA * 128 * rbA);
+                for (int g = 0; g < groupsA; ++g)
+                    tma_load_4d(sA + stA * p.a_stage + g * 128 * rbA, &tmS, barA_full + 8 * stA, a0 + g * p.chunkA, x0, y0, img);
+                if (++stA == SA) { stA = 0; phA ^= 1; }
+                for (int k = 0; k < ntap; ++k) {
+                    const int tap = tap0 + k, r = tap / p.kw, s = tap % p.kw;
+                    mbar_wait(barB_empty + 8 * stB, phB ^ 1);
+                    mbar_expect_tx(barB_full + 8 * stB, p.groupsB * 128 * rbB);
+                    for (int g = 0; g < p.groupsB; ++g)
+                        tma_load_4d(sB + stB * p.b_stage + g * 128 * rbB, &tmG, barB_full + 8 * stB, b0 + g * p.chunkB,
+                                    x0 + s * p.dil - p.pad_w, y0 + r * p.dil - p.pad_h, img);
+                    if (++stB == p.stagesB) { stB = 0; phB ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // c=F32, a=b=BF16, A and B MN-major (bits 15, 16), N>>3 @17, M>>4 @24
+            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) |
+                                   ((uint32_t)(p.TN >> 3) << 17) | ((128u >> 4) << 24);
+            int stA = 0, stB = 0;
+            uint32_t phA = 0, phB = 0;
+            for (int64_t t = t_beg; t < t_end; ++t) {
+                mbar_wait(barA_full + 8 * stA, phA);
+                tc_fence_after();
+                const uint32_t aaddr = sA + stA * p.a_stage;
+                for (int k = 0; k < ntap; ++k) {
+                    mbar_wait(barB_full + 8 * stB, phB);
+                    tc_fence_after();
+                    const uint32_t baddr = sB + stB * p.b_stage;
+                    const uint32_t tmem_d = tmem_base + k * p.TN;
+#pragma unroll
+                    for (int kk = 0; kk < 8; ++kk) {                       // 128 pixels = 8 x K16
+                        const uint64_t da = umma_desc_mn(aaddr + kk * 16 * rbA, rbA, 128 * rbA);
+                        const uint64_t db = umma_desc_mn(baddr + kk * 16 * rbB, rbB, 128 * rbB);
+                        umma_bf16(tmem_d, da, db, idesc, (t > t_beg || kk > 0) ? 1u : 0u);
+                    }
+                    umma_commit(barB_empty + 8 * stB);
+                    if (++stB == p.stagesB) { stB = 0; phB ^= 1; }
+                }
+                umma_commit(barA_empty + 8 * stA);
+                if (++stA == SA) { stA = 0; phA ^= 1; }
+            }
+            umma_commit(bar_done);
+        }
+    } else {
+        const int quad = warp & 3, row = quad * 32 + lane;
+        if (t_end > t_beg) {
+            mbar_wait(bar_done, 0);
+            tc_fence_after();
+        }
+        for (int k = 0; k < ntap; ++k) {
+            float* out = partial + (((int64_t)split * taps + tap0 + k) * p.Apad + a0 + row) * p.Bpad + b0;
+            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + k * p.TN;
+            for (int c0 = 0; c0 < p.TN; c0 += 16) {
+                uint32_t v[16];
+                if (t_end > t_beg) { tmem_ld16(taddr + c0, v); tmem_ld_wait(); }
+                else {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j) v[j] = 0u;                 // empty split: contributes zeros
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    *reinterpret_cast<uint4*>(out + c0 + 4 * j) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)p.tmem_cols));
+    }
+}
+
+void pick_tile_pow2(int H, int W, int& tw, int& th) {
+    double best = -1;
+    tw = 16; th = 8;
+    for (int w = 128; w >= 1; w >>= 1) {
+        const int h = 128 / w;
+        const double tiles = (double)((W + w - 1) / w) * ((H + h - 1) / h);
+        const double eff = (double)W * H / (tiles * 128.0);
+        if (eff > best + 1e-9) { best = eff; tw = w; th = h; }
+    }
+}
+
+void wgrad_plan(const msx_conv_desc* d, WgParams& p) {
+    const int A = d->cout, B = d->cin;
+    p.N = d->n; p.H = d->h; p.W = d->w;
+    p.kh = d->kh; p.kw = d->kw; p.dil = d->dil; p.pad_h = d->pad_h; p.pad_w = d->pad_w;
+    pick_tile_pow2(p.H, p.W, p.tw, p.th);
+    p.tiles_x = (p.W + p.tw - 1) / p.tw;
+    p.tiles_y = (p.H + p.th - 1) / p.th;
+    p.pix_tiles = (int64_t)p.tiles_x * p.tiles_y * p.N;
+    p.Ap = round_up(A, 8); p.Bp = round_up(B, 8);
+    p.a_tiles = (p.Ap + 127) / 128;
+    const int Bn = round_up(B, 16);
+    p.b_tiles = (Bn + 255) / 256;
+    p.TN = round_up((Bn + p.b_tiles - 1) / p.b_tiles, 16);
+    p.chunkA = p.Ap <= 32 ? 32 : 64;
+    p.chunkB = p.Bp <= 32 ? 32 : 64;
+    p.groupsB = (p.TN + p.chunkB - 1) / p.chunkB;
+    const int taps = p.kh * p.kw;
+    p.tg = 512 / p.TN < taps ? 512 / p.TN : taps;
+    p.tap_groups = (taps + p.tg - 1) / p.tg;
+    int cols = 32;
+    while (cols < p.tg * p.TN) cols <<= 1;
+    p.tmem_cols = cols;
+    p.Apad = p.a_tiles * 128; p.Bpad = p.b_tiles * p.TN;
+    const int64_t units0 = (int64_t)p.a_tiles * p.b_tiles * p.tap_groups;
+    int64_t splits = (kNumSMs + units0 - 1) / units0;
+    if (splits > p.pix_tiles) splits = p.pix_tiles;
+    if (splits < 1) splits = 1;
+    p.splits = (int)splits;
+    p.a_stage = 128u * 256u;                                    // 128 channels x 128 pixels of bf16
+    p.b_stage = (uint32_t)p.groupsB * 128u * (p.chunkB * 2);
+    int sb = (int)((kSmemBudget - 2 * p.a_stage) / p.b_stage);
+    p.stagesB = sb > kMaxStages ? kMaxStages : (sb < 2 ? 2 : sb);
+}
+
 }  // namespace
 
 bool conv_tc_supported(const msx_conv_desc* d, bool fwd_pass) {
@@ -300,6 +503,50 @@ bool conv_tc_supported(const msx_conv_desc* d, bool fwd_pass) {
     if (d->dtype != MSX_BF16 || d->transposed || d->stride != 1) return false;
     if (d->oh != d->h || d->ow != d->w) return false;          // 'same' geometry (all stride-1 convs of the reference)
     return encode_fn() != nullptr;
+}
+
+size_t conv_wgrad_tc_ws_bytes(const msx_conv_desc* d) {
+    WgParams p;
+    wgrad_plan(d, p);
+    return (size_t)p.splits * p.kh * p.kw * p.Apad * (size_t)p.Bpad * sizeof(float);
+}
+
+int wgrad_reduce_launch(const float* partial, int splits, int taps, int A, int B, int Apad, int Bpad, float* dw, cudaStream_t st);
+
+// x: module input (big side, cin), dy: gradient of the module output (small side, cout); dw: [cout][cin][kh][kw] fp32.
+int conv_wgrad_tc(const msx_conv_desc* d, const void* x, const void* dy, float* dw, void* ws, size_t ws_bytes, cudaStream_t st) {
+    WgParams p;
+    wgrad_plan(d, p);
+    const size_t need = conv_wgrad_tc_ws_bytes(d);
+    if (ws_bytes < need) return set_error(MSX_ERR_WORKSPACE, "conv wgrad (tcgen05): workspace %zu < %zu", ws_bytes, need);
+    CUtensorMap tmS, tmG;
+    {
+        cuuint64_t dims[4] = {(cuuint64_t)p.Ap, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.N};
+        cuuint64_t strides[3] = {(cuuint64_t)d->ldy * 2, (cuuint64_t)d->ldy * 2 * p.W, (cuuint64_t)d->ldy * 2 * p.W * p.H};
+        cuuint32_t box[4] = {(cuuint32_t)p.chunkA, (cuuint32_t)p.tw, (cuuint32_t)p.th, 1};
+        MSX_TRY(make_map(&tmS, 4, dy, dims, strides, box, p.chunkA == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B));
+    }
+    {
+        cuuint64_t dims[4] = {(cuuint64_t)p.Bp, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.N};
+        cuuint64_t strides[3] = {(cuuint64_t)d->ldx * 2, (cuuint64_t)d->ldx * 2 * p.W, (cuuint64_t)d->ldx * 2 * p.W * p.H};
+        cuuint32_t box[4] = {(cuuint32_t)p.chunkB, (cuuint32_t)p.tw, (cuuint32_t)p.th, 1};
+        MSX_TRY(make_map(&tmG, 4, x, dims, strides, box, p.chunkB == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B));
+    }
+    static bool attr_set = false;
+    if (!attr_set) {
+        MSX_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr_set = true;
+    }
+    const size_t smem = 1024 + 2 * (size_t)p.a_stage + (size_t)p.stagesB * p.b_stage + 32 + 16 * kMaxStages + 64;
+    const int grid = p.a_tiles * p.b_tiles * p.tap_groups * p.splits;
+    const int taps = p.kh * p.kw;
+    const double M = (double)p.N * p.H * p.W;
+    {
+        ProfScope ps__(K_WGRAD_TC, st, M * (d->cin + d->cout) * 2.0, 2.0 * M * d->cin * d->cout * taps);
+        wgrad_tc_kernel<<<grid, kThreads, smem, st>>>(tmS, tmG, static_cast<float*>(ws), p);
+    }
+    MSX_LAUNCH_CHECK();
+    return wgrad_reduce_launch(static_cast<const float*>(ws), p.splits, taps, d->cout, d->cin, p.Apad, p.Bpad, dw, st);
 }
 
 int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
