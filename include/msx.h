@@ -144,6 +144,26 @@ int msx_bn_act_bwd(int dtype, const void* s, int32_t lds, const void* dz, int32_
  * consumers (DUCK.in_bn output feeds nine convolutions, models/ducknet.py:144-149). */
 int msx_sum_n(int dtype, int n_in, const void* const* host_xs, const int32_t* host_ldxs,
               int64_t pixels, int32_t channels, void* out, int32_t ldout, void* stream);
+/* Same computation and results as msx_bn_act_bwd, for callers that cannot allocate device memory or
+ * pass a workspace (engines with a fixed memory plan, deployments where cudaMalloc after start-up is
+ * not allowed, plug-ins that only see their input/output buffers).  It has no counterpart in the
+ * reference.  The reduction scratch is a fixed array inside the library image, so:
+ *   - channels must be <= MSX_BN_STATIC_MAX_CHANNELS, otherwise MSX_ERR_UNSUPPORTED is returned;
+ *   - each GPU that loads libmsx.so holds about 2.4 MB for it until the process exits;
+ *   - the device the buffers live on must be the current device;
+ *   - the first call on each device looks the scratch address up (no allocation); make that first call
+ *     before starting any stream capture;
+ *   - every call uses the same scratch: two calls that can run at the same time on one GPU (different
+ *     streams, or different host threads on different streams) race on it - keep them on one stream or
+ *     order them yourself.  Nothing has to be cleared between calls.
+ * The function performs no cudaMalloc / cudaFree and calls no allocating library routine (leave the
+ * optional msx_profile_enable() measurement mode off: it creates CUDA events). */
+#define MSX_BN_STATIC_MAX_CHANNELS 256
+int msx_bn_act_bwd_static(int dtype, const void* s, int32_t lds, const void* dz, int32_t lddz,
+                          int64_t pixels, int32_t channels,
+                          const float* gamma, const float* beta, const float* save_mean, const float* save_invstd,
+                          int relu, void* ds, int32_t ldds, float* dgamma, float* dbeta, void* stream);
+
 /* backward of the nearest-2x upsample: da[n,y,x,:] = sum of the 2x2 block of ds. */
 int msx_upsample2x_bwd(int dtype, const void* ds, int32_t ldds, int32_t n, int32_t h, int32_t w,
                        int32_t channels, void* da, int32_t ldda, void* stream);

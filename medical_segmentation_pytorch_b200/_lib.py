@@ -29,7 +29,7 @@ class MsxError(RuntimeError):
 def _load():
     if not os.path.exists(LIB_PATH):
         raise ImportError(
-            f'{LIB_PATH} not found: build it with `python -m medical_segmentation_pytorch_b200.build` '
+            f'{LIB_PATH} not found: build it with `python medical_segmentation_pytorch_b200/build.py` '
             '(nvcc, sm_100a). There is no fallback path.')
     lib = C.CDLL(LIB_PATH)
     p, i32, i64, f32, sz = C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_size_t
@@ -58,6 +58,7 @@ def _load():
                                          i32, i32, i32, i32, p, i32, p, p, p, p, p, f32, f32, C.c_int, C.c_int,
                                          p, i32, p, p, p, sz, p]),
         'msx_bn_act_bwd': (C.c_int, [C.c_int, p, i32, p, i32, i64, i32, p, p, p, p, C.c_int, p, i32, p, p, p, sz, p]),
+        'msx_bn_act_bwd_static': (C.c_int, [C.c_int, p, i32, p, i32, i64, i32, p, p, p, p, C.c_int, p, i32, p, p, p]),
         'msx_sum_n': (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(i32), i64, i32, p, i32, p]),
         'msx_upsample2x_bwd': (C.c_int, [C.c_int, p, i32, i32, i32, i32, i32, p, i32, p]),
         'msx_maxpool3s2_fwd': (C.c_int, [C.c_int, p, i32, i32, i32, i32, i32, p, i32, p, i32, p]),

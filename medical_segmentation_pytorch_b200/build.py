@@ -1,6 +1,6 @@
 """In-tree build of libmsx.so (sm_100a only) with nvcc; no torch headers are involved.
 
-``python -m medical_segmentation_pytorch_b200.build`` or ``__graft_entry__.build()``.
+``python medical_segmentation_pytorch_b200/build.py`` or ``__graft_entry__.build()``.
 nvcc cross-compiles without a GPU; the .so stays next to this file (git-ignored, but it travels
 to the GPU box with the gpurun snapshot).
 """
@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, 'csrc')
 LIB = os.path.join(HERE, 'libmsx.so')
 STAMP = os.path.join(HERE, 'csrc', '.build_stamp')
-SOURCES = ['api.cu', 'norm.cu', 'conv_simt.cu', 'conv_tc.cu', 'conv_api.cu', 'loss.cu', 'head.cu', 'optim.cu']
+SOURCES = ['api.cu', 'norm.cu', 'conv_simt.cu', 'conv_tc.cu', 'conv_api.cu', 'loss.cu', 'head.cu', 'optim.cu', 'noalloc.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-lineinfo', '-std=c++17',
               '-Xcompiler', '-fPIC', '--expt-relaxed-constexpr']
 
