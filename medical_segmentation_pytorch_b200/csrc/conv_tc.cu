@@ -19,6 +19,7 @@
 //                 TMEM ring of 2 accumulators (tmem_full / tmem_empty mbarriers).
 //   Scheduling    persistent: grid = min(#tiles, 148), static round-robin over (pixel tile, n tile).
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 
@@ -41,7 +42,7 @@ struct TcParams {
     int stages;
     uint32_t a_bytes, b_bytes, a_stage, b_stage;   // TMA box bytes and smem stage pitch
     int tmem_cols;
-    int64_t total_tiles;
+    int total_tiles;
 };
 
 // ---- PTX wrappers -----------------------------------------------------------------------------
@@ -138,20 +139,19 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
     const int taps = p.kh * p.kw;
-    const int64_t tiles_per_img = (int64_t)p.tiles_x * p.tiles_y;
-    const int64_t m_tiles = tiles_per_img * p.N;
+    const int tiles_per_img = p.tiles_x * p.tiles_y;
+    const int m_tiles = tiles_per_img * p.N;
 
     if (warp == 0) {
         // ================= TMA producer =================
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int64_t t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
-                const int nt = (int)(t / m_tiles);
-                const int64_t mt = t % m_tiles;
-                const int img = (int)(mt / tiles_per_img);
-                const int rem = (int)(mt % tiles_per_img);
-                const int y0 = (rem / p.tiles_x) * p.th, x0 = (rem % p.tiles_x) * p.tw;
+            for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
+                const int nt = t / m_tiles, mt = t - nt * m_tiles;
+                const int img = mt / tiles_per_img, rem = mt - img * tiles_per_img;
+                const int ty = rem / p.tiles_x;
+                const int y0 = ty * p.th, x0 = (rem - ty * p.tiles_x) * p.tw;
                 for (int tap = 0; tap < taps; ++tap) {
                     const int r = tap / p.kw, s = tap % p.kw;
                     const int sy = y0 + r * p.mul_t + p.off_h, sx = x0 + s * p.mul_t + p.off_w;
@@ -174,7 +174,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
-            for (int64_t t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
+            for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
                 const int as = it & 1;
                 mbar_wait(bar_tempty + 8 * as, ((it >> 1) & 1) ^ 1);         // epilogue has drained this accumulator
                 tc_fence_after();
@@ -205,13 +205,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int m = quad * 32 + lane;
         const int dy = m / p.tw, dx = m % p.tw;
         int it = 0;
-        for (int64_t t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
+        for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
             const int as = it & 1;
-            const int nt = (int)(t / m_tiles);
-            const int64_t mt = t % m_tiles;
-            const int img = (int)(mt / tiles_per_img);
-            const int rem = (int)(mt % tiles_per_img);
-            const int y = (rem / p.tiles_x) * p.th + dy, x = (rem % p.tiles_x) * p.tw + dx;
+            const int nt = t / m_tiles, mt = t - nt * m_tiles;
+            const int img = mt / tiles_per_img, rem = mt - img * tiles_per_img;
+            const int ty = rem / p.tiles_x;
+            const int y = ty * p.th + dy, x = (rem - ty * p.tiles_x) * p.tw + dx;
             const bool valid = dy < p.th && y < p.H && x < p.W;
             const int n0 = nt * p.BN;
             const int ncols = min(p.BN, p.ncp - n0);                         // multiple of 8
@@ -230,6 +229,158 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                         float a = __uint_as_float(v[2 * j]), b = __uint_as_float(v[2 * j + 1]);
                         if (bias) {
                             const int c = n0 + c0 + 2 * j;
+                            a += c < p.Nc ? bias[c] : 0.f;
+                            b += c + 1 < p.Nc ? bias[c + 1] : 0.f;
+                        }
+                        __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+                        w[j] = *reinterpret_cast<uint32_t*>(&h);
+                    }
+                    *reinterpret_cast<uint4*>(out + c0) = make_uint4(w[0], w[1], w[2], w[3]);
+                    if (c0 + 8 < ncols) *reinterpret_cast<uint4*>(out + c0 + 8) = make_uint4(w[4], w[5], w[6], w[7]);
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)p.tmem_cols));
+    }
+}
+
+// =================================================================================================
+// "Halo" variant for layers whose whole reduction fits one 64-channel chunk and whose weights fit in
+// shared memory (DUCK-Net's 17/34-channel levels, UNet's 32/64: >80 % of the conv bytes).
+// The streaming kernel above re-fetches the A tile once per tap (9x L2->SM traffic for a 3x3).  Here the
+// tile is an 8 (x) by 16 (y) pixel patch and ONE TMA box brings the patch plus its halo, Wh = 16 (or 8)
+// pixels wide, into shared memory.  Because the row pitch of the halo (Wh pixels = Wh*128 B) is a
+// multiple of the 1024 B swizzle period, the A operand of tap (r, s) is the same shared memory seen
+// through a descriptor whose start is shifted by (r'*Wh + s') pixel rows and whose 8-row groups are
+// Wh*128 B apart: the 8 pixels of tile row dy are 8 consecutive halo rows.  All taps' weights stay resident.
+struct HaloParams {
+    int N, H, W, tiles_x, tiles_y, total_tiles;
+    int kh, kw, mul_t, off_h, off_w, oy_min, ox_min;
+    int Wh, Hh, BN, ksteps, Nc, ncp, ldd;
+    int stages, tmem_cols;
+    uint32_t a_bytes, a_stage, b_tap_bytes;
+};
+
+// Start address shifted by whole 128 B pixel rows, base_offset field left 0: measured on B200, the
+// 128B swizzle is applied to the absolute shared-memory address bits, so a window that starts at any
+// row of a TMA-written (1024 B aligned) buffer reads back consistently.  (Setting the descriptor's
+// base_offset to (addr >> 7) & 7 gives wrong results.)
+__device__ __forceinline__ uint64_t umma_desc_halo(uint32_t saddr, uint32_t sbo_bytes) {
+    return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    bf16* __restrict__ dst, const float* __restrict__ bias, const HaloParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    const int taps = p.kh * p.kw;
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t sB = base, sA = base + ((taps * p.b_tap_bytes + 1023u) & ~1023u);
+    const uint32_t bars = sA + p.stages * p.a_stage;
+    const uint32_t bar_full = bars, bar_empty = bars + 8 * kMaxStages;
+    const uint32_t bar_tfull = bars + 16 * kMaxStages, bar_tempty = bar_tfull + 16, bar_w = bar_tempty + 16;
+    const uint32_t tmem_slot = bar_w + 8;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < p.stages; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(bar_tfull + 8 * a, 1); mbar_init(bar_tempty + 8 * a, 4); }
+        mbar_init(bar_w, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"((uint32_t)p.tmem_cols));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    uint32_t tmem_base;
+    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+    const int tiles_per_img = p.tiles_x * p.tiles_y;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            mbar_expect_tx(bar_w, taps * p.b_tap_bytes);                       // resident weights, once per CTA
+            for (int tap = 0; tap < taps; ++tap) tma_load_3d(sB + tap * p.b_tap_bytes, &tmB, bar_w, 0, 0, tap);
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
+                const int img = t / tiles_per_img, rem = t - img * tiles_per_img;
+                const int ty = rem / p.tiles_x;
+                const int y0 = ty * 16, x0 = (rem - ty * p.tiles_x) * 8;
+                mbar_wait(bar_empty + 8 * stage, phase ^ 1);
+                mbar_expect_tx(bar_full + 8 * stage, p.a_bytes);
+                tma_load_4d(sA + stage * p.a_stage, &tmA, bar_full + 8 * stage, 0, x0 + p.ox_min, y0 + p.oy_min, img);
+                if (++stage == p.stages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((128u >> 4) << 24);
+            const uint32_t sbo = p.Wh * 128;
+            mbar_wait(bar_w, 0);
+            tc_fence_after();
+            int stage = 0, it = 0;
+            uint32_t phase = 0;
+            for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
+                const int as = it & 1;
+                mbar_wait(bar_tempty + 8 * as, ((it >> 1) & 1) ^ 1);
+                mbar_wait(bar_full + 8 * stage, phase);
+                tc_fence_after();
+                const uint32_t tmem_d = tmem_base + as * p.BN;
+                const uint32_t abase = sA + stage * p.a_stage;
+                uint32_t acc = 0;
+                for (int tap = 0; tap < taps; ++tap) {
+                    const int r = tap / p.kw, s = tap - r * p.kw;
+                    const int ry = r * p.mul_t + p.off_h - p.oy_min, sx = s * p.mul_t + p.off_w - p.ox_min;
+                    const uint64_t da = umma_desc_halo(abase + (ry * p.Wh + sx) * 128, sbo);
+                    const uint64_t db = umma_desc(sB + tap * p.b_tap_bytes, 128);
+                    for (int k = 0; k < p.ksteps; ++k) {
+                        umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, acc);
+                        acc = 1;
+                    }
+                }
+                umma_commit(bar_empty + 8 * stage);
+                umma_commit(bar_tfull + 8 * as);
+                if (++stage == p.stages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else {
+        const int quad = warp & 3;
+        const int m = quad * 32 + lane;
+        const int dy = m >> 3, dx = m & 7;
+        const int ncols = p.ncp;
+        int it = 0;
+        for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
+            const int as = it & 1;
+            const int img = t / tiles_per_img, rem = t - img * tiles_per_img;
+            const int ty = rem / p.tiles_x;
+            const int y = ty * 16 + dy, x = (rem - ty * p.tiles_x) * 8 + dx;
+            const bool valid = y < p.H && x < p.W;
+            bf16* out = dst + ((int64_t)(img * p.H + y) * p.W + x) * p.ldd;
+            mbar_wait(bar_tfull + 8 * as, (it >> 1) & 1);
+            tc_fence_after();
+            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + as * p.BN;
+            for (int c0 = 0; c0 < ncols; c0 += 16) {
+                uint32_t v[16];
+                tmem_ld16(taddr + c0, v);
+                tmem_ld_wait();
+                if (valid) {
+                    uint32_t w[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        float a = __uint_as_float(v[2 * j]), b = __uint_as_float(v[2 * j + 1]);
+                        if (bias) {
+                            const int c = c0 + 2 * j;
                             a += c < p.Nc ? bias[c] : 0.f;
                             b += c + 1 < p.Nc ? bias[c + 1] : 0.f;
                         }
@@ -549,8 +700,87 @@ int conv_wgrad_tc(const msx_conv_desc* d, const void* x, const void* dy, float* 
     return wgrad_reduce_launch(static_cast<const float*>(ws), p.splits, taps, d->cout, d->cin, p.Apad, p.Bpad, dw, st);
 }
 
+static int g_halo_mode = -1;   // -1: read MSX_TC_HALO from the environment (0 = streaming kernel only; measurement switch)
+
+static int halo_mode() {
+    if (g_halo_mode < 0) {
+        const char* e = getenv("MSX_TC_HALO");
+        g_halo_mode = e ? atoi(e) : 1;
+    }
+    return g_halo_mode;
+}
+
+static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
+                               void* dst, cudaStream_t st, bool* used) {
+    *used = false;
+    const int mode = halo_mode();
+    if (mode == 0) return MSX_OK;
+    const int K = fwd_pass ? d->cin : d->cout, Nc = fwd_pass ? d->cout : d->cin;
+    const int Kp = round_up(K, 8), Np = round_up(Nc, 16), taps = d->kh * d->kw;
+    if (Kp > 64 || Np > 256 || taps < 2) return MSX_OK;
+    if ((size_t)taps * Np * 128 > 80 * 1024) return MSX_OK;
+    const int span_w = (d->kw - 1) * d->dil, span_h = (d->kh - 1) * d->dil;
+    if (8 + span_w > 16) return MSX_OK;
+    HaloParams p;
+    p.N = d->n; p.H = d->h; p.W = d->w;
+    p.tiles_x = (p.W + 7) / 8; p.tiles_y = (p.H + 15) / 16;
+    const double eff = (double)p.W * p.H / ((double)p.tiles_x * p.tiles_y * 128.0);
+    if (eff < 0.75) return MSX_OK;
+    p.total_tiles = p.tiles_x * p.tiles_y * p.N;
+    p.kh = d->kh; p.kw = d->kw;
+    if (fwd_pass) { p.mul_t = d->dil; p.off_h = -d->pad_h; p.off_w = -d->pad_w; p.oy_min = p.off_h; p.ox_min = p.off_w; }
+    else          { p.mul_t = -d->dil; p.off_h = d->pad_h; p.off_w = d->pad_w; p.oy_min = p.off_h - span_h; p.ox_min = p.off_w - span_w; }
+    p.Wh = span_w > 0 ? 16 : 8;
+    p.Hh = 16 + span_h;
+    p.BN = Np; p.ksteps = (Kp + 15) / 16;
+    p.Nc = Nc; p.ncp = round_up(Nc, 8); p.ldd = fwd_pass ? d->ldy : d->ldx;
+    p.a_bytes = (uint32_t)p.Hh * p.Wh * 128;
+    p.a_stage = (p.a_bytes + 1023u) & ~1023u;
+    p.b_tap_bytes = (uint32_t)p.BN * 128;
+    const uint32_t bres = ((uint32_t)taps * p.b_tap_bytes + 1023u) & ~1023u;
+    int stages = (int)((kSmemBudget - bres) / p.a_stage);
+    p.stages = stages > kMaxStages ? kMaxStages : stages;
+    if (p.stages < 2) return MSX_OK;
+    int cols = 32;
+    while (cols < 2 * p.BN) cols <<= 1;
+    p.tmem_cols = cols;
+    const int lds = fwd_pass ? d->ldx : d->ldy;
+    CUtensorMap tmA, tmB;
+    {
+        cuuint64_t dims[4] = {(cuuint64_t)Kp, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.N};
+        cuuint64_t strides[3] = {(cuuint64_t)lds * 2, (cuuint64_t)lds * 2 * p.W, (cuuint64_t)lds * 2 * p.W * p.H};
+        cuuint32_t box[4] = {64, (cuuint32_t)p.Wh, (cuuint32_t)p.Hh, 1};
+        MSX_TRY(make_map(&tmA, 4, src, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B));
+    }
+    {
+        cuuint64_t dims[3] = {(cuuint64_t)Kp, (cuuint64_t)Np, (cuuint64_t)taps};
+        cuuint64_t strides[2] = {(cuuint64_t)Kp * 2, (cuuint64_t)Kp * 2 * Np};
+        cuuint32_t box[3] = {64, (cuuint32_t)p.BN, 1};
+        MSX_TRY(make_map(&tmB, 3, packed, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B));
+    }
+    static bool attr_set = false;
+    if (!attr_set) {
+        MSX_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        attr_set = true;
+    }
+    const size_t smem = 1024 + bres + (size_t)p.stages * p.a_stage + 16 * kMaxStages + 96;
+    const int grid = p.total_tiles < kNumSMs ? p.total_tiles : kNumSMs;
+    const double M = (double)p.N * p.H * p.W;
+    {
+        ProfScope ps__(K_CONV_TC, st, M * (K + Nc) * 2.0, 2.0 * M * Nc * K * taps);
+        conv_tc_halo_kernel<<<grid, kThreads, smem, st>>>(tmA, tmB, static_cast<bf16*>(dst), bias, p);
+    }
+    MSX_LAUNCH_CHECK();
+    note_conv_engine(MSX_ENGINE_TCGEN05);
+    *used = true;
+    return MSX_OK;
+}
+
 int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
                    void* dst, cudaStream_t st) {
+    bool used = false;
+    MSX_TRY(conv_gather_tc_halo(d, fwd_pass, src, packed, bias, dst, st, &used));
+    if (used) return MSX_OK;
     TcParams p;
     const int K = fwd_pass ? d->cin : d->cout, Nc = fwd_pass ? d->cout : d->cin;
     const int lds = fwd_pass ? d->ldx : d->ldy;
@@ -568,7 +798,7 @@ int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const
     pick_tile(p.H, p.W, p.tw, p.th);
     p.tiles_x = (p.W + p.tw - 1) / p.tw;
     p.tiles_y = (p.H + p.th - 1) / p.th;
-    p.total_tiles = (int64_t)p.tiles_x * p.tiles_y * p.N * p.n_tiles;
+    p.total_tiles = p.tiles_x * p.tiles_y * p.N * p.n_tiles;
     const uint32_t row_bytes = p.chunk * 2;
     p.a_bytes = (uint32_t)p.tw * p.th * row_bytes;
     p.b_bytes = (uint32_t)p.BN * row_bytes;
@@ -600,7 +830,7 @@ int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const
         MSX_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_set = true;
     }
-    const int grid = (int)(p.total_tiles < kNumSMs ? p.total_tiles : kNumSMs);
+    const int grid = p.total_tiles < kNumSMs ? p.total_tiles : kNumSMs;
     const double M = (double)p.N * p.H * p.W;
     {
         ProfScope ps__(K_CONV_TC, st, M * (K + Nc) * 2.0, 2.0 * M * Nc * K * p.kh * p.kw);

@@ -77,6 +77,10 @@ TC_CASES = [
     (32, 32, 3, 3, 1, 64, 64, 1),
     (64, 32, 3, 3, 1, 40, 40, 2),       # UNet-style, 40x40 (ragged tiles)
     (128, 256, 3, 3, 1, 20, 20, 2),
+    (17, 17, 1, 7, 1, 32, 64, 2),       # halo path, x-halo 6
+    (17, 17, 7, 1, 1, 64, 32, 2),       # halo path, no x-halo (8-pixel-wide halo rows)
+    (17, 17, 3, 3, 3, 48, 48, 2),       # halo path, dilation 3
+    (64, 64, 3, 3, 1, 48, 40, 1),       # halo path, full 64-channel chunk
 ]
 
 
