@@ -28,6 +28,7 @@ namespace msx {
 namespace {
 
 constexpr int kThreads = 192;
+constexpr int kHaloThreads = 320;      // TMA warp + MMA warp + 2 x 4 epilogue warps
 constexpr int kMaxStages = 8;
 constexpr uint32_t kSmemBudget = 200 * 1024;
 
@@ -102,6 +103,20 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
           "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
         : "r"(taddr));
 }
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+          "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+          "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+}
+__device__ __forceinline__ uint32_t pack_bf16(uint32_t a, uint32_t b) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(a), __uint_as_float(b));
+    return *reinterpret_cast<uint32_t*>(&h);
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // K-major operand descriptor for a tile of rows x (64|32) bf16, rows `row_bytes` apart, 8-row swizzle
@@ -171,6 +186,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             // cute::UMMA::InstrDescriptor: c=F32 (bit 4), a=b=BF16 (bits 7, 10), K-major A and B, N>>3 @17, M>>4 @24
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((128u >> 4) << 24);
             const uint32_t row_bytes = p.chunk * 2;
+            const uint64_t hi = umma_desc(0, row_bytes);
+            const uint32_t a_lo0 = (sA & 0x3FFFFu) >> 4, b_lo0 = (sB & 0x3FFFFu) >> 4, a_step = p.a_stage >> 4, b_step = p.b_stage >> 4;
+            const int full_ksteps = p.chunk / 16;
+            const int last_ksteps = (p.Kp - (p.kchunks - 1) * p.chunk + 15) / 16;
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
@@ -184,14 +203,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     for (int kc = 0; kc < p.kchunks; ++kc) {
                         mbar_wait(bar_full + 8 * stage, phase);              // TMA bytes have landed
                         tc_fence_after();
-                        const int kleft = p.Kp - kc * p.chunk;
-                        const int ksteps = kleft >= p.chunk ? p.chunk / 16 : (kleft + 15) / 16;
-                        const uint64_t da = umma_desc(sA + stage * p.a_stage, row_bytes);
-                        const uint64_t db = umma_desc(sB + stage * p.b_stage, row_bytes);
-                        for (int k = 0; k < ksteps; ++k) {
-                            umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, acc);   // +32 B per K=16 step
-                            acc = 1;
-                        }
+                        const int ksteps = kc == p.kchunks - 1 ? last_ksteps : full_ksteps;
+                        const uint64_t da = hi | (uint64_t)(a_lo0 + stage * a_step);
+                        const uint64_t db = hi | (uint64_t)(b_lo0 + stage * b_step);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            if (k < ksteps) { umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, acc); acc = 1; }   // +32 B per K=16 step
                         umma_commit(bar_empty + 8 * stage);                  // frees the smem stage when the MMAs retire
                         if (++stage == p.stages) { stage = 0; phase ^= 1; }
                     }
@@ -277,7 +294,7 @@ __device__ __forceinline__ uint64_t umma_desc_halo(uint32_t saddr, uint32_t sbo_
     return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
 
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kHaloThreads, 1)
 conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     bf16* __restrict__ dst, const float* __restrict__ bias, const HaloParams p) {
     extern __shared__ uint8_t smem_raw[];
@@ -326,7 +343,21 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     } else if (warp == 1) {
         if (lane == 0) {
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((128u >> 4) << 24);
-            const uint32_t sbo = p.Wh * 128;
+            // The issuing thread is latency bound on its own instruction stream, so everything that does
+            // not change per tile is hoisted: per-tap start-address offsets (16 B units, the descriptor's
+            // address field) live in registers and the tap / k loops are fully unrolled.
+            constexpr int kMaxTaps = 9;
+            uint32_t a_off[kMaxTaps], b_lo[kMaxTaps];
+#pragma unroll
+            for (int tap = 0; tap < kMaxTaps; ++tap) {
+                const int r = tap / p.kw, s = tap - r * p.kw;
+                const int ry = r * p.mul_t + p.off_h - p.oy_min, sx = s * p.mul_t + p.off_w - p.ox_min;
+                a_off[tap] = (uint32_t)((ry * p.Wh + sx) * 128) >> 4;
+                b_lo[tap] = ((sB + tap * p.b_tap_bytes) & 0x3FFFFu) >> 4;
+            }
+            const uint64_t hi_a = (1ull << 16) | ((uint64_t)((p.Wh * 128) >> 4) << 32) | (1ull << 46) | (2ull << 61);
+            const uint64_t hi_b = (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+            const int ksteps = p.ksteps;
             mbar_wait(bar_w, 0);
             tc_fence_after();
             int stage = 0, it = 0;
@@ -337,16 +368,15 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 mbar_wait(bar_full + 8 * stage, phase);
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + as * p.BN;
-                const uint32_t abase = sA + stage * p.a_stage;
-                uint32_t acc = 0;
-                for (int tap = 0; tap < taps; ++tap) {
-                    const int r = tap / p.kw, s = tap - r * p.kw;
-                    const int ry = r * p.mul_t + p.off_h - p.oy_min, sx = s * p.mul_t + p.off_w - p.ox_min;
-                    const uint64_t da = umma_desc_halo(abase + (ry * p.Wh + sx) * 128, sbo);
-                    const uint64_t db = umma_desc(sB + tap * p.b_tap_bytes, 128);
-                    for (int k = 0; k < p.ksteps; ++k) {
-                        umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, acc);
-                        acc = 1;
+                const uint32_t a_lo = ((sA + stage * p.a_stage) & 0x3FFFFu) >> 4;
+#pragma unroll
+                for (int tap = 0; tap < kMaxTaps; ++tap) {
+                    if (tap < taps) {
+                        const uint64_t da = hi_a | (uint64_t)(a_lo + a_off[tap]);
+                        const uint64_t db = hi_b | (uint64_t)b_lo[tap];
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            if (k < ksteps) umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (tap | k) ? 1u : 0u);
                     }
                 }
                 umma_commit(bar_empty + 8 * stage);
@@ -355,45 +385,60 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
         }
     } else {
-        const int quad = warp & 3;
+        // ===== epilogue: two groups of four warps; group g drains accumulator g (tiles with it % 2 == g), so
+        // two tiles are converted and stored concurrently (each group alone is latency bound) =====
+        const int quad = warp & 3, grp = (warp - 2) >> 2;
         const int m = quad * 32 + lane;
         const int dy = m >> 3, dx = m & 7;
         const int ncols = p.ncp;
-        int it = 0;
-        for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
-            const int as = it & 1;
+        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + grp * p.BN;
+        int it = grp;
+        for (int t = blockIdx.x + grp * gridDim.x; t < p.total_tiles; t += 2 * gridDim.x, it += 2) {
             const int img = t / tiles_per_img, rem = t - img * tiles_per_img;
             const int ty = rem / p.tiles_x;
             const int y = ty * 16 + dy, x = (rem - ty * p.tiles_x) * 8 + dx;
             const bool valid = y < p.H && x < p.W;
             bf16* out = dst + ((int64_t)(img * p.H + y) * p.W + x) * p.ldd;
-            mbar_wait(bar_tfull + 8 * as, (it >> 1) & 1);
+            mbar_wait(bar_tfull + 8 * grp, (it >> 1) & 1);
             tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + as * p.BN;
-            for (int c0 = 0; c0 < ncols; c0 += 16) {
+            int c0 = 0;
+            for (; c0 + 32 <= ncols || (c0 < ncols && ncols - c0 > 16); c0 += 32) {
+                uint32_t v[32];
+                tmem_ld32(taddr + c0, v);
+                tmem_ld_wait();
+                if (valid) {
+                    if (bias) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + (c0 + j < p.Nc ? bias[c0 + j] : 0.f));
+                    }
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+                        if (c0 + 8 * q < ncols)
+                            *reinterpret_cast<uint4*>(out + c0 + 8 * q) =
+                                make_uint4(pack_bf16(v[8 * q], v[8 * q + 1]), pack_bf16(v[8 * q + 2], v[8 * q + 3]),
+                                           pack_bf16(v[8 * q + 4], v[8 * q + 5]), pack_bf16(v[8 * q + 6], v[8 * q + 7]));
+                }
+            }
+            for (; c0 < ncols; c0 += 16) {
                 uint32_t v[16];
                 tmem_ld16(taddr + c0, v);
                 tmem_ld_wait();
                 if (valid) {
-                    uint32_t w[8];
+                    if (bias) {
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        float a = __uint_as_float(v[2 * j]), b = __uint_as_float(v[2 * j + 1]);
-                        if (bias) {
-                            const int c = c0 + 2 * j;
-                            a += c < p.Nc ? bias[c] : 0.f;
-                            b += c + 1 < p.Nc ? bias[c + 1] : 0.f;
-                        }
-                        __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-                        w[j] = *reinterpret_cast<uint32_t*>(&h);
+                        for (int j = 0; j < 16; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + (c0 + j < p.Nc ? bias[c0 + j] : 0.f));
                     }
-                    *reinterpret_cast<uint4*>(out + c0) = make_uint4(w[0], w[1], w[2], w[3]);
-                    if (c0 + 8 < ncols) *reinterpret_cast<uint4*>(out + c0 + 8) = make_uint4(w[4], w[5], w[6], w[7]);
+#pragma unroll
+                    for (int q = 0; q < 2; ++q)
+                        if (c0 + 8 * q < ncols)
+                            *reinterpret_cast<uint4*>(out + c0 + 8 * q) =
+                                make_uint4(pack_bf16(v[8 * q], v[8 * q + 1]), pack_bf16(v[8 * q + 2], v[8 * q + 3]),
+                                           pack_bf16(v[8 * q + 4], v[8 * q + 5]), pack_bf16(v[8 * q + 6], v[8 * q + 7]));
                 }
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
+            if (lane == 0) mbar_arrive(bar_tempty + 8 * grp);
         }
     }
     tc_fence_before();
@@ -717,7 +762,7 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     if (mode == 0) return MSX_OK;
     const int K = fwd_pass ? d->cin : d->cout, Nc = fwd_pass ? d->cout : d->cin;
     const int Kp = round_up(K, 8), Np = round_up(Nc, 16), taps = d->kh * d->kw;
-    if (Kp > 64 || Np > 256 || taps < 2) return MSX_OK;
+    if (Kp > 64 || Np > 256 || taps < 2 || taps > 9) return MSX_OK;
     if ((size_t)taps * Np * 128 > 80 * 1024) return MSX_OK;
     const int span_w = (d->kw - 1) * d->dil, span_h = (d->kh - 1) * d->dil;
     if (8 + span_w > 16) return MSX_OK;
@@ -768,7 +813,7 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     const double M = (double)p.N * p.H * p.W;
     {
         ProfScope ps__(K_CONV_TC, st, M * (K + Nc) * 2.0, 2.0 * M * Nc * K * taps);
-        conv_tc_halo_kernel<<<grid, kThreads, smem, st>>>(tmA, tmB, static_cast<bf16*>(dst), bias, p);
+        conv_tc_halo_kernel<<<grid, kHaloThreads, smem, st>>>(tmA, tmB, static_cast<bf16*>(dst), bias, p);
     }
     MSX_LAUNCH_CHECK();
     note_conv_engine(MSX_ENGINE_TCGEN05);

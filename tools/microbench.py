@@ -23,12 +23,16 @@ def main():
     ap.add_argument('--batch', type=int, default=16)
     ap.add_argument('--reps', type=int, default=5)
     ap.add_argument('--engine', type=int, default=0)
+    ap.add_argument('--only', type=int, default=-1, help='index into SHAPES')
+    ap.add_argument('--passes', default='fprop,dgrad,wgrad')
     a = ap.parse_args()
     dev = torch.device('cuda')
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     st = L.stream()
     print(f'{"shape":28s} {"pass":6s} {"us":>9s} {"GB/s":>8s} {"TF/s":>8s}')
-    for cin, cout, kh, kw, dil, hw in SHAPES:
+    for idx, (cin, cout, kh, kw, dil, hw) in enumerate(SHAPES):
+        if a.only >= 0 and idx != a.only:
+            continue
         n = a.batch
         g = ops.ConvGeom(cin, cout, kh, kw, 1, dil, (kh - 1) // 2 * dil, (kw - 1) // 2 * dil, engine=a.engine)
         x = torch.randn(n, hw, hw, ops.rup(cin), device=dev).bfloat16()
@@ -53,6 +57,8 @@ def main():
         def wgrad():
             L.check(lib.msx_conv2d_bwd(C.byref(d), L.ptr(x), L.ptr(w), L.ptr(dy), L.ptr(pk), None, L.ptr(dw), None, L.ptr(ws), ws.numel(), st))
         for name, fn in (('fprop', fprop), ('dgrad', dgrad), ('wgrad', wgrad)):
+            if name not in a.passes.split(','):
+                continue
             fn()
             torch.cuda.synchronize()
             best = 1e9
