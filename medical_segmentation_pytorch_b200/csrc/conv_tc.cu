@@ -512,6 +512,7 @@ struct WgParams {
     int stagesB, tmem_cols;
     uint32_t a_stage, b_stage;
     int64_t pix_tiles;
+    int halo, Wh, Hh;                 // halo mode: one x patch (+halo) per pixel tile serves every tap
 };
 
 // MN-major operand descriptor: MN groups `lbo` bytes apart, 8-row (K) groups 8*row_bytes apart.
@@ -576,14 +577,21 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
                 for (int g = 0; g < groupsA; ++g)
                     tma_load_4d(sA + stA * p.a_stage + g * 128 * rbA, &tmS, barA_full + 8 * stA, a0 + g * p.chunkA, x0, y0, img);
                 if (++stA == SA) { stA = 0; phA ^= 1; }
-                for (int k = 0; k < ntap; ++k) {
-                    const int tap = tap0 + k, r = tap / p.kw, s = tap % p.kw;
+                if (p.halo) {
                     mbar_wait(barB_empty + 8 * stB, phB ^ 1);
-                    mbar_expect_tx(barB_full + 8 * stB, p.groupsB * 128 * rbB);
-                    for (int g = 0; g < p.groupsB; ++g)
-                        tma_load_4d(sB + stB * p.b_stage + g * 128 * rbB, &tmG, barB_full + 8 * stB, b0 + g * p.chunkB,
-                                    x0 + s * p.dil - p.pad_w, y0 + r * p.dil - p.pad_h, img);
+                    mbar_expect_tx(barB_full + 8 * stB, (uint32_t)p.Hh * p.Wh * rbB);
+                    tma_load_4d(sB + stB * p.b_stage, &tmG, barB_full + 8 * stB, b0, x0 - p.pad_w, y0 - p.pad_h, img);
                     if (++stB == p.stagesB) { stB = 0; phB ^= 1; }
+                } else {
+                    for (int k = 0; k < ntap; ++k) {
+                        const int tap = tap0 + k, r = tap / p.kw, s = tap % p.kw;
+                        mbar_wait(barB_empty + 8 * stB, phB ^ 1);
+                        mbar_expect_tx(barB_full + 8 * stB, p.groupsB * 128 * rbB);
+                        for (int g = 0; g < p.groupsB; ++g)
+                            tma_load_4d(sB + stB * p.b_stage + g * 128 * rbB, &tmG, barB_full + 8 * stB, b0 + g * p.chunkB,
+                                        x0 + s * p.dil - p.pad_w, y0 + r * p.dil - p.pad_h, img);
+                        if (++stB == p.stagesB) { stB = 0; phB ^= 1; }
+                    }
                 }
             }
         }
@@ -594,6 +602,42 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
                                    ((uint32_t)(p.TN >> 3) << 17) | ((128u >> 4) << 24);
             int stA = 0, stB = 0;
             uint32_t phA = 0, phB = 0;
+            if (p.halo) {
+                // per-tap start offsets of the shifted x window inside the halo patch (16 B units), hoisted
+                constexpr int kMaxTaps = 9;
+                uint32_t b_off[kMaxTaps];
+#pragma unroll
+                for (int k = 0; k < kMaxTaps; ++k) {
+                    const int tap = tap0 + k, r = tap / p.kw, s = tap - r * p.kw;
+                    b_off[k] = (uint32_t)((r * p.dil * p.Wh + s * p.dil) * 128) >> 4;
+                }
+                const uint64_t hi_a = ((uint64_t)(((128 * rbA) >> 4) & 0x3FFFu) << 16) | ((uint64_t)((8 * rbA) >> 4) << 32) | (1ull << 46) |
+                                      ((rbA == 128 ? 2ull : 4ull) << 61);
+                const uint64_t hi_b = ((uint64_t)((p.Wh * 128) >> 4) << 32) | (1ull << 46) | (2ull << 61);    // one MN group: LBO unused
+                const uint32_t a_kk = (16 * rbA) >> 4, b_kk = (uint32_t)(2 * p.Wh * 128) >> 4;               // 16 pixels = 2 tile rows
+                for (int64_t t = t_beg; t < t_end; ++t) {
+                    mbar_wait(barA_full + 8 * stA, phA);
+                    mbar_wait(barB_full + 8 * stB, phB);
+                    tc_fence_after();
+                    const uint32_t a_lo = ((sA + stA * p.a_stage) & 0x3FFFFu) >> 4;
+                    const uint32_t b_lo = ((sB + stB * p.b_stage) & 0x3FFFFu) >> 4;
+                    const uint32_t first = t > t_beg ? 1u : 0u;
+#pragma unroll
+                    for (int k = 0; k < kMaxTaps; ++k) {
+                        if (k < ntap) {
+                            const uint32_t tmem_d = tmem_base + k * p.TN;
+#pragma unroll
+                            for (int kk = 0; kk < 8; ++kk)
+                                umma_bf16(tmem_d, hi_a | (uint64_t)(a_lo + kk * a_kk), hi_b | (uint64_t)(b_lo + b_off[k] + kk * b_kk),
+                                          idesc, kk ? 1u : first);
+                        }
+                    }
+                    umma_commit(barB_empty + 8 * stB);
+                    umma_commit(barA_empty + 8 * stA);
+                    if (++stB == p.stagesB) { stB = 0; phB ^= 1; }
+                    if (++stA == SA) { stA = 0; phA ^= 1; }
+                }
+            } else
             for (int64_t t = t_beg; t < t_end; ++t) {
                 mbar_wait(barA_full + 8 * stA, phA);
                 tc_fence_after();
@@ -647,6 +691,16 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
     }
 }
 
+int g_halo_mode = -1;   // -1: read MSX_TC_HALO from the environment (0 = streaming kernels only; measurement switch)
+
+int halo_mode() {
+    if (g_halo_mode < 0) {
+        const char* e = getenv("MSX_TC_HALO");
+        g_halo_mode = e ? atoi(e) : 1;
+    }
+    return g_halo_mode;
+}
+
 void pick_tile_pow2(int H, int W, int& tw, int& th) {
     double best = -1;
     tw = 16; th = 8;
@@ -688,6 +742,23 @@ void wgrad_plan(const msx_conv_desc* d, WgParams& p) {
     p.splits = (int)splits;
     p.a_stage = 128u * 256u;                                    // 128 channels x 128 pixels of bf16
     p.b_stage = (uint32_t)p.groupsB * 128u * (p.chunkB * 2);
+    // halo mode (see conv_tc_halo_kernel): x channels fit one 64-wide group, 8x16 tiles cover the image well
+    p.halo = 0; p.Wh = 0; p.Hh = 0;
+    {
+        const int span_w = (p.kw - 1) * p.dil, span_h = (p.kh - 1) * p.dil;
+        const int tx = (p.W + 7) / 8, ty = (p.H + 15) / 16;
+        const double eff = (double)p.W * p.H / ((double)tx * ty * 128.0);
+        if (halo_mode() && p.Bp <= 64 && p.b_tiles == 1 && taps >= 2 && taps <= 9 && 8 + span_w <= 16 && eff >= 0.75) {
+            p.halo = 1;
+            p.tw = 8; p.th = 16; p.tiles_x = tx; p.tiles_y = ty;
+            p.pix_tiles = (int64_t)tx * ty * p.N;
+            if (splits > p.pix_tiles) { splits = p.pix_tiles; p.splits = (int)splits; }
+            p.Wh = span_w > 0 ? 16 : 8;
+            p.Hh = 16 + span_h;
+            p.chunkB = 64; p.groupsB = 1;
+            p.b_stage = ((uint32_t)p.Hh * p.Wh * 128u + 1023u) & ~1023u;
+        }
+    }
     int sb = (int)((kSmemBudget - 2 * p.a_stage) / p.b_stage);
     p.stagesB = sb > kMaxStages ? kMaxStages : (sb < 2 ? 2 : sb);
 }
@@ -725,7 +796,7 @@ int conv_wgrad_tc(const msx_conv_desc* d, const void* x, const void* dy, float* 
     {
         cuuint64_t dims[4] = {(cuuint64_t)p.Bp, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.N};
         cuuint64_t strides[3] = {(cuuint64_t)d->ldx * 2, (cuuint64_t)d->ldx * 2 * p.W, (cuuint64_t)d->ldx * 2 * p.W * p.H};
-        cuuint32_t box[4] = {(cuuint32_t)p.chunkB, (cuuint32_t)p.tw, (cuuint32_t)p.th, 1};
+        cuuint32_t box[4] = {(cuuint32_t)p.chunkB, (cuuint32_t)(p.halo ? p.Wh : p.tw), (cuuint32_t)(p.halo ? p.Hh : p.th), 1};
         MSX_TRY(make_map(&tmG, 4, x, dims, strides, box, p.chunkB == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B));
     }
     static bool attr_set = false;
@@ -743,16 +814,6 @@ int conv_wgrad_tc(const msx_conv_desc* d, const void* x, const void* dy, float* 
     }
     MSX_LAUNCH_CHECK();
     return wgrad_reduce_launch(static_cast<const float*>(ws), p.splits, taps, d->cout, d->cin, p.Apad, p.Bpad, dw, st);
-}
-
-static int g_halo_mode = -1;   // -1: read MSX_TC_HALO from the environment (0 = streaming kernel only; measurement switch)
-
-static int halo_mode() {
-    if (g_halo_mode < 0) {
-        const char* e = getenv("MSX_TC_HALO");
-        g_halo_mode = e ? atoi(e) : 1;
-    }
-    return g_halo_mode;
 }
 
 static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,

@@ -84,7 +84,21 @@ __global__ void __launch_bounds__(256) bn_stats_kernel(const T* __restrict__ x, 
 #pragma unroll
     for (int j = 0; j < 2 * VEC; ++j) acc[j] = 0.0;
     if (t.active) {
-        for (int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane; p < pixels; p += (int64_t)gridDim.x * t.lanes) {
+        const int64_t step = (int64_t)gridDim.x * t.lanes;
+        int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane;
+        for (; p + 3 * step < pixels; p += 4 * step) {           // 4 independent 16 B loads in flight per thread
+            float v[4][VEC];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) Vec<T>::load(x + (p + u * step) * ld + t.c0, v[u]);
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int j = 0; j < VEC; ++j) {
+                    acc[j] += (double)v[u][j];
+                    acc[VEC + j] += (double)v[u][j] * (double)v[u][j];
+                }
+        }
+        for (; p < pixels; p += step) {
             float v[VEC];
             Vec<T>::load(x + p * ld + t.c0, v);
 #pragma unroll
@@ -108,7 +122,18 @@ __global__ void __launch_bounds__(256) bn_stats_kernel(const T* __restrict__ x, 
 __device__ inline void reduce_partials(const double* __restrict__ partials, int nblk, int cp, int c, double& s, double& q) {
     const int lane = threadIdx.x & 31;
     s = 0.0; q = 0.0;
-    for (int b = lane; b < nblk; b += 32) {
+    int b = lane;
+    for (; b + 96 < nblk; b += 128) {                           // 8 independent loads in flight
+        double s4[4], q4[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            s4[u] = partials[((int64_t)(b + 32 * u) * 2 + 0) * cp + c];
+            q4[u] = partials[((int64_t)(b + 32 * u) * 2 + 1) * cp + c];
+        }
+        s += (s4[0] + s4[1]) + (s4[2] + s4[3]);
+        q += (q4[0] + q4[1]) + (q4[2] + q4[3]);
+    }
+    for (; b < nblk; b += 32) {
         s += partials[((int64_t)b * 2 + 0) * cp + c];
         q += partials[((int64_t)b * 2 + 1) * cp + c];
     }
@@ -167,7 +192,23 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const T* __restrict__ x, 
         sc[j] = ok ? invstd[c] * gamma[c] : 0.f;
         sh[j] = ok ? beta[c] : 0.f;
     }
-    for (int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane; p < pixels; p += (int64_t)gridDim.x * t.lanes) {
+    const int64_t step = (int64_t)gridDim.x * t.lanes;
+    int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane;
+    for (; p + 3 * step < pixels; p += 4 * step) {
+        float v[4][VEC];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) Vec<T>::load(x + (p + u * step) * ldx + t.c0, v[u]);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) {
+                float r = (v[u][j] - mu[j]) * sc[j] + sh[j];
+                v[u][j] = relu ? fmaxf(r, 0.f) : r;
+            }
+            Vec<T>::store(z + (p + u * step) * ldz + t.c0, v[u]);
+        }
+    }
+    for (; p < pixels; p += step) {
         float v[VEC];
         Vec<T>::load(x + p * ldx + t.c0, v);
 #pragma unroll
@@ -203,10 +244,9 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const T* __restrict_
         acc[j] = 0.0; acc[VEC + j] = 0.0;
     }
     if (t.active) {
-        for (int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane; p < pixels; p += (int64_t)gridDim.x * t.lanes) {
-            float v[VEC], g[VEC];
-            Vec<T>::load(x + p * ldx + t.c0, v);
-            Vec<T>::load(dz + p * lddz + t.c0, g);
+        const int64_t step = (int64_t)gridDim.x * t.lanes;
+        int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane;
+        auto body = [&](const float (&v)[VEC], const float (&g)[VEC]) {
 #pragma unroll
             for (int j = 0; j < VEC; ++j) {
                 const float xh = (v[j] - mu[j]) * is[j];
@@ -215,6 +255,21 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const T* __restrict_
                 acc[j] += (double)gg;
                 acc[VEC + j] += (double)gg * (double)xh;
             }
+        };
+        for (; p + step < pixels; p += 2 * step) {               // 4 independent 16 B loads in flight per thread
+            float v0[VEC], g0[VEC], v1[VEC], g1[VEC];
+            Vec<T>::load(x + p * ldx + t.c0, v0);
+            Vec<T>::load(dz + p * lddz + t.c0, g0);
+            Vec<T>::load(x + (p + step) * ldx + t.c0, v1);
+            Vec<T>::load(dz + (p + step) * lddz + t.c0, g1);
+            body(v0, g0);
+            body(v1, g1);
+        }
+        for (; p < pixels; p += step) {
+            float v[VEC], g[VEC];
+            Vec<T>::load(x + p * ldx + t.c0, v);
+            Vec<T>::load(dz + p * lddz + t.c0, g);
+            body(v, g);
         }
     }
     lane_reduce<2 * VEC>(acc, shm, vch, t.lane, t.lanes);
@@ -264,10 +319,9 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const T* __restrict__
         k1[j] = ok ? c1[c] : 0.f;
         k2[j] = ok ? c2[c] : 0.f;
     }
-    for (int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane; p < pixels; p += (int64_t)gridDim.x * t.lanes) {
-        float v[VEC], g[VEC];
-        Vec<T>::load(x + p * ldx + t.c0, v);
-        Vec<T>::load(dz + p * lddz + t.c0, g);
+    const int64_t step = (int64_t)gridDim.x * t.lanes;
+    int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane;
+    auto body = [&](float (&v)[VEC], const float (&g)[VEC]) {
 #pragma unroll
         for (int j = 0; j < VEC; ++j) {
             const float xh = (v[j] - mu[j]) * is[j];
@@ -275,6 +329,23 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const T* __restrict__
             const float gg = (relu && !(out > 0.f)) ? 0.f : g[j];
             v[j] = (ga[j] * is[j]) * (gg - k1[j] - xh * k2[j]);
         }
+    };
+    for (; p + step < pixels; p += 2 * step) {
+        float v0[VEC], g0[VEC], v1[VEC], g1[VEC];
+        Vec<T>::load(x + p * ldx + t.c0, v0);
+        Vec<T>::load(dz + p * lddz + t.c0, g0);
+        Vec<T>::load(x + (p + step) * ldx + t.c0, v1);
+        Vec<T>::load(dz + (p + step) * lddz + t.c0, g1);
+        body(v0, g0);
+        body(v1, g1);
+        Vec<T>::store(dx + p * lddx + t.c0, v0);
+        Vec<T>::store(dx + (p + step) * lddx + t.c0, v1);
+    }
+    for (; p < pixels; p += step) {
+        float v[VEC], g[VEC];
+        Vec<T>::load(x + p * ldx + t.c0, v);
+        Vec<T>::load(dz + p * lddz + t.c0, g);
+        body(v, g);
         Vec<T>::store(dx + p * lddx + t.c0, v);
     }
 }
