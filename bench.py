@@ -124,6 +124,7 @@ def main():
     ap.add_argument('--dtype', default='bf16', choices=['bf16', 'fp32'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--profile-steps', type=int, default=2)
+    ap.add_argument('--no-graph', action='store_true', help='launch every kernel from Python instead of replaying one CUDA graph per step')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'b200' else args.warmup
     if args.impl == 'reference':
@@ -159,7 +160,8 @@ def main():
     ema = msx.ModelEma(model)
     loss_fn = msx.get_loss_fn(Cfg, dev)
     xh, th = synth_batch(B, S, S, seed=1 + rank)
-    xh, th = xh.pin_memory(), th.pin_memory()
+    if not os.environ.get('MSX_DBG_NOPIN'):
+        xh, th = xh.pin_memory(), th.pin_memory()
     xd, td = xh.to(dev), th.to(dev)
     it = [0]
 
@@ -168,9 +170,12 @@ def main():
         with torch.autocast('cuda', dtype=torch.bfloat16, enabled=bf16):
             loss = loss_fn(net(x), t)
         loss.backward()
-        opt.step()
+        dbg = os.environ.get('MSX_DBG_STEP', '')
+        if 'noopt' not in dbg:
+            opt.step()
         it[0] += 1
-        ema.update(model, it[0])
+        if 'noema' not in dbg:
+            ema.update(model, it[0])
         return loss
 
     def barrier():
@@ -191,24 +196,58 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms)
 
+    # static input buffers: the timed step either launches its ~3.5 k kernels from Python or replays them
+    # as ONE CUDA graph captured after an eager warm-up (F1 of SURVEY §8f: kills the launch overhead)
+    sx, st_ = xd.clone(), td.clone()
     for _ in range(args.warmup):
-        loss = step(xd, td)
+        # .detach(): a live eager loss keeps its autograd graph - and the parameters' AccumulateGrad nodes, which
+        # remember the (default) stream they were created on - alive; the captured backward would then wait on
+        # that uncaptured stream (cudaErrorStreamCaptureIsolation)
+        loss = step(sx, st_).detach()
     torch.cuda.synchronize()
     assert torch.isfinite(loss).item(), 'non-finite loss in warm-up'
+    graph, graph_err, launches_per_step = None, None, None
+    if not args.no_graph:
+        try:
+            l0 = _lib.lib.msx_launch_count()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                gloss = step(sx, st_)
+            launches_per_step = _lib.lib.msx_launch_count() - l0
+            graph.replay()
+            torch.cuda.synchronize()
+            assert torch.isfinite(gloss).item(), 'non-finite loss from the graph replay'
+        except Exception as e:                                   # noqa: BLE001 - report and fall back to eager launches
+            graph, graph_err = None, f'{type(e).__name__}: {e}'[:300]
+            if os.environ.get('MSX_BENCH_DEBUG'):
+                import traceback
+                traceback.print_exc()
+            torch.cuda.synchronize()
+    if world > 1:                                              # every rank must take the same path
+        flag = torch.tensor([1 if graph is not None else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag) == 0:
+            graph = None
+
+    def run_step():
+        if graph is not None:
+            graph.replay()
+            return gloss
+        return step(sx, st_)
 
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     l0 = _lib.lib.msx_launch_count()
-    ms = timed(lambda: step(xd, td), args.steps)
-    launches = _lib.lib.msx_launch_count() - l0
+    ms = timed(run_step, args.steps)
+    launches = (_lib.lib.msx_launch_count() - l0) if graph is None else launches_per_step * args.steps
     clocks = sampler.stop() if rank == 0 else None
 
     # end to end: pinned host buffers -> device every step, loss read back every step
     def e2e_step():
-        x = xh.to(dev, non_blocking=True)
-        t = th.to(dev, non_blocking=True)
-        return float(step(x, t))
+        sx.copy_(xh, non_blocking=True)
+        st_.copy_(th, non_blocking=True)
+        return float(run_step())
     e2e_step()
     ms_e2e = timed(e2e_step, args.steps)
 
@@ -217,7 +256,7 @@ def main():
     if rank == 0 and args.profile_steps > 0:
         _lib.lib.msx_profile_enable(1)
         for _ in range(args.profile_steps):
-            step(xd, td)
+            step(sx, st_)
         prof = _lib.profile_collect()
         _lib.lib.msx_profile_enable(0)
     barrier()
@@ -256,7 +295,8 @@ def main():
         'dtype': 'bf16' if bf16 else 'f32', 'data': 'synthetic',
         'config': {'workload': f'{args.model} training step (fwd+CE+bwd+Adam+EMA copy), {S}x{S}, batch {B}/GPU, num_class 2, per-GPU BN',
                    'global_batch': B * world, 'parallelism': f'dp{world}', 'l2': 'per-step working set >> 126 MB L2 (no flush needed)',
-                   'seed': 'weights manual_seed(1); data PCG64(1+rank)'},
+                   'seed': 'weights manual_seed(1); data PCG64(1+rank)',
+                   'launch': 'one CUDA graph replay per step' if graph is not None else 'eager Python launches' + (f' (graph capture failed: {graph_err})' if graph_err else '')},
         'clocks': clocks,
         'e2e': {'value': imgs / (ms_e2e / 1e3), 'unit': 'img/s', 'h2d_bytes_per_step': xh.numel() * 4 + th.numel() * 8, 'd2h_bytes_per_step': 4},
         'gpu_launches': int(launches),

@@ -677,9 +677,11 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
 #pragma unroll
                     for (int j = 0; j < 16; ++j) v[j] = 0u;                 // empty split: contributes zeros
                 }
+                if (a0 + row < p.Ap) {                                   // rows past the real channels are never read back
 #pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    *reinterpret_cast<uint4*>(out + c0 + 4 * j) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                    for (int j = 0; j < 4; ++j)
+                        *reinterpret_cast<uint4*>(out + c0 + 4 * j) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                }
             }
         }
     }

@@ -90,13 +90,15 @@ __global__ void __launch_bounds__(256) bn_stats_kernel(const T* __restrict__ x, 
             float v[4][VEC];
 #pragma unroll
             for (int u = 0; u < 4; ++u) Vec<T>::load(x + (p + u * step) * ld + t.c0, v[u]);
+            // fp32 over the 4 pixels, ONE F2F.F64 per channel and sum: the fp32->fp64 convert pipe, not HBM,
+            // was the limiter when every element was converted
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
-#pragma unroll
-                for (int j = 0; j < VEC; ++j) {
-                    acc[j] += (double)v[u][j];
-                    acc[VEC + j] += (double)v[u][j] * (double)v[u][j];
-                }
+            for (int j = 0; j < VEC; ++j) {
+                const float fs = (v[0][j] + v[1][j]) + (v[2][j] + v[3][j]);
+                const float fq = fmaf(v[0][j], v[0][j], v[1][j] * v[1][j]) + fmaf(v[2][j], v[2][j], v[3][j] * v[3][j]);
+                acc[j] += (double)fs;
+                acc[VEC + j] += (double)fq;
+            }
         }
         for (; p < pixels; p += step) {
             float v[VEC];
@@ -246,30 +248,38 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const T* __restrict_
     if (t.active) {
         const int64_t step = (int64_t)gridDim.x * t.lanes;
         int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane;
-        auto body = [&](const float (&v)[VEC], const float (&g)[VEC]) {
+        float fs[VEC], fq[VEC];
+        auto body = [&](const float (&v)[VEC], const float (&g)[VEC], bool first) {
 #pragma unroll
             for (int j = 0; j < VEC; ++j) {
                 const float xh = (v[j] - mu[j]) * is[j];
                 const float out = (v[j] - mu[j]) * (is[j] * ga[j]) + be[j];
                 const float gg = (relu && !(out > 0.f)) ? 0.f : g[j];
-                acc[j] += (double)gg;
-                acc[VEC + j] += (double)gg * (double)xh;
+                fs[j] = first ? gg : fs[j] + gg;
+                fq[j] = first ? gg * xh : fmaf(gg, xh, fq[j]);
             }
         };
-        for (; p + step < pixels; p += 2 * step) {               // 4 independent 16 B loads in flight per thread
-            float v0[VEC], g0[VEC], v1[VEC], g1[VEC];
-            Vec<T>::load(x + p * ldx + t.c0, v0);
-            Vec<T>::load(dz + p * lddz + t.c0, g0);
-            Vec<T>::load(x + (p + step) * ldx + t.c0, v1);
-            Vec<T>::load(dz + (p + step) * lddz + t.c0, g1);
-            body(v0, g0);
-            body(v1, g1);
+        auto flush = [&]() {
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) { acc[j] += (double)fs[j]; acc[VEC + j] += (double)fq[j]; }
+        };
+        for (; p + 3 * step < pixels; p += 4 * step) {           // 8 independent 16 B loads in flight per thread
+            float v[4][VEC], g[4][VEC];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                Vec<T>::load(x + (p + u * step) * ldx + t.c0, v[u]);
+                Vec<T>::load(dz + (p + u * step) * lddz + t.c0, g[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) body(v[u], g[u], u == 0);
+            flush();                                             // one fp32->fp64 conversion per 4 pixels
         }
         for (; p < pixels; p += step) {
             float v[VEC], g[VEC];
             Vec<T>::load(x + p * ldx + t.c0, v);
             Vec<T>::load(dz + p * lddz + t.c0, g);
-            body(v, g);
+            body(v, g, true);
+            flush();
         }
     }
     lane_reduce<2 * VEC>(acc, shm, vch, t.lane, t.lanes);
@@ -363,8 +373,12 @@ __global__ void __launch_bounds__(256) sum_stats_kernel(SumArgs a, int up2x, int
     __shared__ double sh[256];
     const ChanThread t = chan_thread<VEC>(cp, vch);
     double acc[2 * VEC];
+    float fs[VEC], fq[VEC];
+    int pending = 0;
 #pragma unroll
     for (int j = 0; j < 2 * VEC; ++j) acc[j] = 0.0;
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) { fs[j] = 0.f; fq[j] = 0.f; }
     if (t.active) {
         for (int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane; p < pixels; p += (int64_t)gridDim.x * t.lanes) {
             int64_t p0 = p;
@@ -385,14 +399,21 @@ __global__ void __launch_bounds__(256) sum_stats_kernel(SumArgs a, int up2x, int
             }
             Vec<T>::store(s + p * lds + t.c0, v);
             // statistics of the value as stored (bf16 rounding included), so that apply/backward,
-            // which re-read s, see the same numbers
+            // which re-read s, see the same numbers; fp32 over 4 pixels, then one conversion to double
 #pragma unroll
             for (int j = 0; j < VEC; ++j) {
-                const double w = (double)to_float(from_float<T>(v[j]));
-                acc[j] += w;
-                acc[VEC + j] += w * w;
+                const float w = to_float(from_float<T>(v[j]));
+                fs[j] += w;
+                fq[j] = fmaf(w, w, fq[j]);
+            }
+            if (++pending == 4) {
+#pragma unroll
+                for (int j = 0; j < VEC; ++j) { acc[j] += (double)fs[j]; acc[VEC + j] += (double)fq[j]; fs[j] = 0.f; fq[j] = 0.f; }
+                pending = 0;
             }
         }
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) { acc[j] += (double)fs[j]; acc[VEC + j] += (double)fq[j]; }
     }
     lane_reduce<2 * VEC>(acc, sh, vch, t.lane, t.lanes);
     if (t.active && t.lane == 0 && partials) {
