@@ -247,23 +247,33 @@ def main():
     def e2e_step():
         sx.copy_(xh, non_blocking=True)
         st_.copy_(th, non_blocking=True)
-        return float(run_step())
+        return float(run_step().detach())
     e2e_step()
     ms_e2e = timed(e2e_step, args.steps)
 
     # profiled pass: per-launch CUDA events on the launching stream, algorithmic bytes/flops per launch
     prof = {}
-    if rank == 0 and args.profile_steps > 0:
-        _lib.lib.msx_profile_enable(1)
+    if args.profile_steps > 0:                                   # every rank steps (collectives), rank 0 records
+        if rank == 0:
+            _lib.lib.msx_profile_enable(1)
         for _ in range(args.profile_steps):
-            step(sx, st_)
-        prof = _lib.profile_collect()
-        _lib.lib.msx_profile_enable(0)
+            step(sx, st_).detach()
+        if rank == 0:
+            prof = _lib.profile_collect()
+            _lib.lib.msx_profile_enable(0)
     barrier()
 
-    if rank != 0:
+    def leave():
+        # ranks leave through os._exit after a final barrier: tearing the NCCL communicator down while CUDA
+        # graphs that captured its collectives are still alive can block in ncclCommDestroy
         if world > 1:
-            dist.destroy_process_group()
+            dist.barrier()
+            torch.cuda.synchronize()
+            sys.stdout.flush()
+            os._exit(0)
+
+    if rank != 0:
+        leave()
         return
     pk = peaks()
     imgs = B * world * args.steps
@@ -308,8 +318,7 @@ def main():
         'kernels': kernels,
     }
     print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
+    leave()
 
 
 if __name__ == '__main__':
