@@ -32,11 +32,20 @@ constexpr int kHaloThreads = 320;      // TMA warp + MMA warp + 2 x 4 epilogue w
 constexpr int kMaxStages = 8;
 constexpr uint32_t kSmemBudget = 200 * 1024;
 
+constexpr int kTapMax = 16;
+struct TapTable {          // one entry per (source phase, shift, weight tap) the pass visits
+    int n;
+    signed char map[kTapMax], dx[kTapMax], dy[kTapMax], wtap[kTapMax];
+};
+struct PhaseMaps { CUtensorMap m[4]; };   // source seen through up to 4 stride-2 phase views
+
 struct TcParams {
-    int N, H, W;          // destination == source spatial size (stride 1)
+    int N, H, W;          // tile-grid domain: the destination image, or one stride-2 phase of it
+    int Hd, Wd;           // full destination image size
+    int dmul, da, db;     // destination pixel of grid point (y, x) is (y*dmul + da, x*dmul + db)
     int tw, th, tiles_x, tiles_y;
     int n_tiles, BN;      // tiling of the output-channel axis
-    int kh, kw, mul_t, off_h, off_w;
+    TapTable taps;
     int kchunks, chunk;   // K chunks per tap, channels per chunk (64 or 32)
     int Kp;               // padded reduction channels (multiple of 8)
     int Nc, ncp, ldd;     // output channels, round_up(Nc, 8), destination pixel stride
@@ -127,8 +136,8 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t row_bytes
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
-conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-               bf16* __restrict__ dst, const float* __restrict__ bias, const TcParams p) {
+conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CUtensorMap tmB,
+               bf16* __restrict__ dst, const float* __restrict__ bias, const __grid_constant__ TcParams p) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;             // swizzle atoms need 1024 B alignment
     const uint32_t sA = base, sB = base + p.stages * p.a_stage;
@@ -153,7 +162,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     uint32_t tmem_base;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
-    const int taps = p.kh * p.kw;
+    const int taps = p.taps.n;
     const int tiles_per_img = p.tiles_x * p.tiles_y;
     const int m_tiles = tiles_per_img * p.N;
 
@@ -168,13 +177,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 const int ty = rem / p.tiles_x;
                 const int y0 = ty * p.th, x0 = (rem - ty * p.tiles_x) * p.tw;
                 for (int tap = 0; tap < taps; ++tap) {
-                    const int r = tap / p.kw, s = tap % p.kw;
-                    const int sy = y0 + r * p.mul_t + p.off_h, sx = x0 + s * p.mul_t + p.off_w;
+                    const int sy = y0 + p.taps.dy[tap], sx = x0 + p.taps.dx[tap];
+                    const CUtensorMap* mapA = &tmA.m[p.taps.map[tap]];
+                    const int wtap = p.taps.wtap[tap];
                     for (int kc = 0; kc < p.kchunks; ++kc) {
                         mbar_wait(bar_empty + 8 * stage, phase ^ 1);
                         mbar_expect_tx(bar_full + 8 * stage, p.a_bytes + p.b_bytes);
-                        tma_load_4d(sA + stage * p.a_stage, &tmA, bar_full + 8 * stage, kc * p.chunk, sx, sy, img);
-                        tma_load_3d(sB + stage * p.b_stage, &tmB, bar_full + 8 * stage, kc * p.chunk, nt * p.BN, tap);
+                        tma_load_4d(sA + stage * p.a_stage, mapA, bar_full + 8 * stage, kc * p.chunk, sx, sy, img);
+                        tma_load_3d(sB + stage * p.b_stage, &tmB, bar_full + 8 * stage, kc * p.chunk, nt * p.BN, wtap);
                         if (++stage == p.stages) { stage = 0; phase ^= 1; }
                     }
                 }
@@ -231,7 +241,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const bool valid = dy < p.th && y < p.H && x < p.W;
             const int n0 = nt * p.BN;
             const int ncols = min(p.BN, p.ncp - n0);                         // multiple of 8
-            bf16* out = dst + ((int64_t)(img * p.H + y) * p.W + x) * p.ldd + n0;
+            bf16* out = dst + ((int64_t)(img * p.Hd + y * p.dmul + p.da) * p.Wd + x * p.dmul + p.db) * p.ldd + n0;
             mbar_wait(bar_tfull + 8 * as, (it >> 1) & 1);
             tc_fence_after();
             const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + as * p.BN;
@@ -513,6 +523,7 @@ struct WgParams {
     uint32_t a_stage, b_stage;
     int64_t pix_tiles;
     int halo, Wh, Hh;                 // halo mode: one x patch (+halo) per pixel tile serves every tap
+    TapTable taps;                    // streaming mode: per tap, which phase view of the big side and which shift
 };
 
 // MN-major operand descriptor: MN groups `lbo` bytes apart, 8-row (K) groups 8*row_bytes apart.
@@ -523,8 +534,8 @@ __device__ __forceinline__ uint64_t umma_desc_mn(uint32_t saddr, uint32_t row_by
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
-wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CUtensorMap tmG,
-                float* __restrict__ partial, const WgParams p) {
+wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ PhaseMaps tmG,
+                float* __restrict__ partial, const __grid_constant__ WgParams p) {
     extern __shared__ uint8_t smem_raw[];
     constexpr int SA = 2;
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -580,16 +591,17 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
                 if (p.halo) {
                     mbar_wait(barB_empty + 8 * stB, phB ^ 1);
                     mbar_expect_tx(barB_full + 8 * stB, (uint32_t)p.Hh * p.Wh * rbB);
-                    tma_load_4d(sB + stB * p.b_stage, &tmG, barB_full + 8 * stB, b0, x0 - p.pad_w, y0 - p.pad_h, img);
+                    tma_load_4d(sB + stB * p.b_stage, &tmG.m[0], barB_full + 8 * stB, b0, x0 - p.pad_w, y0 - p.pad_h, img);
                     if (++stB == p.stagesB) { stB = 0; phB ^= 1; }
                 } else {
                     for (int k = 0; k < ntap; ++k) {
-                        const int tap = tap0 + k, r = tap / p.kw, s = tap % p.kw;
+                        const int tap = tap0 + k;
+                        const CUtensorMap* mapG = &tmG.m[p.taps.map[tap]];
                         mbar_wait(barB_empty + 8 * stB, phB ^ 1);
                         mbar_expect_tx(barB_full + 8 * stB, p.groupsB * 128 * rbB);
                         for (int g = 0; g < p.groupsB; ++g)
-                            tma_load_4d(sB + stB * p.b_stage + g * 128 * rbB, &tmG, barB_full + 8 * stB, b0 + g * p.chunkB,
-                                        x0 + s * p.dil - p.pad_w, y0 + r * p.dil - p.pad_h, img);
+                            tma_load_4d(sB + stB * p.b_stage + g * 128 * rbB, mapG, barB_full + 8 * stB, b0 + g * p.chunkB,
+                                        x0 + p.taps.dx[tap], y0 + p.taps.dy[tap], img);
                         if (++stB == p.stagesB) { stB = 0; phB ^= 1; }
                     }
                 }
@@ -715,8 +727,10 @@ void pick_tile_pow2(int H, int W, int& tw, int& th) {
 }
 
 void wgrad_plan(const msx_conv_desc* d, WgParams& p) {
-    const int A = d->cout, B = d->cin;
-    p.N = d->n; p.H = d->h; p.W = d->w;
+    // "small" side = the F-form destination (dy for Conv2d, x for ConvTranspose2d), "big" = the gathered side
+    const int A = d->transposed ? d->cin : d->cout, B = d->transposed ? d->cout : d->cin;
+    p.N = d->n;
+    p.H = d->transposed ? d->h : d->oh; p.W = d->transposed ? d->w : d->ow;
     p.kh = d->kh; p.kw = d->kw; p.dil = d->dil; p.pad_h = d->pad_h; p.pad_w = d->pad_w;
     pick_tile_pow2(p.H, p.W, p.tw, p.th);
     p.tiles_x = (p.W + p.tw - 1) / p.tw;
@@ -750,7 +764,7 @@ void wgrad_plan(const msx_conv_desc* d, WgParams& p) {
         const int span_w = (p.kw - 1) * p.dil, span_h = (p.kh - 1) * p.dil;
         const int tx = (p.W + 7) / 8, ty = (p.H + 15) / 16;
         const double eff = (double)p.W * p.H / ((double)tx * ty * 128.0);
-        if (halo_mode() && p.Bp <= 64 && p.b_tiles == 1 && taps >= 2 && taps <= 9 && 8 + span_w <= 16 && eff >= 0.75) {
+        if (halo_mode() && d->stride == 1 && !d->transposed && p.Bp <= 64 && p.b_tiles == 1 && taps >= 2 && taps <= 9 && 8 + span_w <= 16 && eff >= 0.75) {
             p.halo = 1;
             p.tw = 8; p.th = 16; p.tiles_x = tx; p.tiles_y = ty;
             p.pix_tiles = (int64_t)tx * ty * p.N;
@@ -769,9 +783,14 @@ void wgrad_plan(const msx_conv_desc* d, WgParams& p) {
 
 bool conv_tc_supported(const msx_conv_desc* d, bool fwd_pass) {
     (void)fwd_pass;
-    if (d->dtype != MSX_BF16 || d->transposed || d->stride != 1) return false;
-    if (d->oh != d->h || d->ow != d->w) return false;          // 'same' geometry (all stride-1 convs of the reference)
-    return encode_fn() != nullptr;
+    if (d->dtype != MSX_BF16 || encode_fn() == nullptr) return false;
+    if (d->kh * d->kw > kTapMax) return false;
+    if (d->stride == 1) return !d->transposed && d->oh == d->h && d->ow == d->w;      // 'same' convs of the reference
+    if (d->stride != 2 || d->dil != 1 || d->kh < 2 || d->kw < 2) return false;
+    // stride 2 (Conv2d 3x3 p1 / 2x2 p0, ConvTranspose2d 3x3 p1 op1): fine side even and exactly twice the coarse side
+    const int fh = d->transposed ? d->oh : d->h, fw = d->transposed ? d->ow : d->w;
+    const int ch = d->transposed ? d->h : d->oh, cw = d->transposed ? d->w : d->ow;
+    return fh % 2 == 0 && fw % 2 == 0 && fh == 2 * ch && fw == 2 * cw;
 }
 
 size_t conv_wgrad_tc_ws_bytes(const msx_conv_desc* d) {
@@ -783,24 +802,31 @@ size_t conv_wgrad_tc_ws_bytes(const msx_conv_desc* d) {
 int wgrad_reduce_launch(const float* partial, int splits, int taps, int A, int B, int Apad, int Bpad, float* dw, cudaStream_t st);
 
 // x: module input (big side, cin), dy: gradient of the module output (small side, cout); dw: [cout][cin][kh][kw] fp32.
+static int make_src_maps(PhaseMaps& maps, const void* src, int Kp, int N, int Hs, int Ws, int lds, int stride,
+                         int chunk, int tw, int th, unsigned used_mask);
+static unsigned build_taps(const msx_conv_desc* d, bool f_form, int pa, int pb, TapTable& t);
+
 int conv_wgrad_tc(const msx_conv_desc* d, const void* x, const void* dy, float* dw, void* ws, size_t ws_bytes, cudaStream_t st) {
     WgParams p;
     wgrad_plan(d, p);
     const size_t need = conv_wgrad_tc_ws_bytes(d);
     if (ws_bytes < need) return set_error(MSX_ERR_WORKSPACE, "conv wgrad (tcgen05): workspace %zu < %zu", ws_bytes, need);
-    CUtensorMap tmS, tmG;
+    const void* small = d->transposed ? x : dy;
+    const void* big = d->transposed ? dy : x;
+    const int lda = d->transposed ? d->ldx : d->ldy, ldb = d->transposed ? d->ldy : d->ldx;
+    const int Hb = d->transposed ? d->oh : d->h, Wb = d->transposed ? d->ow : d->w;
+    const int A = d->transposed ? d->cin : d->cout, B = d->transposed ? d->cout : d->cin;
+    const unsigned mask = build_taps(d, true, 0, 0, p.taps);       // big = small*stride + r*dil - pad
+    if (mask == 0 || p.taps.n != p.kh * p.kw) return set_error(MSX_ERR_UNSUPPORTED, "conv wgrad (tcgen05): too many taps");
+    CUtensorMap tmS;
+    PhaseMaps tmG;
     {
         cuuint64_t dims[4] = {(cuuint64_t)p.Ap, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.N};
-        cuuint64_t strides[3] = {(cuuint64_t)d->ldy * 2, (cuuint64_t)d->ldy * 2 * p.W, (cuuint64_t)d->ldy * 2 * p.W * p.H};
+        cuuint64_t strides[3] = {(cuuint64_t)lda * 2, (cuuint64_t)lda * 2 * p.W, (cuuint64_t)lda * 2 * p.W * p.H};
         cuuint32_t box[4] = {(cuuint32_t)p.chunkA, (cuuint32_t)p.tw, (cuuint32_t)p.th, 1};
-        MSX_TRY(make_map(&tmS, 4, dy, dims, strides, box, p.chunkA == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B));
+        MSX_TRY(make_map(&tmS, 4, small, dims, strides, box, p.chunkA == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B));
     }
-    {
-        cuuint64_t dims[4] = {(cuuint64_t)p.Bp, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.N};
-        cuuint64_t strides[3] = {(cuuint64_t)d->ldx * 2, (cuuint64_t)d->ldx * 2 * p.W, (cuuint64_t)d->ldx * 2 * p.W * p.H};
-        cuuint32_t box[4] = {(cuuint32_t)p.chunkB, (cuuint32_t)(p.halo ? p.Wh : p.tw), (cuuint32_t)(p.halo ? p.Hh : p.th), 1};
-        MSX_TRY(make_map(&tmG, 4, x, dims, strides, box, p.chunkB == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B));
-    }
+    MSX_TRY(make_src_maps(tmG, big, p.Bp, p.N, Hb, Wb, ldb, d->stride, p.chunkB, p.halo ? p.Wh : p.tw, p.halo ? p.Hh : p.th, mask));
     static bool attr_set = false;
     if (!attr_set) {
         MSX_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
@@ -809,13 +835,13 @@ int conv_wgrad_tc(const msx_conv_desc* d, const void* x, const void* dy, float* 
     const size_t smem = 1024 + 2 * (size_t)p.a_stage + (size_t)p.stagesB * p.b_stage + 32 + 16 * kMaxStages + 64;
     const int grid = p.a_tiles * p.b_tiles * p.tap_groups * p.splits;
     const int taps = p.kh * p.kw;
-    const double M = (double)p.N * p.H * p.W;
+    const double Ms = (double)p.N * p.H * p.W, Mb = (double)p.N * Hb * Wb;
     {
-        ProfScope ps__(K_WGRAD_TC, st, M * (d->cin + d->cout) * 2.0, 2.0 * M * d->cin * d->cout * taps);
+        ProfScope ps__(K_WGRAD_TC, st, (Ms * A + Mb * B) * 2.0, 2.0 * Ms * A * B * taps);
         wgrad_tc_kernel<<<grid, kThreads, smem, st>>>(tmS, tmG, static_cast<float*>(ws), p);
     }
     MSX_LAUNCH_CHECK();
-    return wgrad_reduce_launch(static_cast<const float*>(ws), p.splits, taps, d->cout, d->cin, p.Apad, p.Bpad, dw, st);
+    return wgrad_reduce_launch(static_cast<const float*>(ws), p.splits, taps, A, B, p.Apad, p.Bpad, dw, st);
 }
 
 static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
@@ -884,18 +910,77 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     return MSX_OK;
 }
 
+// Source activation seen through tensor maps: one map for stride 1, or the four stride-2 phase views
+// (phase (py, px) holds pixels (2y + py, 2x + px)); a strided convolution then reads every tap as a plain
+// shifted box of one phase, so zero padding stays TMA out-of-bounds fill.
+static int make_src_maps(PhaseMaps& maps, const void* src, int Kp, int N, int Hs, int Ws, int lds, int stride,
+                         int chunk, int tw, int th, unsigned used_mask) {
+    const CUtensorMapSwizzle sw = chunk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+    cuuint32_t box[4] = {(cuuint32_t)chunk, (cuuint32_t)tw, (cuuint32_t)th, 1};
+    if (stride == 1) {
+        cuuint64_t dims[4] = {(cuuint64_t)Kp, (cuuint64_t)Ws, (cuuint64_t)Hs, (cuuint64_t)N};
+        cuuint64_t strides[3] = {(cuuint64_t)lds * 2, (cuuint64_t)lds * 2 * Ws, (cuuint64_t)lds * 2 * Ws * Hs};
+        MSX_TRY(make_map(&maps.m[0], 4, src, dims, strides, box, sw));
+        maps.m[1] = maps.m[2] = maps.m[3] = maps.m[0];
+        return MSX_OK;
+    }
+    int first = -1;
+    for (int ph = 0; ph < 4; ++ph) {
+        if (!(used_mask & (1u << ph))) continue;
+        const int py = ph >> 1, px = ph & 1;
+        const char* base = static_cast<const char*>(src) + ((size_t)py * Ws + px) * lds * 2;
+        cuuint64_t dims[4] = {(cuuint64_t)Kp, (cuuint64_t)((Ws - px + 1) / 2), (cuuint64_t)((Hs - py + 1) / 2), (cuuint64_t)N};
+        cuuint64_t strides[3] = {(cuuint64_t)lds * 4, (cuuint64_t)lds * 4 * Ws, (cuuint64_t)lds * 2 * Ws * Hs};
+        MSX_TRY(make_map(&maps.m[ph], 4, base, dims, strides, box, sw));
+        if (first < 0) first = ph;
+    }
+    for (int ph = 0; ph < 4; ++ph)
+        if (!(used_mask & (1u << ph))) maps.m[ph] = maps.m[first];
+    return MSX_OK;
+}
+
+static inline int mod2(int v) { return ((v % 2) + 2) % 2; }
+
+// Tap table of one gather launch.  f_form: src = dst*stride + r*dil - pad.  Otherwise (b-form)
+// src = (dst + pad - r*dil) / stride, and for stride 2 the launch covers destination phase (pa, pb).
+static unsigned build_taps(const msx_conv_desc* d, bool f_form, int pa, int pb, TapTable& t) {
+    unsigned mask = 0;
+    t.n = 0;
+    for (int r = 0; r < d->kh; ++r)
+        for (int s = 0; s < d->kw; ++s) {
+            int map = 0, dy, dx;
+            if (f_form) {
+                const int vy = r * d->dil - d->pad_h, vx = s * d->dil - d->pad_w;
+                if (d->stride == 1) { dy = vy; dx = vx; }
+                else { const int py = mod2(vy), px = mod2(vx); map = py * 2 + px; dy = (vy - py) / 2; dx = (vx - px) / 2; }
+            } else {
+                const int vy = pa + d->pad_h - r * d->dil, vx = pb + d->pad_w - s * d->dil;
+                if (d->stride == 1) { dy = vy; dx = vx; }
+                else { if (mod2(vy) || mod2(vx)) continue; dy = (vy - mod2(vy)) / 2; dx = (vx - mod2(vx)) / 2; }
+            }
+            if (t.n >= kTapMax) return 0;
+            t.map[t.n] = (signed char)map; t.dy[t.n] = (signed char)dy; t.dx[t.n] = (signed char)dx;
+            t.wtap[t.n] = (signed char)(r * d->kw + s);
+            mask |= 1u << map;
+            ++t.n;
+        }
+    return mask;
+}
+
 int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
                    void* dst, cudaStream_t st) {
-    bool used = false;
-    MSX_TRY(conv_gather_tc_halo(d, fwd_pass, src, packed, bias, dst, st, &used));
-    if (used) return MSX_OK;
+    const bool f_form = d->transposed ? !fwd_pass : fwd_pass;
+    if (d->stride == 1 && !d->transposed) {
+        bool used = false;
+        MSX_TRY(conv_gather_tc_halo(d, fwd_pass, src, packed, bias, dst, st, &used));
+        if (used) return MSX_OK;
+    }
     TcParams p;
     const int K = fwd_pass ? d->cin : d->cout, Nc = fwd_pass ? d->cout : d->cin;
     const int lds = fwd_pass ? d->ldx : d->ldy;
-    p.N = d->n; p.H = d->h; p.W = d->w;
-    p.kh = d->kh; p.kw = d->kw;
-    if (fwd_pass) { p.mul_t = d->dil; p.off_h = -d->pad_h; p.off_w = -d->pad_w; }
-    else          { p.mul_t = -d->dil; p.off_h = d->pad_h; p.off_w = d->pad_w; }
+    const int Hs = fwd_pass ? d->h : d->oh, Ws = fwd_pass ? d->w : d->ow;
+    p.Hd = fwd_pass ? d->oh : d->h; p.Wd = fwd_pass ? d->ow : d->w;
+    p.N = d->n;
     p.Kp = round_up(K, 8);
     p.Nc = Nc; p.ncp = round_up(Nc, 8); p.ldd = fwd_pass ? d->ldy : d->ldx;
     const int Np = round_up(Nc, 16);
@@ -903,12 +988,7 @@ int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const
     p.BN = round_up((Np + p.n_tiles - 1) / p.n_tiles, 16);
     p.chunk = p.Kp <= 32 ? 32 : 64;
     p.kchunks = (p.Kp + p.chunk - 1) / p.chunk;
-    pick_tile(p.H, p.W, p.tw, p.th);
-    p.tiles_x = (p.W + p.tw - 1) / p.tw;
-    p.tiles_y = (p.H + p.th - 1) / p.th;
-    p.total_tiles = p.tiles_x * p.tiles_y * p.N * p.n_tiles;
     const uint32_t row_bytes = p.chunk * 2;
-    p.a_bytes = (uint32_t)p.tw * p.th * row_bytes;
     p.b_bytes = (uint32_t)p.BN * row_bytes;
     p.a_stage = 128 * row_bytes;                                 // full 128-row operand tile
     p.b_stage = (p.b_bytes + 1023u) & ~1023u;
@@ -918,17 +998,10 @@ int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const
     while (cols < 2 * p.BN) cols <<= 1;
     p.tmem_cols = cols;
     const size_t smem = 1024 + (size_t)p.stages * (p.a_stage + p.b_stage) + 16 * kMaxStages + 64;
-
     const CUtensorMapSwizzle sw = p.chunk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
-    CUtensorMap tmA, tmB;
+    CUtensorMap tmB;
     {
-        cuuint64_t dims[4] = {(cuuint64_t)p.Kp, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.N};
-        cuuint64_t strides[3] = {(cuuint64_t)lds * 2, (cuuint64_t)lds * 2 * p.W, (cuuint64_t)lds * 2 * p.W * p.H};
-        cuuint32_t box[4] = {(cuuint32_t)p.chunk, (cuuint32_t)p.tw, (cuuint32_t)p.th, 1};
-        MSX_TRY(make_map(&tmA, 4, src, dims, strides, box, sw));
-    }
-    {
-        cuuint64_t dims[3] = {(cuuint64_t)p.Kp, (cuuint64_t)Np, (cuuint64_t)(p.kh * p.kw)};
+        cuuint64_t dims[3] = {(cuuint64_t)p.Kp, (cuuint64_t)Np, (cuuint64_t)(d->kh * d->kw)};
         cuuint64_t strides[2] = {(cuuint64_t)p.Kp * 2, (cuuint64_t)p.Kp * 2 * Np};
         cuuint32_t box[3] = {(cuuint32_t)p.chunk, (cuuint32_t)p.BN, 1};
         MSX_TRY(make_map(&tmB, 3, packed, dims, strides, box, sw));
@@ -938,13 +1011,28 @@ int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const
         MSX_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_set = true;
     }
-    const int grid = p.total_tiles < kNumSMs ? p.total_tiles : kNumSMs;
-    const double M = (double)p.N * p.H * p.W;
-    {
-        ProfScope ps__(K_CONV_TC, st, M * (K + Nc) * 2.0, 2.0 * M * Nc * K * p.kh * p.kw);
-        conv_tc_kernel<<<grid, kThreads, smem, st>>>(tmA, tmB, static_cast<bf16*>(dst), bias, p);
+    const int nphase = (!f_form && d->stride == 2) ? 4 : 1;      // b-form stride 2: one launch per destination phase
+    for (int ph = 0; ph < nphase; ++ph) {
+        const int pa = ph >> 1, pb = ph & 1;
+        const unsigned mask = build_taps(d, f_form, pa, pb, p.taps);
+        if (p.taps.n == 0 || mask == 0) return set_error(MSX_ERR_UNSUPPORTED, "conv (tcgen05): empty tap set for this geometry");
+        if (nphase == 4) { p.dmul = 2; p.da = pa; p.db = pb; p.H = (p.Hd - pa + 1) / 2; p.W = (p.Wd - pb + 1) / 2; }
+        else             { p.dmul = 1; p.da = 0; p.db = 0; p.H = p.Hd; p.W = p.Wd; }
+        pick_tile(p.H, p.W, p.tw, p.th);
+        p.tiles_x = (p.W + p.tw - 1) / p.tw;
+        p.tiles_y = (p.H + p.th - 1) / p.th;
+        p.total_tiles = p.tiles_x * p.tiles_y * p.N * p.n_tiles;
+        p.a_bytes = (uint32_t)p.tw * p.th * row_bytes;
+        PhaseMaps maps;
+        MSX_TRY(make_src_maps(maps, src, p.Kp, p.N, Hs, Ws, lds, f_form ? d->stride : 1, p.chunk, p.tw, p.th, mask));
+        const int grid = p.total_tiles < kNumSMs ? p.total_tiles : kNumSMs;
+        const double Mg = (double)p.N * p.H * p.W, Ms = (double)p.N * Hs * Ws / nphase;
+        {
+            ProfScope ps__(K_CONV_TC, st, (Mg * Nc + Ms * K) * 2.0, 2.0 * Mg * Nc * K * p.taps.n);
+            conv_tc_kernel<<<grid, kThreads, smem, st>>>(maps, tmB, static_cast<bf16*>(dst), bias, p);
+        }
+        MSX_LAUNCH_CHECK();
     }
-    MSX_LAUNCH_CHECK();
     note_conv_engine(MSX_ENGINE_TCGEN05);
     return MSX_OK;
 }

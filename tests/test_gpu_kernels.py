@@ -111,6 +111,47 @@ def test_conv_tcgen05_fwd_dgrad(case):
     assert e_y < 6e-3 and e_dx < 6e-3 and e_dw < 6e-3          # output rounding to bf16: ~2^-9 per element
 
 
+S2_CASES = [
+    # cin, cout, k, pad, H, W, n, transposed     (stride 2 through the four phase views of the fine side)
+    (34, 68, 3, 1, 16, 16, 2, False),
+    (3, 34, 2, 0, 32, 32, 2, False),
+    (17, 34, 3, 1, 32, 48, 2, False),
+    (136, 272, 3, 1, 22, 22, 2, False),
+    (272, 544, 2, 0, 22, 22, 1, False),
+    (64, 32, 3, 1, 20, 20, 2, True),         # ConvTranspose2d(3, s2, p1, op1): 20 -> 40
+    (512, 256, 3, 1, 11, 11, 1, True),
+    (17, 24, 3, 1, 12, 20, 2, True),
+]
+
+
+@pytest.mark.parametrize('case', S2_CASES)
+def test_conv_tcgen05_stride2_and_transposed(case):
+    """Stride-2 Conv2d (3x3 p1, 2x2 p0) and ConvTranspose2d(3, 2, 1, 1): fprop, dgrad and wgrad on tcgen05."""
+    ops = _ops()
+    from medical_segmentation_pytorch_b200 import _lib
+    cin, cout, k, pad, H, W, n, tr = case
+    torch.manual_seed(sum(case[:7]))
+    x = torch.randn(n, cin, H, W).bfloat16().float()
+    wshape = (cin, cout, k, k) if tr else (cout, cin, k, k)
+    w = (torch.randn(wshape) / (cin * k * k) ** 0.5).bfloat16().float()
+    xd, wd = x.double().requires_grad_(True), w.double().requires_grad_(True)
+    yref = F.conv_transpose2d(xd, wd, None, 2, pad, 1) if tr else F.conv2d(xd, wd, None, 2, pad)
+    dy = torch.randn(yref.shape).bfloat16().float()
+    yref.backward(dy.double())
+    g = ops.ConvGeom(cin, cout, k, k, 2, 1, pad, pad, transposed=tr, out_pad=1 if tr else 0, engine=2)
+    a = to_act(x, torch.bfloat16, requires_grad=True)
+    wp = torch.nn.Parameter(w.to(DEV))
+    y = ops.Conv2dFn.apply(a.t, wp, g)
+    assert _lib.lib.msx_last_conv_engine() == 2
+    assert tuple(y.shape[1:3]) == tuple(yref.shape[2:])
+    assert float(y.detach()[..., cout:].float().abs().sum()) == 0.0
+    y.backward(to_act(dy, torch.bfloat16).t)
+    torch.cuda.synchronize()
+    e_y, e_dx, e_dw = rel(from_act(y, cout), yref), rel(from_act(a.t.grad, cin), xd.grad), rel(wp.grad, wd.grad)
+    print(f'tc-s2 {case}: y {e_y:.2e} dx {e_dx:.2e} dw {e_dw:.2e}')
+    assert e_y < 6e-3 and e_dx < 6e-3 and e_dw < 6e-3
+
+
 @pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
 def test_conv_transpose_bn_relu(dtype):
     """DeConvBNAct: ConvTranspose2d(3, s2, p1, op1, bias) -> BN(train) -> ReLU, forward and all gradients."""
