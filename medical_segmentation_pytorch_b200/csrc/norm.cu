@@ -42,22 +42,23 @@ __device__ inline ChanThread chan_thread(int cp, int vch) {
 }
 
 // Sum v[j] over the pixel lanes of the CTA (threads that share threadIdx.x % vch); result valid
-// in lane 0.  sh: 256 doubles.
+// in lane 0.  sh: NV * 256 doubles; all NV values go through ONE tree (log2(lanes) barriers in total).
 template <int NV>
 __device__ inline void lane_reduce(double (&v)[NV], double* sh, int vch, int lane, int lanes) {
     int p2 = 1;
     while (p2 < lanes) p2 <<= 1;
 #pragma unroll
-    for (int j = 0; j < NV; ++j) {
-        sh[threadIdx.x] = v[j];
-        __syncthreads();
-        for (int off = p2 >> 1; off > 0; off >>= 1) {
-            if (lane < off && lane + off < lanes) sh[threadIdx.x] += sh[threadIdx.x + off * vch];
-            __syncthreads();
+    for (int j = 0; j < NV; ++j) sh[j * 256 + threadIdx.x] = v[j];
+    __syncthreads();
+    for (int off = p2 >> 1; off > 0; off >>= 1) {
+        if (lane < off && lane + off < lanes) {
+#pragma unroll
+            for (int j = 0; j < NV; ++j) sh[j * 256 + threadIdx.x] += sh[j * 256 + threadIdx.x + off * vch];
         }
-        v[j] = sh[threadIdx.x];
         __syncthreads();
     }
+#pragma unroll
+    for (int j = 0; j < NV; ++j) v[j] = sh[j * 256 + threadIdx.x];
 }
 
 inline int reduce_grid(int64_t pixels, int lanes) {
@@ -78,7 +79,7 @@ template <typename T>
 __global__ void __launch_bounds__(256) bn_stats_kernel(const T* __restrict__ x, int ld, int64_t pixels, int cp, int vch,
                                                        double* __restrict__ partials) {
     constexpr int VEC = Vec<T>::N;
-    __shared__ double sh[256];
+    __shared__ double sh[2 * VEC * 256];
     const ChanThread t = chan_thread<VEC>(cp, vch);
     double acc[2 * VEC];
 #pragma unroll
@@ -231,7 +232,7 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const T* __restrict_
                                                             const float* __restrict__ gamma, const float* __restrict__ beta,
                                                             int relu, double* __restrict__ partials) {
     constexpr int VEC = Vec<T>::N;
-    __shared__ double shm[256];
+    __shared__ double shm[2 * VEC * 256];
     const ChanThread t = chan_thread<VEC>(cp, vch);
     float mu[VEC], is[VEC], ga[VEC], be[VEC];
     double acc[2 * VEC];
@@ -366,11 +367,11 @@ struct SumArgs {
     int ld[8];
     int n;
 };
-template <typename T>
+template <typename T, bool STATS>
 __global__ void __launch_bounds__(256) sum_stats_kernel(SumArgs a, int up2x, int H, int W, T* __restrict__ s, int lds,
                                                         int64_t pixels, int cp, int vch, double* __restrict__ partials) {
     constexpr int VEC = Vec<T>::N;
-    __shared__ double sh[256];
+    __shared__ double sh[STATS ? 2 * VEC * 256 : 1];
     const ChanThread t = chan_thread<VEC>(cp, vch);
     double acc[2 * VEC];
     float fs[VEC], fq[VEC];
@@ -391,13 +392,24 @@ __global__ void __launch_bounds__(256) sum_stats_kernel(SumArgs a, int up2x, int
             }
             float v[VEC];
             Vec<T>::load(static_cast<const T*>(a.x[0]) + p0 * a.ld[0] + t.c0, v);
-            for (int i = 1; i < a.n; ++i) {
-                float u[VEC];
-                Vec<T>::load(static_cast<const T*>(a.x[i]) + p * a.ld[i] + t.c0, u);
+            // inputs in groups of four: four independent 16 B loads in flight, then the adds
 #pragma unroll
-                for (int j = 0; j < VEC; ++j) v[j] += u[j];
+            for (int i0 = 1; i0 < 8; i0 += 4) {
+                if (i0 < a.n) {
+                    float u[4][VEC];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        if (i0 + i < a.n) Vec<T>::load(static_cast<const T*>(a.x[i0 + i]) + p * a.ld[i0 + i] + t.c0, u[i]);
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        if (i0 + i < a.n) {
+#pragma unroll
+                            for (int j = 0; j < VEC; ++j) v[j] += u[i][j];
+                        }
+                }
             }
             Vec<T>::store(s + p * lds + t.c0, v);
+            if (!STATS) continue;
             // statistics of the value as stored (bf16 rounding included), so that apply/backward,
             // which re-read s, see the same numbers; fp32 over 4 pixels, then one conversion to double
 #pragma unroll
@@ -415,6 +427,7 @@ __global__ void __launch_bounds__(256) sum_stats_kernel(SumArgs a, int up2x, int
 #pragma unroll
         for (int j = 0; j < VEC; ++j) { acc[j] += (double)fs[j]; acc[VEC + j] += (double)fq[j]; }
     }
+    if (!STATS) return;
     lane_reduce<2 * VEC>(acc, sh, vch, t.lane, t.lanes);
     if (t.active && t.lane == 0 && partials) {
 #pragma unroll
@@ -690,7 +703,7 @@ int msx_sum_bn_act_fwd(int dtype, int n_in, const void* const* host_xs, const in
         MSX_DISPATCH_DTYPE(dtype, T, {
             const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
             nblk = reduce_grid(pixels, c.lanes);
-            { ProfScope ps__(K_SUM, st, (double)pixels * channels * (double)sizeof(T) * (n_in + 1.0), 0); sum_stats_kernel<T><<<dim3(nblk, c.nchunk), 256, 0, st>>>(a, up2x_first, h, w, static_cast<T*>(s), lds, pixels, c.cp, c.vch,
+            { ProfScope ps__(K_SUM, st, (double)pixels * channels * (double)sizeof(T) * (n_in + 1.0), 0); sum_stats_kernel<T, true><<<dim3(nblk, c.nchunk), 256, 0, st>>>(a, up2x_first, h, w, static_cast<T*>(s), lds, pixels, c.cp, c.vch,
                                                                      training ? partials : nullptr); }
         });
         MSX_LAUNCH_CHECK();
@@ -720,7 +733,7 @@ int msx_sum_n(int dtype, int n_in, const void* const* host_xs, const int32_t* ho
     }
     MSX_DISPATCH_DTYPE(dtype, T, {
         const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
-        { ProfScope ps__(K_SUM, as_stream(stream), (double)pixels * channels * (double)sizeof(T) * (n_in + 1.0), 0); sum_stats_kernel<T><<<dim3(stream_grid(pixels, c.lanes), c.nchunk), 256, 0, as_stream(stream)>>>(
+        { ProfScope ps__(K_SUM, as_stream(stream), (double)pixels * channels * (double)sizeof(T) * (n_in + 1.0), 0); sum_stats_kernel<T, false><<<dim3(stream_grid(pixels, c.lanes), c.nchunk), 256, 0, as_stream(stream)>>>(
             a, 0, 1, 1, static_cast<T*>(out), ldout, pixels, c.cp, c.vch, nullptr); }
     });
     MSX_LAUNCH_CHECK();

@@ -138,3 +138,64 @@ def test_unknown_names_raise_like_the_reference():
         msx.get_model(Cfg(model='unet', use_aux=True))
     with pytest.raises(NotImplementedError):
         msx.modules.Activation('swishh')
+
+
+def test_kd_training_step_and_eval_sweep():
+    """BASELINE config 5 shape of work (teacher logits -> KD + CE student step, then a Dice/mIoU sweep over
+    val_bs = 1 updates, core/seg_trainer.py:69-75,114-125) against the oracle on the same tensors."""
+    import medical_segmentation_pytorch_b200 as msx
+    from medical_segmentation_pytorch_b200.synth import synth_batch
+    from oracle import ref_loss, ref_metrics
+    torch.manual_seed(5)
+    cfg = Cfg(kd_loss_type='kl_div', kd_temperature=4.0)
+    student = msx.UNet(2, 3, 8).to(DEV).train()
+    x, t = synth_batch(2, 64, 64, seed=9, ignore_band=0.02)
+    x, t = x.to(DEV), t.to(DEV)
+    teacher_logits = torch.randn(2, 2, 64, 64, device=DEV) * 2          # stand-in for teacher(images).detach()
+    preds = student(x)
+    loss = msx.get_loss_fn(cfg, DEV)(preds, t)
+    loss_kd = msx.kd_loss_fn(cfg, preds, teacher_logits)
+    total = loss + 1.0 * loss_kd                                          # kd_loss_coefficient = 1.0 (base_config.py:103)
+    total.backward()
+    pd = preds.detach().double().cpu().requires_grad_(True)
+    ref = ref_loss.ce_loss(pd, t.cpu()) + ref_loss.kd_loss(pd, teacher_logits.double().cpu(), 'kl_div', 4.0)
+    ref.backward()
+    assert abs(float(total) - float(ref)) < 1e-5 * abs(float(ref))
+    assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in student.parameters())
+    # eval sweep: one image per update into both metrics
+    student.eval()
+    dice, iou = msx.get_seg_metrics(cfg, 'dice').to(DEV), msx.get_seg_metrics(cfg, 'iou').to(DEV)
+    cm_iou = np.zeros((2, 2), dtype=np.int64)
+    cm_dice = np.zeros((2, 2), dtype=np.int64)
+    t_clean = torch.where(t == 255, torch.zeros_like(t), t)
+    with torch.no_grad():
+        for i in range(2):
+            lg = student(x[i:i + 1])
+            iou.update(lg, t[i:i + 1])
+            dice.update(lg, t_clean[i:i + 1])
+            cm_iou += ref_metrics.confusion_matrix(lg.cpu().numpy(), t[i:i + 1].cpu().numpy(), 2, 255)
+            cm_dice += ref_metrics.confusion_matrix(lg.cpu().numpy(), t_clean[i:i + 1].cpu().numpy(), 2, None)
+    assert np.array_equal(iou.confmat.cpu().numpy(), cm_iou) and np.array_equal(dice.confmat.cpu().numpy(), cm_dice)
+    assert np.array_equal(iou.compute().cpu().numpy(), ref_metrics.iou_per_class(cm_iou))
+    assert float(dice.compute()) == float(ref_metrics.dice_macro(cm_dice))
+
+
+def test_unet32_fp32_config0_shape_runs_and_is_consistent():
+    """BASELINE config 0 geometry (UNet-32, 320x320, fp32) at batch 2: train step + eval; fp32 and bf16 paths of
+    the same weights agree on the loss to the stated bf16 tolerance, and every gradient is finite."""
+    import medical_segmentation_pytorch_b200 as msx
+    from medical_segmentation_pytorch_b200.synth import synth_batch
+    torch.manual_seed(1)
+    m = msx.UNet(2, 3, 32).to(DEV).train()
+    x, t = synth_batch(2, 320, 320, seed=1)
+    x, t = x.to(DEV), t.to(DEV)
+    lf = msx.get_loss_fn(Cfg(), DEV)
+    l32 = lf(m(x), t)
+    l32.backward()
+    g32 = [p.grad.clone() for p in m.parameters()]
+    with torch.autocast('cuda', dtype=torch.bfloat16):
+        l16 = lf(m(x), t)
+    assert abs(float(l16) - float(l32)) < 5e-2 * abs(float(l32))
+    assert all(torch.isfinite(g).all() for g in g32)
+    want = torch.nn.functional.cross_entropy(m(x).detach(), t, ignore_index=255)
+    assert torch.isfinite(want)
