@@ -206,14 +206,24 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(const T* __restrict__ s
 // dW[(a*B + b)*taps + tap] = sum_split partial[split][tap][a][b]   (reference OIHW / IOHW layout)
 __global__ void wgrad_reduce_kernel(const float* __restrict__ partial, int splits, int taps, int A, int B, int Apad, int Bpad,
                                     float* __restrict__ dw) {
+    // thread -> (tap, a, b) with b fastest: the (many) partial reads are coalesced, the single write scatters
     const int64_t total = (int64_t)A * B * taps;
+    const int64_t zstride = (int64_t)taps * Apad * Bpad;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int tap = (int)(i % taps);
-        const int64_t ab = i / taps;
-        const int b = (int)(ab % B), a = (int)(ab / B);
-        float s = 0.f;
-        for (int z = 0; z < splits; ++z) s += partial[((int64_t)(z * taps + tap) * Apad + a) * Bpad + b];
-        dw[i] = s;
+        const int b = (int)(i % B);
+        const int64_t q = i / B;
+        const int a = (int)(q % A), tap = (int)(q / A);
+        const float* src = partial + ((int64_t)tap * Apad + a) * Bpad + b;
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        int z = 0;
+        for (; z + 3 < splits; z += 4) {                          // four independent loads in flight, fixed order
+            s0 += src[(z + 0) * zstride];
+            s1 += src[(z + 1) * zstride];
+            s2 += src[(z + 2) * zstride];
+            s3 += src[(z + 3) * zstride];
+        }
+        for (; z < splits; ++z) s0 += src[z * zstride];
+        dw[((int64_t)a * B + b) * taps + tap] = (s0 + s1) + (s2 + s3);
     }
 }
 

@@ -30,6 +30,7 @@ namespace {
 constexpr int kThreads = 192;
 constexpr int kHaloThreads = 320;      // TMA warp + MMA warp + 2 x 4 epilogue warps
 constexpr int kMaxStages = 8;
+constexpr int kMaxAcc = 8;
 constexpr uint32_t kSmemBudget = 200 * 1024;
 
 constexpr int kTapMax = 16;
@@ -100,6 +101,32 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
         "}\n" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
 }
+// Same instruction with the descriptors assembled from 32-bit halves inside the asm block and a compile-time
+// accumulate flag: the single issuing thread is bound by its own instruction latency, so every integer
+// instruction per MMA counts (no "memory" clobber: asm volatile statements keep their mutual order).
+template <int ACC>
+__device__ __forceinline__ void umma_bf16_lh(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi, uint32_t idesc) {
+    asm volatile(
+        "{\n"
+        ".reg .b64 da, db;\n"
+        ".reg .pred p;\n"
+        "mov.b64 da, {%1, %2};\n"
+        "mov.b64 db, {%3, %4};\n"
+        "setp.ne.b32 p, %6, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n"
+        "}\n" ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "n"(ACC));
+}
+__device__ __forceinline__ void umma_bf16_lhr(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n"
+        ".reg .b64 da, db;\n"
+        ".reg .pred p;\n"
+        "mov.b64 da, {%1, %2};\n"
+        "mov.b64 db, {%3, %4};\n"
+        "setp.ne.b32 p, %6, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n"
+        "}\n" ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(acc));
+}
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
@@ -135,7 +162,7 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t row_bytes
     return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)((8 * row_bytes) >> 4) << 32) | (1ull << 46) | (layout << 61);
 }
 
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kHaloThreads, 1)
 conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CUtensorMap tmB,
                bf16* __restrict__ dst, const float* __restrict__ bias, const __grid_constant__ TcParams p) {
     extern __shared__ uint8_t smem_raw[];
@@ -196,44 +223,45 @@ conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CU
             // cute::UMMA::InstrDescriptor: c=F32 (bit 4), a=b=BF16 (bits 7, 10), K-major A and B, N>>3 @17, M>>4 @24
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((128u >> 4) << 24);
             const uint32_t row_bytes = p.chunk * 2;
-            const uint64_t hi = umma_desc(0, row_bytes);
-            const uint32_t a_lo0 = (sA & 0x3FFFFu) >> 4, b_lo0 = (sB & 0x3FFFFu) >> 4, a_step = p.a_stage >> 4, b_step = p.b_stage >> 4;
+            const uint32_t hi = (uint32_t)((8 * row_bytes) >> 4) | (1u << 14) | ((row_bytes == 128 ? 2u : 4u) << 29);
+            const uint32_t a_lo0 = ((sA & 0x3FFFFu) >> 4) | (1u << 16), b_lo0 = ((sB & 0x3FFFFu) >> 4) | (1u << 16);
+            const uint32_t a_step = p.a_stage >> 4, b_step = p.b_stage >> 4;
             const int full_ksteps = p.chunk / 16;
             const int last_ksteps = (p.Kp - (p.kchunks - 1) * p.chunk + 15) / 16;
+            const int kchunks = p.kchunks, stages = p.stages, BN = p.BN, total = p.total_tiles;
             int stage = 0;
             uint32_t phase = 0;
             int it = 0;
-            for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
+            for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
                 const int as = it & 1;
                 mbar_wait(bar_tempty + 8 * as, ((it >> 1) & 1) ^ 1);         // epilogue has drained this accumulator
                 tc_fence_after();
-                const uint32_t tmem_d = tmem_base + as * p.BN;
+                const uint32_t tmem_d = tmem_base + as * BN;
                 uint32_t acc = 0;
                 for (int tap = 0; tap < taps; ++tap) {
-                    for (int kc = 0; kc < p.kchunks; ++kc) {
+                    for (int kc = 0; kc < kchunks; ++kc) {
                         mbar_wait(bar_full + 8 * stage, phase);              // TMA bytes have landed
                         tc_fence_after();
-                        const int ksteps = kc == p.kchunks - 1 ? last_ksteps : full_ksteps;
-                        const uint64_t da = hi | (uint64_t)(a_lo0 + stage * a_step);
-                        const uint64_t db = hi | (uint64_t)(b_lo0 + stage * b_step);
+                        const int ksteps = kc == kchunks - 1 ? last_ksteps : full_ksteps;
+                        const uint32_t da = a_lo0 + stage * a_step, db = b_lo0 + stage * b_step;
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
-                            if (k < ksteps) { umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, acc); acc = 1; }   // +32 B per K=16 step
+                            if (k < ksteps) { umma_bf16_lhr(tmem_d, da + 2 * k, hi, db + 2 * k, hi, idesc, acc); acc = 1; }   // +32 B per K=16 step
                         umma_commit(bar_empty + 8 * stage);                  // frees the smem stage when the MMAs retire
-                        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                        if (++stage == stages) { stage = 0; phase ^= 1; }
                     }
                 }
                 umma_commit(bar_tfull + 8 * as);                             // accumulator complete -> epilogue
             }
         }
     } else {
-        // ================= epilogue (warps 2..5) =================
-        const int quad = warp & 3;                                           // TMEM lane quadrant this warp may read
+        // ================= epilogue: two groups of four warps, group g drains accumulator g =================
+        const int quad = warp & 3, grp = (warp - 2) >> 2;                    // TMEM lane quadrant this warp may read
         const int m = quad * 32 + lane;
         const int dy = m / p.tw, dx = m % p.tw;
-        int it = 0;
-        for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
-            const int as = it & 1;
+        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + grp * p.BN;
+        int it = grp;
+        for (int t = blockIdx.x + grp * gridDim.x; t < p.total_tiles; t += 2 * gridDim.x, it += 2) {
             const int nt = t / m_tiles, mt = t - nt * m_tiles;
             const int img = mt / tiles_per_img, rem = mt - img * tiles_per_img;
             const int ty = rem / p.tiles_x;
@@ -242,33 +270,46 @@ conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CU
             const int n0 = nt * p.BN;
             const int ncols = min(p.BN, p.ncp - n0);                         // multiple of 8
             bf16* out = dst + ((int64_t)(img * p.Hd + y * p.dmul + p.da) * p.Wd + x * p.dmul + p.db) * p.ldd + n0;
-            mbar_wait(bar_tfull + 8 * as, (it >> 1) & 1);
+            mbar_wait(bar_tfull + 8 * grp, (it >> 1) & 1);
             tc_fence_after();
-            const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + as * p.BN;
-            for (int c0 = 0; c0 < ncols; c0 += 16) {
+            int c0 = 0;
+            for (; c0 < ncols && ncols - c0 > 16; c0 += 32) {
+                uint32_t v[32];
+                tmem_ld32(taddr + c0, v);
+                tmem_ld_wait();
+                if (valid) {
+                    if (bias) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + (n0 + c0 + j < p.Nc ? bias[n0 + c0 + j] : 0.f));
+                    }
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+                        if (c0 + 8 * q < ncols)
+                            *reinterpret_cast<uint4*>(out + c0 + 8 * q) =
+                                make_uint4(pack_bf16(v[8 * q], v[8 * q + 1]), pack_bf16(v[8 * q + 2], v[8 * q + 3]),
+                                           pack_bf16(v[8 * q + 4], v[8 * q + 5]), pack_bf16(v[8 * q + 6], v[8 * q + 7]));
+                }
+            }
+            for (; c0 < ncols; c0 += 16) {
                 uint32_t v[16];
                 tmem_ld16(taddr + c0, v);
                 tmem_ld_wait();
                 if (valid) {
-                    uint32_t w[8];
+                    if (bias) {
 #pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        float a = __uint_as_float(v[2 * j]), b = __uint_as_float(v[2 * j + 1]);
-                        if (bias) {
-                            const int c = n0 + c0 + 2 * j;
-                            a += c < p.Nc ? bias[c] : 0.f;
-                            b += c + 1 < p.Nc ? bias[c + 1] : 0.f;
-                        }
-                        __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-                        w[j] = *reinterpret_cast<uint32_t*>(&h);
+                        for (int j = 0; j < 16; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + (n0 + c0 + j < p.Nc ? bias[n0 + c0 + j] : 0.f));
                     }
-                    *reinterpret_cast<uint4*>(out + c0) = make_uint4(w[0], w[1], w[2], w[3]);
-                    if (c0 + 8 < ncols) *reinterpret_cast<uint4*>(out + c0 + 8) = make_uint4(w[4], w[5], w[6], w[7]);
+#pragma unroll
+                    for (int q = 0; q < 2; ++q)
+                        if (c0 + 8 * q < ncols)
+                            *reinterpret_cast<uint4*>(out + c0 + 8 * q) =
+                                make_uint4(pack_bf16(v[8 * q], v[8 * q + 1]), pack_bf16(v[8 * q + 2], v[8 * q + 3]),
+                                           pack_bf16(v[8 * q + 4], v[8 * q + 5]), pack_bf16(v[8 * q + 6], v[8 * q + 7]));
                 }
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
+            if (lane == 0) mbar_arrive(bar_tempty + 8 * grp);
         }
     }
     tc_fence_before();
@@ -292,7 +333,7 @@ struct HaloParams {
     int N, H, W, tiles_x, tiles_y, total_tiles;
     int kh, kw, mul_t, off_h, off_w, oy_min, ox_min;
     int Wh, Hh, BN, ksteps, Nc, ncp, ldd;
-    int stages, tmem_cols;
+    int stages, tmem_cols, nacc;   // nacc TMEM accumulators in flight (hides the commit -> epilogue -> release round trip)
     uint32_t a_bytes, a_stage, b_tap_bytes;
 };
 
@@ -304,6 +345,7 @@ __device__ __forceinline__ uint64_t umma_desc_halo(uint32_t saddr, uint32_t sbo_
     return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
 
+template <int TAPS, int KSTEPS>
 __global__ void __launch_bounds__(kHaloThreads, 1)
 conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     bf16* __restrict__ dst, const float* __restrict__ bias, const HaloParams p) {
@@ -313,13 +355,13 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const uint32_t sB = base, sA = base + ((taps * p.b_tap_bytes + 1023u) & ~1023u);
     const uint32_t bars = sA + p.stages * p.a_stage;
     const uint32_t bar_full = bars, bar_empty = bars + 8 * kMaxStages;
-    const uint32_t bar_tfull = bars + 16 * kMaxStages, bar_tempty = bar_tfull + 16, bar_w = bar_tempty + 16;
+    const uint32_t bar_tfull = bars + 16 * kMaxStages, bar_tempty = bar_tfull + 8 * kMaxAcc, bar_w = bar_tempty + 8 * kMaxAcc;
     const uint32_t tmem_slot = bar_w + 8;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < p.stages; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(bar_tfull + 8 * a, 1); mbar_init(bar_tempty + 8 * a, 4); }
+        for (int a = 0; a < p.nacc; ++a) { mbar_init(bar_tfull + 8 * a, 1); mbar_init(bar_tempty + 8 * a, 4); }
         mbar_init(bar_w, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -353,45 +395,43 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     } else if (warp == 1) {
         if (lane == 0) {
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((128u >> 4) << 24);
-            // The issuing thread is latency bound on its own instruction stream, so everything that does
-            // not change per tile is hoisted: per-tap start-address offsets (16 B units, the descriptor's
-            // address field) live in registers and the tap / k loops are fully unrolled.
-            constexpr int kMaxTaps = 9;
-            uint32_t a_off[kMaxTaps], b_lo[kMaxTaps];
+            // The issuing thread is latency bound on its own instruction stream (measured: the issue loop, not
+            // TMA, MMA or the epilogue, set the tile rate), so TAPS / KSTEPS are template constants, the loops
+            // are fully unrolled without predicates and per-tap address offsets live in registers.
+            uint32_t a_off[TAPS], b_lo[TAPS];
 #pragma unroll
-            for (int tap = 0; tap < kMaxTaps; ++tap) {
+            for (int tap = 0; tap < TAPS; ++tap) {
                 const int r = tap / p.kw, s = tap - r * p.kw;
                 const int ry = r * p.mul_t + p.off_h - p.oy_min, sx = s * p.mul_t + p.off_w - p.ox_min;
                 a_off[tap] = (uint32_t)((ry * p.Wh + sx) * 128) >> 4;
-                b_lo[tap] = ((sB + tap * p.b_tap_bytes) & 0x3FFFFu) >> 4;
+                b_lo[tap] = (((sB + tap * p.b_tap_bytes) & 0x3FFFFu) >> 4) | (1u << 16);
             }
-            const uint64_t hi_a = (1ull << 16) | ((uint64_t)((p.Wh * 128) >> 4) << 32) | (1ull << 46) | (2ull << 61);
-            const uint64_t hi_b = (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
-            const int ksteps = p.ksteps;
+            const uint32_t hi_a = (uint32_t)((p.Wh * 128) >> 4) | (1u << 14) | (2u << 29);     // SBO, version 1, SWIZZLE_128B
+            const uint32_t hi_b = (uint32_t)(1024 >> 4) | (1u << 14) | (2u << 29);
+            const int nacc = p.nacc, stages = p.stages, total = p.total_tiles, BN = p.BN;
+            const uint32_t a_stage16 = p.a_stage >> 4, a_lo0 = ((sA & 0x3FFFFu) >> 4) | (1u << 16);
             mbar_wait(bar_w, 0);
             tc_fence_after();
-            int stage = 0, it = 0;
-            uint32_t phase = 0;
-            for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
-                const int as = it & 1;
-                mbar_wait(bar_tempty + 8 * as, ((it >> 1) & 1) ^ 1);
+            int stage = 0, as = 0;
+            uint32_t phase = 0, aphase = 1;
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                mbar_wait(bar_tempty + 8 * as, aphase);
                 mbar_wait(bar_full + 8 * stage, phase);
                 tc_fence_after();
-                const uint32_t tmem_d = tmem_base + as * p.BN;
-                const uint32_t a_lo = ((sA + stage * p.a_stage) & 0x3FFFFu) >> 4;
+                const uint32_t tmem_d = tmem_base + as * BN;
+                const uint32_t a_lo = a_lo0 + stage * a_stage16;
 #pragma unroll
-                for (int tap = 0; tap < kMaxTaps; ++tap) {
-                    if (tap < taps) {
-                        const uint64_t da = hi_a | (uint64_t)(a_lo + a_off[tap]);
-                        const uint64_t db = hi_b | (uint64_t)b_lo[tap];
+                for (int tap = 0; tap < TAPS; ++tap) {
 #pragma unroll
-                        for (int k = 0; k < 4; ++k)
-                            if (k < ksteps) umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (tap | k) ? 1u : 0u);
+                    for (int k = 0; k < KSTEPS; ++k) {
+                        if (tap == 0 && k == 0) umma_bf16_lh<0>(tmem_d, a_lo + a_off[tap], hi_a, b_lo[tap], hi_b, idesc);
+                        else umma_bf16_lh<1>(tmem_d, a_lo + a_off[tap] + 2 * k, hi_a, b_lo[tap] + 2 * k, hi_b, idesc);
                     }
                 }
                 umma_commit(bar_empty + 8 * stage);
                 umma_commit(bar_tfull + 8 * as);
-                if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                if (++stage == stages) { stage = 0; phase ^= 1; }
+                if (++as == nacc) { as = 0; aphase ^= 1; }
             }
         }
     } else {
@@ -401,7 +441,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int m = quad * 32 + lane;
         const int dy = m >> 3, dx = m & 7;
         const int ncols = p.ncp;
-        const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + grp * p.BN;
+        const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
         int it = grp;
         for (int t = blockIdx.x + grp * gridDim.x; t < p.total_tiles; t += 2 * gridDim.x, it += 2) {
             const int img = t / tiles_per_img, rem = t - img * tiles_per_img;
@@ -409,7 +449,9 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const int y = ty * 16 + dy, x = (rem - ty * p.tiles_x) * 8 + dx;
             const bool valid = y < p.H && x < p.W;
             bf16* out = dst + ((int64_t)(img * p.H + y) * p.W + x) * p.ldd;
-            mbar_wait(bar_tfull + 8 * grp, (it >> 1) & 1);
+            const int as = it % p.nacc;
+            const uint32_t taddr = tlane + as * p.BN;
+            mbar_wait(bar_tfull + 8 * as, (it / p.nacc) & 1);
             tc_fence_after();
             int c0 = 0;
             for (; c0 + 32 <= ncols || (c0 < ncols && ncols - c0 > 16); c0 += 32) {
@@ -448,7 +490,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(bar_tempty + 8 * grp);
+            if (lane == 0) mbar_arrive(bar_tempty + 8 * as);
         }
     }
     tc_fence_before();
@@ -623,30 +665,34 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
                     const int tap = tap0 + k, r = tap / p.kw, s = tap - r * p.kw;
                     b_off[k] = (uint32_t)((r * p.dil * p.Wh + s * p.dil) * 128) >> 4;
                 }
-                const uint64_t hi_a = ((uint64_t)(((128 * rbA) >> 4) & 0x3FFFu) << 16) | ((uint64_t)((8 * rbA) >> 4) << 32) | (1ull << 46) |
-                                      ((rbA == 128 ? 2ull : 4ull) << 61);
-                const uint64_t hi_b = ((uint64_t)((p.Wh * 128) >> 4) << 32) | (1ull << 46) | (2ull << 61);    // one MN group: LBO unused
+                // descriptor halves: low = start address | LBO << 16, high = SBO | version | layout
+                const uint32_t lbo_a = (((128 * rbA) >> 4) & 0x3FFFu) << 16;
+                const uint32_t hi_a = ((8 * rbA) >> 4) | (1u << 14) | ((rbA == 128 ? 2u : 4u) << 29);
+                const uint32_t hi_b = (uint32_t)((p.Wh * 128) >> 4) | (1u << 14) | (2u << 29);                 // one MN group: LBO unused
                 const uint32_t a_kk = (16 * rbA) >> 4, b_kk = (uint32_t)(2 * p.Wh * 128) >> 4;               // 16 pixels = 2 tile rows
+                const uint32_t a_lo0 = ((sA & 0x3FFFFu) >> 4) | lbo_a, b_lo0 = (sB & 0x3FFFFu) >> 4;
+                const uint32_t a_st = p.a_stage >> 4, b_st = p.b_stage >> 4;
+                const int stagesB = p.stagesB, TN = p.TN;
                 for (int64_t t = t_beg; t < t_end; ++t) {
                     mbar_wait(barA_full + 8 * stA, phA);
                     mbar_wait(barB_full + 8 * stB, phB);
                     tc_fence_after();
-                    const uint32_t a_lo = ((sA + stA * p.a_stage) & 0x3FFFFu) >> 4;
-                    const uint32_t b_lo = ((sB + stB * p.b_stage) & 0x3FFFFu) >> 4;
+                    const uint32_t a_lo = a_lo0 + stA * a_st;
+                    const uint32_t b_lo = b_lo0 + stB * b_st;
                     const uint32_t first = t > t_beg ? 1u : 0u;
 #pragma unroll
                     for (int k = 0; k < kMaxTaps; ++k) {
                         if (k < ntap) {
-                            const uint32_t tmem_d = tmem_base + k * p.TN;
+                            const uint32_t tmem_d = tmem_base + k * TN;
+                            umma_bf16_lhr(tmem_d, a_lo, hi_a, b_lo + b_off[k], hi_b, idesc, first);
 #pragma unroll
-                            for (int kk = 0; kk < 8; ++kk)
-                                umma_bf16(tmem_d, hi_a | (uint64_t)(a_lo + kk * a_kk), hi_b | (uint64_t)(b_lo + b_off[k] + kk * b_kk),
-                                          idesc, kk ? 1u : first);
+                            for (int kk = 1; kk < 8; ++kk)
+                                umma_bf16_lh<1>(tmem_d, a_lo + kk * a_kk, hi_a, b_lo + b_off[k] + kk * b_kk, hi_b, idesc);
                         }
                     }
                     umma_commit(barB_empty + 8 * stB);
                     umma_commit(barA_empty + 8 * stA);
-                    if (++stB == p.stagesB) { stB = 0; phB ^= 1; }
+                    if (++stB == stagesB) { stB = 0; phB ^= 1; }
                     if (++stA == SA) { stA = 0; phA ^= 1; }
                 }
             } else
@@ -659,12 +705,14 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
                     tc_fence_after();
                     const uint32_t baddr = sB + stB * p.b_stage;
                     const uint32_t tmem_d = tmem_base + k * p.TN;
+                    const uint32_t a_lo = ((aaddr & 0x3FFFFu) >> 4) | ((((128 * rbA) >> 4) & 0x3FFFu) << 16);
+                    const uint32_t b_lo = ((baddr & 0x3FFFFu) >> 4) | ((((128 * rbB) >> 4) & 0x3FFFu) << 16);
+                    const uint32_t hi_a = ((8 * rbA) >> 4) | (1u << 14) | ((rbA == 128 ? 2u : 4u) << 29);
+                    const uint32_t hi_b = ((8 * rbB) >> 4) | (1u << 14) | ((rbB == 128 ? 2u : 4u) << 29);
+                    umma_bf16_lhr(tmem_d, a_lo, hi_a, b_lo, hi_b, idesc, t > t_beg ? 1u : 0u);
 #pragma unroll
-                    for (int kk = 0; kk < 8; ++kk) {                       // 128 pixels = 8 x K16
-                        const uint64_t da = umma_desc_mn(aaddr + kk * 16 * rbA, rbA, 128 * rbA);
-                        const uint64_t db = umma_desc_mn(baddr + kk * 16 * rbB, rbB, 128 * rbB);
-                        umma_bf16(tmem_d, da, db, idesc, (t > t_beg || kk > 0) ? 1u : 0u);
-                    }
+                    for (int kk = 1; kk < 8; ++kk)                         // 128 pixels = 8 x K16
+                        umma_bf16_lh<1>(tmem_d, a_lo + kk * ((16 * rbA) >> 4), hi_a, b_lo + kk * ((16 * rbB) >> 4), hi_b, idesc);
                     umma_commit(barB_empty + 8 * stB);
                     if (++stB == p.stagesB) { stB = 0; phB ^= 1; }
                 }
@@ -875,8 +923,10 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     int stages = (int)((kSmemBudget - bres) / p.a_stage);
     p.stages = stages > kMaxStages ? kMaxStages : stages;
     if (p.stages < 2) return MSX_OK;
+    p.nacc = 512 / p.BN < kMaxAcc ? 512 / p.BN : kMaxAcc;
+    if (p.nacc % 2) --p.nacc;                                     // two epilogue groups alternate tiles
     int cols = 32;
-    while (cols < 2 * p.BN) cols <<= 1;
+    while (cols < p.nacc * p.BN) cols <<= 1;
     p.tmem_cols = cols;
     const int lds = fwd_pass ? d->ldx : d->ldy;
     CUtensorMap tmA, tmB;
@@ -892,17 +942,28 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
         cuuint32_t box[3] = {64, (cuuint32_t)p.BN, 1};
         MSX_TRY(make_map(&tmB, 3, packed, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B));
     }
-    static bool attr_set = false;
-    if (!attr_set) {
-        MSX_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        attr_set = true;
-    }
-    const size_t smem = 1024 + bres + (size_t)p.stages * p.a_stage + 16 * kMaxStages + 96;
+    const size_t smem = 1024 + bres + (size_t)p.stages * p.a_stage + 16 * kMaxStages + 16 * kMaxAcc + 96;
     const int grid = p.total_tiles < kNumSMs ? p.total_tiles : kNumSMs;
     const double M = (double)p.N * p.H * p.W;
+    typedef void (*HaloKernel)(const CUtensorMap, const CUtensorMap, bf16*, const float*, const HaloParams);
+    HaloKernel kern = nullptr;
+#define MSX_HALO_CASE(T, K) if (taps == T && p.ksteps == K) kern = conv_tc_halo_kernel<T, K>;
+    MSX_HALO_CASE(9, 1) MSX_HALO_CASE(9, 2) MSX_HALO_CASE(9, 3) MSX_HALO_CASE(9, 4)
+    MSX_HALO_CASE(7, 1) MSX_HALO_CASE(7, 2) MSX_HALO_CASE(7, 3) MSX_HALO_CASE(7, 4)
+#undef MSX_HALO_CASE
+    if (!kern) return MSX_OK;                                     // other tap counts: streaming kernel
+    {
+        static HaloKernel seen[8] = {nullptr};                    // opt in to > 48 KB dynamic smem once per instantiation
+        int i = 0;
+        while (i < 8 && seen[i] && seen[i] != kern) ++i;
+        if (i < 8 && !seen[i]) {
+            MSX_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+            seen[i] = kern;
+        }
+    }
     {
         ProfScope ps__(K_CONV_TC, st, M * (K + Nc) * 2.0, 2.0 * M * Nc * K * taps);
-        conv_tc_halo_kernel<<<grid, kHaloThreads, smem, st>>>(tmA, tmB, static_cast<bf16*>(dst), bias, p);
+        kern<<<grid, kHaloThreads, smem, st>>>(tmA, tmB, static_cast<bf16*>(dst), bias, p);
     }
     MSX_LAUNCH_CHECK();
     note_conv_engine(MSX_ENGINE_TCGEN05);
@@ -1029,7 +1090,7 @@ int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const
         const double Mg = (double)p.N * p.H * p.W, Ms = (double)p.N * Hs * Ws / nphase;
         {
             ProfScope ps__(K_CONV_TC, st, (Mg * Nc + Ms * K) * 2.0, 2.0 * Mg * Nc * K * p.taps.n);
-            conv_tc_kernel<<<grid, kThreads, smem, st>>>(maps, tmB, static_cast<bf16*>(dst), bias, p);
+            conv_tc_kernel<<<grid, kHaloThreads, smem, st>>>(maps, tmB, static_cast<bf16*>(dst), bias, p);
         }
         MSX_LAUNCH_CHECK();
     }

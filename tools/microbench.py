@@ -61,16 +61,18 @@ def main():
                 continue
             fn()
             torch.cuda.synchronize()
-            best = 1e9
+            # kernel-only time from the library's per-launch CUDA events (host launch latency excluded)
+            L.profile_collect()
+            lib.msx_profile_enable(1)
             for _ in range(a.reps):
                 flush.zero_()
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record()
                 fn()
-                e1.record()
-                torch.cuda.synchronize()
-                best = min(best, e0.elapsed_time(e1))
-            print(f'{cin:4d}->{cout:4d} {kh}x{kw} d{dil} @{hw:3d}^2     {name:6s} {best * 1e3:9.1f} {by / best / 1e6:8.0f} {fl / best / 1e9:8.1f}')
+            prof = L.profile_collect()
+            lib.msx_profile_enable(0)
+            main_k = {k: v for k, v in prof.items() if k.startswith('conv_')}
+            ms = sum(v['ms'] for v in main_k.values()) / a.reps
+            other = sum(v['ms'] for k, v in prof.items() if not k.startswith('conv_')) / a.reps
+            print(f'{cin:4d}->{cout:4d} {kh}x{kw} d{dil} @{hw:3d}^2     {name:6s} {ms * 1e3:9.1f} {by / ms / 1e6:8.0f} {fl / ms / 1e9:8.1f}   (+{other * 1e3:.1f} us pack/reduce)')
 
 
 if __name__ == '__main__':
