@@ -124,9 +124,12 @@ def main():
     ap.add_argument('--dtype', default='bf16', choices=['bf16', 'fp32'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--profile-steps', type=int, default=2)
+    ap.add_argument('--ncu', action='store_true', help='short eager run for an ncu launch list: 1 warm-up + 1 step, no graph / e2e / profile pass')
     ap.add_argument('--no-graph', action='store_true', help='launch every kernel from Python instead of replaying one CUDA graph per step')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'b200' else args.warmup
+    if args.ncu:
+        args.warmup, args.steps, args.no_graph, args.profile_steps, args.no_cpu_baseline = 1, 1, True, 0, True
     if args.impl == 'reference':
         return run_reference(args)
 
@@ -160,8 +163,7 @@ def main():
     ema = msx.ModelEma(model)
     loss_fn = msx.get_loss_fn(Cfg, dev)
     xh, th = synth_batch(B, S, S, seed=1 + rank)
-    if not os.environ.get('MSX_DBG_NOPIN'):
-        xh, th = xh.pin_memory(), th.pin_memory()
+    xh, th = xh.pin_memory(), th.pin_memory()
     xd, td = xh.to(dev), th.to(dev)
     it = [0]
 
@@ -170,12 +172,9 @@ def main():
         with torch.autocast('cuda', dtype=torch.bfloat16, enabled=bf16):
             loss = loss_fn(net(x), t)
         loss.backward()
-        dbg = os.environ.get('MSX_DBG_STEP', '')
-        if 'noopt' not in dbg:
-            opt.step()
+        opt.step()
         it[0] += 1
-        if 'noema' not in dbg:
-            ema.update(model, it[0])
+        ema.update(model, it[0])
         return loss
 
     def barrier():
@@ -248,8 +247,11 @@ def main():
         sx.copy_(xh, non_blocking=True)
         st_.copy_(th, non_blocking=True)
         return float(run_step().detach())
-    e2e_step()
-    ms_e2e = timed(e2e_step, args.steps)
+    if args.ncu:
+        ms_e2e = ms
+    else:
+        e2e_step()
+        ms_e2e = timed(e2e_step, args.steps)
 
     # profiled pass: per-launch CUDA events on the launching stream, algorithmic bytes/flops per launch
     prof = {}

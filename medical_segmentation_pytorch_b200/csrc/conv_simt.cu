@@ -204,26 +204,46 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(const T* __restrict__ s
 }
 
 // dW[(a*B + b)*taps + tap] = sum_split partial[split][tap][a][b]   (reference OIHW / IOHW layout)
-__global__ void wgrad_reduce_kernel(const float* __restrict__ partial, int splits, int taps, int A, int B, int Apad, int Bpad,
-                                    float* __restrict__ dw) {
-    // thread -> (tap, a, b) with b fastest: the (many) partial reads are coalesced, the single write scatters
+__global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restrict__ partial, int splits, int taps, int A, int B,
+                                                           int Apad, int Bpad, float* __restrict__ dw) {
+    // A CTA = 32 consecutive outputs x 8 slices of the split range.  Outputs are ordered (tap, a, b) with b
+    // fastest so the partial reads are coalesced; each slice sums its splits in fixed order (4 loads in
+    // flight), the 8 slice sums are combined in fixed order through shared memory: deterministic.
+    __shared__ float sh[8][33];
     const int64_t total = (int64_t)A * B * taps;
     const int64_t zstride = (int64_t)taps * Apad * Bpad;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int b = (int)(i % B);
-        const int64_t q = i / B;
-        const int a = (int)(q % A), tap = (int)(q / A);
-        const float* src = partial + ((int64_t)tap * Apad + a) * Bpad + b;
-        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-        int z = 0;
-        for (; z + 3 < splits; z += 4) {                          // four independent loads in flight, fixed order
-            s0 += src[(z + 0) * zstride];
-            s1 += src[(z + 1) * zstride];
-            s2 += src[(z + 2) * zstride];
-            s3 += src[(z + 3) * zstride];
+    const int el = threadIdx.x & 31, sub = threadIdx.x >> 5;
+    const int per = (splits + 7) / 8;
+    const int z0 = sub * per, z1 = min(splits, z0 + per);
+    for (int64_t base = (int64_t)blockIdx.x * 32; base < total; base += (int64_t)gridDim.x * 32) {
+        const int64_t i = base + el;
+        float acc = 0.f;
+        int a = 0, b = 0, tap = 0;
+        if (i < total) {
+            b = (int)(i % B);
+            const int64_t q = i / B;
+            a = (int)(q % A); tap = (int)(q / A);
+            const float* src = partial + ((int64_t)tap * Apad + a) * Bpad + b;
+            float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+            int z = z0;
+            for (; z + 3 < z1; z += 4) {
+                s0 += src[(z + 0) * zstride];
+                s1 += src[(z + 1) * zstride];
+                s2 += src[(z + 2) * zstride];
+                s3 += src[(z + 3) * zstride];
+            }
+            for (; z < z1; ++z) s0 += src[z * zstride];
+            acc = (s0 + s1) + (s2 + s3);
         }
-        for (; z < splits; ++z) s0 += src[z * zstride];
-        dw[((int64_t)a * B + b) * taps + tap] = (s0 + s1) + (s2 + s3);
+        sh[sub][el] = acc;
+        __syncthreads();
+        if (sub == 0 && i < total) {
+            float t = 0.f;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) t += sh[k][el];
+            dw[((int64_t)a * B + b) * taps + tap] = t;
+        }
+        __syncthreads();
     }
 }
 
@@ -381,7 +401,7 @@ int conv_wgrad_simt(const msx_conv_desc* d, const void* x, const void* dy, float
     });
     MSX_LAUNCH_CHECK();
     const int64_t total = (int64_t)g.A * g.B * taps;
-    const int rg = (int)((total + 255) / 256 < 2048 ? (total + 255) / 256 : 2048);
+    const int rg = (int)((total + 31) / 32 < 4096 ? (total + 31) / 32 : 4096);
     { ProfScope ps__(K_WGRAD_REDUCE, st, (double)total * 4 * (g.splits + 1), 0); wgrad_reduce_kernel<<<rg, 256, 0, st>>>(static_cast<const float*>(ws), g.splits, taps, g.A, g.B, g.tiles_a * BT, g.tiles_b * BT, dw); }
     MSX_LAUNCH_CHECK();
     return MSX_OK;
@@ -389,7 +409,7 @@ int conv_wgrad_simt(const msx_conv_desc* d, const void* x, const void* dy, float
 
 int wgrad_reduce_launch(const float* partial, int splits, int taps, int A, int B, int Apad, int Bpad, float* dw, cudaStream_t st) {
     const int64_t total = (int64_t)A * B * taps;
-    const int rg = (int)((total + 255) / 256 < 2048 ? (total + 255) / 256 : 2048);
+    const int rg = (int)((total + 31) / 32 < 4096 ? (total + 31) / 32 : 4096);
     {
         ProfScope ps__(K_WGRAD_REDUCE, st, (double)total * 4 * (splits + 1), 0);
         wgrad_reduce_kernel<<<rg, 256, 0, st>>>(partial, splits, taps, A, B, Apad, Bpad, dw);

@@ -64,13 +64,13 @@ __device__ inline void lane_reduce(double (&v)[NV], double* sh, int vch, int lan
 inline int reduce_grid(int64_t pixels, int lanes) {
     int64_t g = cdiv64(pixels, (int64_t)lanes * 8);
     if (g < 1) g = 1;
-    if (g > kMaxPartialBlocks) g = kMaxPartialBlocks;
+    if (g > kNumSMs * 2) g = kNumSMs * 2;      // one resident wave (2 CTAs/SM by registers); halves the finalize work
     return (int)g;
 }
 inline int stream_grid(int64_t pixels, int lanes) {
     int64_t g = cdiv64(pixels, (int64_t)lanes * 4);
     if (g < 1) g = 1;
-    if (g > kNumSMs * 16) g = kNumSMs * 16;
+    if (g > kNumSMs * 6) g = kNumSMs * 6;      // few, fat CTAs: the per-CTA parameter prologue is amortised
     return (int)g;
 }
 
