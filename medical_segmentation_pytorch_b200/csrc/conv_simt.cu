@@ -247,6 +247,22 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restri
     }
 }
 
+// Few splits (wide layers): one thread per output, reads coalesced along b.
+__global__ void __launch_bounds__(256) wgrad_reduce_flat_kernel(const float* __restrict__ partial, int splits, int taps, int A, int B,
+                                                                int Apad, int Bpad, float* __restrict__ dw) {
+    const int64_t total = (int64_t)A * B * taps;
+    const int64_t zstride = (int64_t)taps * Apad * Bpad;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int b = (int)(i % B);
+        const int64_t q = i / B;
+        const int a = (int)(q % A), tap = (int)(q / A);
+        const float* src = partial + ((int64_t)tap * Apad + a) * Bpad + b;
+        float s = 0.f;
+        for (int z = 0; z < splits; ++z) s += src[z * zstride];
+        dw[((int64_t)a * B + b) * taps + tap] = s;
+    }
+}
+
 // master W[A][B][taps] fp32 -> packed [tap][Np][Kp] (n = a or b)
 template <typename T>
 __global__ void pack_weights_kernel(const float* __restrict__ w, int A, int B, int taps, int n_is_a, int Np, int Kp,
@@ -402,7 +418,7 @@ int conv_wgrad_simt(const msx_conv_desc* d, const void* x, const void* dy, float
     MSX_LAUNCH_CHECK();
     const int64_t total = (int64_t)g.A * g.B * taps;
     const int rg = (int)((total + 31) / 32 < 4096 ? (total + 31) / 32 : 4096);
-    { ProfScope ps__(K_WGRAD_REDUCE, st, (double)total * 4 * (g.splits + 1), 0); wgrad_reduce_kernel<<<rg, 256, 0, st>>>(static_cast<const float*>(ws), g.splits, taps, g.A, g.B, g.tiles_a * BT, g.tiles_b * BT, dw); }
+    { ProfScope ps__(K_WGRAD_REDUCE, st, (double)total * 4 * (g.splits + 1), 0); if (g.splits >= 16) wgrad_reduce_kernel<<<rg, 256, 0, st>>>(static_cast<const float*>(ws), g.splits, taps, g.A, g.B, g.tiles_a * BT, g.tiles_b * BT, dw); else wgrad_reduce_flat_kernel<<<(int)((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096), 256, 0, st>>>(static_cast<const float*>(ws), g.splits, taps, g.A, g.B, g.tiles_a * BT, g.tiles_b * BT, dw); }
     MSX_LAUNCH_CHECK();
     return MSX_OK;
 }
@@ -412,7 +428,8 @@ int wgrad_reduce_launch(const float* partial, int splits, int taps, int A, int B
     const int rg = (int)((total + 31) / 32 < 4096 ? (total + 31) / 32 : 4096);
     {
         ProfScope ps__(K_WGRAD_REDUCE, st, (double)total * 4 * (splits + 1), 0);
-        wgrad_reduce_kernel<<<rg, 256, 0, st>>>(partial, splits, taps, A, B, Apad, Bpad, dw);
+        if (splits >= 16) wgrad_reduce_kernel<<<rg, 256, 0, st>>>(partial, splits, taps, A, B, Apad, Bpad, dw);
+        else wgrad_reduce_flat_kernel<<<(int)((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096), 256, 0, st>>>(partial, splits, taps, A, B, Apad, Bpad, dw);
     }
     MSX_LAUNCH_CHECK();
     return MSX_OK;

@@ -566,6 +566,7 @@ struct WgParams {
     int64_t pix_tiles;
     int halo, Wh, Hh;                 // halo mode: one x patch (+halo) per pixel tile serves every tap
     TapTable taps;                    // streaming mode: per tap, which phase view of the big side and which shift
+    int TNa, G, ncg;                  // tap-stacked mode (halo == 2): N = dy channels, G x-taps share one MMA's M axis
 };
 
 // MN-major operand descriptor: MN groups `lbo` bytes apart, 8-row (K) groups 8*row_bytes apart.
@@ -656,7 +657,51 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
                                    ((uint32_t)(p.TN >> 3) << 17) | ((128u >> 4) << 24);
             int stA = 0, stB = 0;
             uint32_t phA = 0, phB = 0;
-            if (p.halo) {
+            if (p.halo == 2) {
+                // Tap-stacked wgrad for few-channel layers.  The x patch (+halo) is the A operand, MN-major with its
+                // MN groups only ONE PIXEL apart (LBO = dil * row bytes): the G groups of one MMA are the same window
+                // shifted by 0..G-1 taps in x, so M = 128 carries G taps x (32|64) channels instead of 17 useful rows,
+                // and a 3x3 needs 3 MMAs per K-step instead of 9.  D[(s, ci)][co] lives in kh * ncg accumulators.
+                const uint32_t idesc2 = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) |
+                                        ((uint32_t)(p.TNa >> 3) << 17) | ((128u >> 4) << 24);
+                constexpr int kMaxAccQ = 9;
+                const int nq = p.kh * p.ncg;
+                uint32_t x_off[kMaxAccQ];
+#pragma unroll
+                for (int q = 0; q < kMaxAccQ; ++q) {
+                    const int r = q / p.ncg, cg = q - r * p.ncg;
+                    x_off[q] = (uint32_t)((r * p.dil * p.Wh + cg * p.G * p.dil) * (int)rbB) >> 4;
+                }
+                const uint32_t hi_x = (uint32_t)((p.Wh * rbB) >> 4) | (1u << 14) | ((rbB == 128 ? 2u : 4u) << 29);
+                const uint32_t hi_y = ((8 * rbA) >> 4) | (1u << 14) | ((rbA == 128 ? 2u : 4u) << 29);
+                const uint32_t x_lo0 = ((sB & 0x3FFFFu) >> 4) | ((((uint32_t)p.dil * rbB) >> 4) << 16);
+                const uint32_t y_lo0 = ((sA & 0x3FFFFu) >> 4) | ((((128 * rbA) >> 4) & 0x3FFFu) << 16);
+                const uint32_t x_kk = (uint32_t)(2 * p.Wh * rbB) >> 4, y_kk = (16 * rbA) >> 4;
+                const uint32_t a_st = p.a_stage >> 4, b_st = p.b_stage >> 4;
+                const int stagesB = p.stagesB, TNa = p.TNa;
+                for (int64_t t = t_beg; t < t_end; ++t) {
+                    mbar_wait(barA_full + 8 * stA, phA);
+                    mbar_wait(barB_full + 8 * stB, phB);
+                    tc_fence_after();
+                    const uint32_t y_lo = y_lo0 + stA * a_st;
+                    const uint32_t x_lo = x_lo0 + stB * b_st;
+                    const uint32_t first = t > t_beg ? 1u : 0u;
+#pragma unroll
+                    for (int q = 0; q < kMaxAccQ; ++q) {
+                        if (q < nq) {
+                            const uint32_t tmem_d = tmem_base + q * TNa;
+                            umma_bf16_lhr(tmem_d, x_lo + x_off[q], hi_x, y_lo, hi_y, idesc2, first);
+#pragma unroll
+                            for (int kk = 1; kk < 8; ++kk)
+                                umma_bf16_lh<1>(tmem_d, x_lo + x_off[q] + kk * x_kk, hi_x, y_lo + kk * y_kk, hi_y, idesc2);
+                        }
+                    }
+                    umma_commit(barB_empty + 8 * stB);
+                    umma_commit(barA_empty + 8 * stA);
+                    if (++stB == stagesB) { stB = 0; phB ^= 1; }
+                    if (++stA == SA) { stA = 0; phA ^= 1; }
+                }
+            } else if (p.halo) {
                 // per-tap start offsets of the shifted x window inside the halo patch (16 B units), hoisted
                 constexpr int kMaxTaps = 9;
                 uint32_t b_off[kMaxTaps];
@@ -727,6 +772,30 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
             mbar_wait(bar_done, 0);
             tc_fence_after();
         }
+        if (p.halo == 2) {
+            const int g = row / p.chunkB, ci = row - g * p.chunkB;
+            const int nq = p.kh * p.ncg;
+            for (int q = 0; q < nq; ++q) {
+                const int r = q / p.ncg, cg = q - r * p.ncg;
+                const int sx = cg * p.G + g;
+                const bool ok = sx < p.kw && ci < p.Bp;
+                float* out = partial + (((int64_t)split * taps + r * p.kw + sx) * p.Apad) * p.Bpad + ci;
+                const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + q * p.TNa;
+                for (int c0 = 0; c0 < p.TNa; c0 += 16) {
+                    uint32_t v[16];
+                    if (t_end > t_beg) { tmem_ld16(taddr + c0, v); tmem_ld_wait(); }
+                    else {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) v[j] = 0u;
+                    }
+                    if (ok) {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j)
+                            if (c0 + j < p.Ap) out[(int64_t)(c0 + j) * p.Bpad] = __uint_as_float(v[j]);
+                    }
+                }
+            }
+        } else
         for (int k = 0; k < ntap; ++k) {
             float* out = partial + (((int64_t)split * taps + tap0 + k) * p.Apad + a0 + row) * p.Bpad + b0;
             const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + k * p.TN;
@@ -821,6 +890,23 @@ void wgrad_plan(const msx_conv_desc* d, WgParams& p) {
             p.Hh = 16 + span_h;
             p.chunkB = 64; p.groupsB = 1;
             p.b_stage = ((uint32_t)p.Hh * p.Wh * 128u + 1023u) & ~1023u;
+        }
+    }
+    p.TNa = 0; p.G = 0; p.ncg = 0;
+    if (p.halo == 1 && p.Ap <= 128 && halo_mode() != 3) {
+        // tap-stacked variant: see the halo == 2 branch of wgrad_tc_kernel
+        const int chunkB = p.Bp <= 32 ? 32 : 64, G = 128 / chunkB, ncg = (p.kw + G - 1) / G;
+        const int TNa = round_up(A, 16);
+        if ((ncg * G - 1) * p.dil + 8 <= p.Wh && p.kh * ncg * TNa <= 512 && p.kh * ncg <= 9) {
+            p.halo = 2;
+            p.chunkB = chunkB; p.G = G; p.ncg = ncg; p.TNa = TNa;
+            p.b_stage = ((uint32_t)p.Hh * p.Wh * (chunkB * 2) + 1023u) & ~1023u;
+            p.a_tiles = 1; p.b_tiles = 1; p.tap_groups = 1; p.tg = taps;
+            int64_t sp = kNumSMs < p.pix_tiles ? kNumSMs : p.pix_tiles;
+            p.splits = (int)sp;
+            int cols2 = 32;
+            while (cols2 < p.kh * ncg * TNa) cols2 <<= 1;
+            p.tmem_cols = cols2;
         }
     }
     int sb = (int)((kSmemBudget - 2 * p.a_stage) / p.b_stage);
