@@ -985,7 +985,7 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     if (mode == 0) return MSX_OK;
     const int K = fwd_pass ? d->cin : d->cout, Nc = fwd_pass ? d->cout : d->cin;
     const int Kp = round_up(K, 8), Np = round_up(Nc, 16), taps = d->kh * d->kw;
-    if (Kp > 64 || Np > 256 || taps < 2 || taps > 9) return MSX_OK;
+    if (Kp > 64 || Np > 256 || taps > 9) return MSX_OK;         // taps == 1 (1x1): no halo, but resident weights + lean issue loop
     if ((size_t)taps * Np * 128 > 80 * 1024) return MSX_OK;
     const int span_w = (d->kw - 1) * d->dil, span_h = (d->kh - 1) * d->dil;
     if (8 + span_w > 16) return MSX_OK;
@@ -1036,13 +1036,14 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
 #define MSX_HALO_CASE(T, K) if (taps == T && p.ksteps == K) kern = conv_tc_halo_kernel<T, K>;
     MSX_HALO_CASE(9, 1) MSX_HALO_CASE(9, 2) MSX_HALO_CASE(9, 3) MSX_HALO_CASE(9, 4)
     MSX_HALO_CASE(7, 1) MSX_HALO_CASE(7, 2) MSX_HALO_CASE(7, 3) MSX_HALO_CASE(7, 4)
+    MSX_HALO_CASE(1, 1) MSX_HALO_CASE(1, 2) MSX_HALO_CASE(1, 3) MSX_HALO_CASE(1, 4)
 #undef MSX_HALO_CASE
     if (!kern) return MSX_OK;                                     // other tap counts: streaming kernel
     {
-        static HaloKernel seen[8] = {nullptr};                    // opt in to > 48 KB dynamic smem once per instantiation
+        static HaloKernel seen[16] = {nullptr};                    // opt in to > 48 KB dynamic smem once per instantiation
         int i = 0;
-        while (i < 8 && seen[i] && seen[i] != kern) ++i;
-        if (i < 8 && !seen[i]) {
+        while (i < 16 && seen[i] && seen[i] != kern) ++i;
+        if (i < 16 && !seen[i]) {
             MSX_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
             seen[i] = kern;
         }
