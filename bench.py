@@ -294,7 +294,14 @@ def main():
         else:
             ach = tv['bytes'] / tv['ms'] / 1e6
             roofline = {'kernel': top, 'bound': 'hbm', 'achieved': ach, 'peak': pk['hbm_gbs'], 'unit': 'GB/s', 'frac': ach / pk['hbm_gbs']}
-        roofline.update({'traffic': None, 'peak_source': pk['src'] + (' (sustained bf16)' if roofline['bound'] == 'tensor' else ''),
+        traffic, traffic_note = None, None
+        try:
+            tr = json.load(open(os.path.join(ROOT, 'profiles', 'ncu_traffic.json'))).get(top)
+            if tr:
+                traffic, traffic_note = tr['traffic_bytes'], f"{tr['kernel']} {tr['shape']}: algorithmic {tr['algorithmic_bytes']} B; {tr['source']}"
+        except Exception:
+            pass
+        roofline.update({'traffic': traffic, 'traffic_note': traffic_note, 'peak_source': pk['src'] + (' (sustained bf16)' if roofline['bound'] == 'tensor' else ''),
                          'avg_launch_us': tv['ms'] / tv['launches'] * 1e3, 'launches_per_step': tv['launches'] // args.profile_steps,
                          'share_of_step': tv['ms'] / tot_ms,
                          'how': f'{args.profile_steps} extra step(s) after the timed region with per-launch CUDA events (msx_profile_*)'})
