@@ -14,17 +14,27 @@ constexpr int kWsWeight = 0, kWsLoss = kLossMaxBlocks, kWsScalars = 2 * kLossMax
 
 template <int PV>
 __device__ inline void load_px(const float* p, float (&v)[PV]) {
-    if constexpr (PV == 4) { float4 r = *reinterpret_cast<const float4*>(p); v[0] = r.x; v[1] = r.y; v[2] = r.z; v[3] = r.w; }
+    if constexpr (PV == 8) {
+        float4 r = *reinterpret_cast<const float4*>(p), u = *reinterpret_cast<const float4*>(p + 4);
+        v[0] = r.x; v[1] = r.y; v[2] = r.z; v[3] = r.w; v[4] = u.x; v[5] = u.y; v[6] = u.z; v[7] = u.w;
+    } else if constexpr (PV == 4) { float4 r = *reinterpret_cast<const float4*>(p); v[0] = r.x; v[1] = r.y; v[2] = r.z; v[3] = r.w; }
     else v[0] = *p;
 }
 template <int PV>
 __device__ inline void store_px(float* p, const float (&v)[PV]) {
-    if constexpr (PV == 4) *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+    if constexpr (PV == 8) {
+        *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<float4*>(p + 4) = make_float4(v[4], v[5], v[6], v[7]);
+    } else if constexpr (PV == 4) *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
     else *p = v[0];
 }
 template <int PV>
 __device__ inline void load_lab(const int64_t* p, int64_t (&t)[PV]) {
-    if constexpr (PV == 4) {
+    if constexpr (PV == 8) {
+        longlong2 a = *reinterpret_cast<const longlong2*>(p), b = *reinterpret_cast<const longlong2*>(p + 2);
+        longlong2 c = *reinterpret_cast<const longlong2*>(p + 4), d = *reinterpret_cast<const longlong2*>(p + 6);
+        t[0] = a.x; t[1] = a.y; t[2] = b.x; t[3] = b.y; t[4] = c.x; t[5] = c.y; t[6] = d.x; t[7] = d.y;
+    } else if constexpr (PV == 4) {
         longlong2 a = *reinterpret_cast<const longlong2*>(p), b = *reinterpret_cast<const longlong2*>(p + 2);
         t[0] = a.x; t[1] = a.y; t[2] = b.x; t[3] = b.y;
     } else t[0] = *p;
@@ -74,7 +84,8 @@ __global__ void __launch_bounds__(256) ce_kernel(const float* __restrict__ logit
     const int64_t gpi = hw / PV;   // pixel groups per image
     float lacc = 0.f;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < groups; i += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t n = i / gpi, q = (i % gpi) * PV;
+        const uint32_t iu = (uint32_t)i, nu = iu / (uint32_t)gpi;      // 32-bit: groups < 2^31 (checked on the host)
+        const int64_t n = nu, q = (int64_t)(iu - nu * (uint32_t)gpi) * PV;
         const float* zp = logits + n * c * hw + q;
         int64_t t[PV];
         load_lab<PV>(labels + n * hw + q, t);
@@ -95,8 +106,9 @@ __global__ void __launch_bounds__(256) ce_kernel(const float* __restrict__ logit
                 if (k < c) {
 #pragma unroll
                     for (int j = 0; j < PV; ++j) {
-                        se[j] += expf(z[k][j] - mx[j]);
                         if (t[j] == k) zt[j] = z[k][j];
+                        z[k][j] = expf(z[k][j] - mx[j]);          // z now holds exp(z - max): reused by the gradient
+                        se[j] += z[k][j];
                     }
                 }
         } else {
@@ -130,6 +142,9 @@ __global__ void __launch_bounds__(256) ce_kernel(const float* __restrict__ logit
             if (MODE == 0) up[j] = invd;
         }
         if (MODE == 1) { store_px<PV>(out_pix + n * hw + q, lp); continue; }
+        float rse[PV];
+#pragma unroll
+        for (int j = 0; j < PV; ++j) rse[j] = 1.f / se[j];
         if (dlogits) {
             float* gp = dlogits + n * c * hw + q;
             if constexpr (CT > 0) {
@@ -139,7 +154,7 @@ __global__ void __launch_bounds__(256) ce_kernel(const float* __restrict__ logit
                         float g[PV];
 #pragma unroll
                         for (int j = 0; j < PV; ++j) {
-                            const float sm = expf(z[k][j] - mx[j]) / se[j];
+                            const float sm = z[k][j] * rse[j];
                             g[j] = vld[j] ? wt[j] * (sm - (t[j] == k ? 1.f : 0.f)) * up[j] : 0.f;
                         }
                         store_px<PV>(gp + k * hw, g);
@@ -174,6 +189,7 @@ __global__ void ce_finalize_kernel(const double* __restrict__ ws, int nwpart, in
     if (threadIdx.x == 0) *loss_out = use_denom ? (float)(l / w) : (float)l;
 }
 
+inline bool groups_ok(int64_t groups) { return groups < (int64_t)1 << 31; }
 inline int loss_grid(int64_t groups) {
     int64_t g = cdiv64(groups, 256);
     if (g < 1) g = 1;
@@ -185,12 +201,15 @@ template <int MODE>
 int ce_dispatch(const float* logits, const int64_t* labels, int n, int c, int64_t hw, const float* cw, int64_t ignore,
                 int nwpart, int use_denom, const float* coef, float* out_pix, float* dlogits, double* ws, int* grid_out,
                 cudaStream_t st) {
-    const bool v4 = hw % 4 == 0;
-    const int64_t groups = (int64_t)n * hw / (v4 ? 4 : 1);
+    const bool v8 = hw % 8 == 0 && c <= 4, v4 = hw % 4 == 0;
+    const int64_t groups = (int64_t)n * hw / (v8 ? 8 : (v4 ? 4 : 1));
+    if (!groups_ok(groups)) return set_error(MSX_ERR_UNSUPPORTED, "loss: more than 2^31 pixel groups");
     const int g = loss_grid(groups);
     *grid_out = g;
 #define MSX_CE_LAUNCH(PV, CT) { ProfScope ps__(K_LOSS, st, (double)n * hw * (MODE == 1 ? 4.0 * c + 12.0 : (MODE == 2 ? 8.0 * c + 12.0 : (dlogits ? 8.0 * c + 8.0 : 4.0 * c + 8.0))), 0); ce_kernel<PV, CT, MODE><<<g, 256, 0, st>>>(logits, labels, c, hw, groups, cw, ignore, nwpart, use_denom, coef, out_pix, dlogits, ws); }
-    if (v4) {
+    if (v8) {
+        if (c <= 2) MSX_CE_LAUNCH(8, 2) else MSX_CE_LAUNCH(8, 4)
+    } else if (v4) {
         if (c <= 2) MSX_CE_LAUNCH(4, 2) else if (c <= 4) MSX_CE_LAUNCH(4, 4) else if (c <= 8) MSX_CE_LAUNCH(4, 8) else MSX_CE_LAUNCH(4, 0)
     } else {
         if (c <= 2) MSX_CE_LAUNCH(1, 2) else if (c <= 4) MSX_CE_LAUNCH(1, 4) else if (c <= 8) MSX_CE_LAUNCH(1, 8) else MSX_CE_LAUNCH(1, 0)
@@ -201,6 +220,67 @@ int ce_dispatch(const float* logits, const int64_t* labels, int n, int c, int64_
 }
 
 // ---- knowledge distillation -----------------------------------------------------------------
+// Register-resident variant for c <= CT classes: every logit is loaded once, 2c exp + 2 log per pixel.
+template <int PV, int CT>
+__global__ void __launch_bounds__(256) kd_kl_reg_kernel(const float* __restrict__ s, const float* __restrict__ t, int c, int64_t hw,
+                                                        int64_t groups, float invT, float gscale, float* __restrict__ ds,
+                                                        double* __restrict__ ws) {
+    const int64_t gpi = hw / PV;
+    float lacc = 0.f;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < groups; i += (int64_t)gridDim.x * blockDim.x) {
+        const uint32_t iu = (uint32_t)i, nu = iu / (uint32_t)gpi;      // 32-bit: groups < 2^31 (checked on the host)
+        const int64_t n = nu, q = (int64_t)(iu - nu * (uint32_t)gpi) * PV;
+        const float* sp = s + n * c * hw + q;
+        const float* tp = t + n * c * hw + q;
+        float a[CT][PV], b[CT][PV], ms[PV], mt[PV], es[PV], et[PV];
+#pragma unroll
+        for (int j = 0; j < PV; ++j) { ms[j] = mt[j] = -INFINITY; es[j] = et[j] = 0.f; }
+#pragma unroll
+        for (int k = 0; k < CT; ++k)
+            if (k < c) {
+                load_px<PV>(sp + k * hw, a[k]);
+                load_px<PV>(tp + k * hw, b[k]);
+            }
+#pragma unroll
+        for (int k = 0; k < CT; ++k)
+            if (k < c) {
+#pragma unroll
+                for (int j = 0; j < PV; ++j) {
+                    a[k][j] *= invT; b[k][j] *= invT;
+                    ms[j] = fmaxf(ms[j], a[k][j]); mt[j] = fmaxf(mt[j], b[k][j]);
+                }
+            }
+        float ea[CT][PV], eb[CT][PV];
+#pragma unroll
+        for (int k = 0; k < CT; ++k)
+            if (k < c) {
+#pragma unroll
+                for (int j = 0; j < PV; ++j) {
+                    a[k][j] -= ms[j]; b[k][j] -= mt[j];
+                    ea[k][j] = expf(a[k][j]); eb[k][j] = expf(b[k][j]);
+                    es[j] += ea[k][j]; et[j] += eb[k][j];
+                }
+            }
+        float ls[PV], lt[PV], rs[PV], rt[PV];
+#pragma unroll
+        for (int j = 0; j < PV; ++j) { ls[j] = logf(es[j]); lt[j] = logf(et[j]); rs[j] = 1.f / es[j]; rt[j] = 1.f / et[j]; }
+#pragma unroll
+        for (int k = 0; k < CT; ++k)
+            if (k < c) {
+                float g[PV];
+#pragma unroll
+                for (int j = 0; j < PV; ++j) {
+                    const float qq = eb[k][j] * rt[j];
+                    if (qq > 0.f) lacc += qq * ((b[k][j] - lt[j]) - (a[k][j] - ls[j]));
+                    g[j] = (ea[k][j] * rs[j] - qq) * gscale;
+                }
+                if (ds) store_px<PV>(ds + n * c * hw + q + k * hw, g);
+            }
+    }
+    const double r = block_sum_d((double)lacc);
+    if (threadIdx.x == 0) ws[kWsLoss + blockIdx.x] = r;
+}
+
 template <int PV>
 __global__ void __launch_bounds__(256) kd_kl_kernel(const float* __restrict__ s, const float* __restrict__ t, int c, int64_t hw,
                                                     int64_t groups, float invT, float gscale, float* __restrict__ ds,
@@ -208,7 +288,8 @@ __global__ void __launch_bounds__(256) kd_kl_kernel(const float* __restrict__ s,
     const int64_t gpi = hw / PV;
     float lacc = 0.f;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < groups; i += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t n = i / gpi, q = (i % gpi) * PV;
+        const uint32_t iu = (uint32_t)i, nu = iu / (uint32_t)gpi;      // 32-bit: groups < 2^31 (checked on the host)
+        const int64_t n = nu, q = (int64_t)(iu - nu * (uint32_t)gpi) * PV;
         const float* sp = s + n * c * hw + q;
         const float* tp = t + n * c * hw + q;
         float ms[PV], mt[PV], es[PV], et[PV];
@@ -272,17 +353,38 @@ template <bool FLOAT_T>
 __device__ inline float target_at(const void* t, int64_t i) {
     return FLOAT_T ? static_cast<const float*>(t)[i] : (float)static_cast<const int64_t*>(t)[i];
 }
+template <bool FLOAT_T>
+__device__ inline void targets4(const void* t, int64_t i, float (&y)[4]) {
+    if (FLOAT_T) load_px<4>(static_cast<const float*>(t) + i, y);
+    else {
+        int64_t l[4];
+        load_lab<4>(static_cast<const int64_t*>(t) + i, l);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) y[j] = (float)l[j];
+    }
+}
 // partial sums: 4 arrays of kLossMaxBlocks doubles starting at ws[0]
 template <bool FLOAT_T>
 __global__ void __launch_bounds__(256) dice_bce_reduce_kernel(const float* __restrict__ z, const void* __restrict__ t, int64_t count,
                                                               double* __restrict__ ws) {
     float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x) {
-        const float x = z[i], y = target_at<FLOAT_T>(t, i);
-        const float sp = fmaxf(x, 0.f) + log1pf(expf(-fabsf(x)));
-        const float p = 1.f / (1.f + expf(-x));
+    auto body = [&](float x, float y) {
+        const float e = expf(-fabsf(x));                        // one exp serves softplus and sigmoid
+        const float sp = fmaxf(x, 0.f) + log1pf(e);
+        const float r = 1.f / (1.f + e);
+        const float p = x >= 0.f ? r : e * r;
         a0 += sp - x * y; a1 += p * y; a2 += p; a3 += y;
+    };
+    const int64_t quads = count >> 2;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < quads; i += (int64_t)gridDim.x * blockDim.x) {
+        float x[4], y[4];
+        load_px<4>(z + 4 * i, x);
+        targets4<FLOAT_T>(t, 4 * i, y);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) body(x[j], y[j]);
     }
+    for (int64_t i = 4 * quads + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x)
+        body(z[i], target_at<FLOAT_T>(t, i));
     __shared__ double sh[32];
     const double r0 = block_sum<double>((double)a0, sh), r1 = block_sum<double>((double)a1, sh);
     const double r2 = block_sum<double>((double)a2, sh), r3 = block_sum<double>((double)a3, sh);
@@ -313,12 +415,23 @@ __global__ void __launch_bounds__(256) dice_bce_grad_kernel(const float* __restr
                                                             const double* __restrict__ ws, float* __restrict__ dz) {
     const float num = (float)ws[kWsScalars + 0], den = (float)ws[kWsScalars + 1];
     const float inv_cnt = 1.f / (float)count, inv_den2 = 1.f / (den * den);
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x) {
-        const float x = z[i], y = target_at<FLOAT_T>(t, i);
-        const float p = 1.f / (1.f + expf(-x));
+    auto grad = [&](float x, float y) {
+        const float e = expf(-fabsf(x)), r = 1.f / (1.f + e);
+        const float p = x >= 0.f ? r : e * r;
         const float ddice_dp = -(2.f * y * den - num) * inv_den2;
-        dz[i] = (p - y) * inv_cnt + ddice_dp * p * (1.f - p);
+        return (p - y) * inv_cnt + ddice_dp * p * (1.f - p);
+    };
+    const int64_t quads = count >> 2;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < quads; i += (int64_t)gridDim.x * blockDim.x) {
+        float x[4], y[4], g[4];
+        load_px<4>(z + 4 * i, x);
+        targets4<FLOAT_T>(t, 4 * i, y);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) g[j] = grad(x[j], y[j]);
+        store_px<4>(dz + 4 * i, g);
     }
+    for (int64_t i = 4 * quads + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x)
+        dz[i] = grad(z[i], target_at<FLOAT_T>(t, i));
 }
 
 __global__ void scale_kernel(float* __restrict__ d, int64_t count, const float* __restrict__ sc) {
@@ -340,7 +453,8 @@ __global__ void __launch_bounds__(256) confmat_kernel(const float* __restrict__ 
     __syncthreads();
     const int64_t gpi = hw / PV;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < groups; i += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t n = i / gpi, q = (i % gpi) * PV;
+        const uint32_t iu = (uint32_t)i, nu = iu / (uint32_t)gpi;      // 32-bit: groups < 2^31 (checked on the host)
+        const int64_t n = nu, q = (int64_t)(iu - nu * (uint32_t)gpi) * PV;
         const float* zp = logits + n * c * hw + q;
         int64_t t[PV];
         load_lab<PV>(labels + n * hw + q, t);
@@ -591,12 +705,25 @@ int msx_kd_loss_fwd_bwd(const float* student, const float* teacher, int32_t n, i
     int g;
     if (kind == 0) {
         MSX_REQUIRE(temperature > 0.f, "kd_loss: temperature must be positive");
-        const bool v4 = hw % 4 == 0;
-        const int64_t groups = (int64_t)n * hw / (v4 ? 4 : 1);
+        const bool v8 = hw % 8 == 0 && c <= 4, v4 = hw % 4 == 0;
+        const int64_t groups = (int64_t)n * hw / (v8 ? 8 : (v4 ? 4 : 1));
+        MSX_REQUIRE(groups_ok(groups), "kd_loss: more than 2^31 pixel groups");
         g = loss_grid(groups);
         const float gscale = (float)((double)temperature / total);      // T^2/(NCHW) * 1/T
-        if (v4) { ProfScope ps__(K_LOSS, st, (double)total * (dstudent ? 12.0 : 8.0), 0); kd_kl_kernel<4><<<g, 256, 0, st>>>(student, teacher, c, hw, groups, 1.f / temperature, gscale, dstudent, w); }
-        else { ProfScope ps__(K_LOSS, st, (double)total * (dstudent ? 12.0 : 8.0), 0); kd_kl_kernel<1><<<g, 256, 0, st>>>(student, teacher, c, hw, groups, 1.f / temperature, gscale, dstudent, w); }
+        {
+            ProfScope ps__(K_LOSS, st, (double)total * (dstudent ? 12.0 : 8.0), 0);
+#define MSX_KD(PV, CT) kd_kl_reg_kernel<PV, CT><<<g, 256, 0, st>>>(student, teacher, c, hw, groups, 1.f / temperature, gscale, dstudent, w)
+            if (v8) {
+                if (c <= 2) MSX_KD(8, 2); else MSX_KD(8, 4);
+            } else if (v4) {
+                if (c <= 2) MSX_KD(4, 2); else if (c <= 4) MSX_KD(4, 4); else if (c <= 8) MSX_KD(4, 8);
+                else kd_kl_kernel<4><<<g, 256, 0, st>>>(student, teacher, c, hw, groups, 1.f / temperature, gscale, dstudent, w);
+            } else {
+                if (c <= 2) MSX_KD(1, 2); else if (c <= 4) MSX_KD(1, 4); else if (c <= 8) MSX_KD(1, 8);
+                else kd_kl_kernel<1><<<g, 256, 0, st>>>(student, teacher, c, hw, groups, 1.f / temperature, gscale, dstudent, w);
+            }
+#undef MSX_KD
+        }
         { ProfScope ps__(K_MISC, st, 0, 0); scaled_sum_finalize_kernel<<<1, 256, 0, st>>>(w, g, (double)temperature * temperature / total, loss_out); }
     } else if (kind == 1) {
         const int64_t count = (int64_t)total;
@@ -622,7 +749,7 @@ int msx_dice_bce_loss_fwd_bwd(const float* logits, const void* targets, int labe
     else { ProfScope ps__(K_LOSS, st, (double)pixels * (labels_are_float ? 8.0 : 12.0), 0); dice_bce_reduce_kernel<false><<<g, 256, 0, st>>>(logits, targets, pixels, w); }
     { ProfScope ps__(K_MISC, st, 0, 0); dice_bce_finalize_kernel<<<1, 256, 0, st>>>(w, g, pixels, eps, loss_out); }
     if (dlogits) {
-        const int g2 = loss_grid(pixels);
+        const int g2 = loss_grid((pixels + 3) / 4);
         if (labels_are_float) { ProfScope ps__(K_LOSS, st, (double)pixels * (labels_are_float ? 12.0 : 16.0), 0); dice_bce_grad_kernel<true><<<g2, 256, 0, st>>>(logits, targets, pixels, w, dlogits); }
         else { ProfScope ps__(K_LOSS, st, (double)pixels * (labels_are_float ? 12.0 : 16.0), 0); dice_bce_grad_kernel<false><<<g2, 256, 0, st>>>(logits, targets, pixels, w, dlogits); }
     }
