@@ -84,6 +84,7 @@ size_t msx_conv_packed_bytes(const msx_conv_desc* d);           /* one packed co
 size_t msx_ws_bytes_conv(const msx_conv_desc* d);               /* wgrad split-K partials + BN partials */
 size_t msx_ws_bytes_bn(int32_t channels);                       /* BN / reduction partials */
 size_t msx_ws_bytes_loss(void);
+size_t msx_ws_bytes_ce(int64_t pixels);   /* msx_ws_bytes_loss() + room for one-byte label codes (see msx_ce_loss_fwd_bwd) */
 
 /* Pack fp32 master weights (reference layout) into the [tap][N][K] operand of the given pass. */
 int msx_conv_pack_weights(const msx_conv_desc* d, int mode, const float* w_master, void* packed, void* stream);
@@ -192,7 +193,9 @@ int msx_head_bwd(int dtype, const void* x, int32_t ldx, int32_t n, int32_t h, in
 /* nn.CrossEntropyLoss(ignore_index, reduction, weight) forward AND gradient in one pass
  * (core/loss.py:29-31; called at core/seg_trainer.py:63).  logits [n,c,h*w] fp32 NCHW, labels int64.
  * loss_out: 1 float (MEAN / SUM).  dlogits (nullable) = d loss / d logits for upstream gradient 1.
- * MEAN divides by the summed class weight of non-ignored pixels (NaN if none, like PyTorch). */
+ * MEAN divides by the summed class weight of non-ignored pixels (NaN if none, like PyTorch).
+ * Workspace: msx_ws_bytes_loss() is enough; with msx_ws_bytes_ce(n*hw) (and c <= 255) the weight pre-pass leaves
+ * one-byte label codes there and the main pass does not read the int64 labels a second time. */
 int msx_ce_loss_fwd_bwd(const float* logits, const int64_t* labels, int32_t n, int32_t c, int64_t hw,
                         const float* class_weights, int64_t ignore_index, int reduction,
                         float* loss_out, float* dlogits, void* ws, size_t ws_bytes, void* stream);

@@ -47,6 +47,7 @@ def _load():
         'msx_ws_bytes_conv': (sz, [dp]),
         'msx_ws_bytes_bn': (sz, [i32]),
         'msx_ws_bytes_loss': (sz, []),
+        'msx_ws_bytes_ce': (sz, [i64]),
         'msx_conv_pack_weights': (C.c_int, [dp, C.c_int, p, p, p]),
         'msx_conv2d_fwd': (C.c_int, [dp, p, p, p, p, p, p]),
         'msx_conv2d_bwd': (C.c_int, [dp, p, p, p, p, p, p, p, p, sz, p]),

@@ -5,6 +5,9 @@
 // the same pass.  Sums are accumulated per thread in fp32 over few elements, then in double.
 #include "common.cuh"
 
+#include <map>
+#include <mutex>
+
 namespace msx {
 namespace {
 
@@ -40,6 +43,56 @@ __device__ inline void load_lab(const int64_t* p, int64_t (&t)[PV]) {
     } else t[0] = *p;
 }
 
+// One-byte label codes written by the weight pre-pass: the class index, or 255 for ignored / out-of-range
+// pixels.  The main pass then reads 1 B/pixel instead of the 8 B int64 label a second time.
+// Both loaders hand the kernel 32-bit class indices with -1 for "no contribution", so the per-class
+// compares in the hot loop are single ISETPs (the int64 form made the kernel issue-bound).
+template <int PV>
+__device__ inline void load_codes(const uint8_t* p, int (&t)[PV]) {
+    if constexpr (PV == 8) {
+        const uint2 r = *reinterpret_cast<const uint2*>(p);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { t[j] = (r.x >> (8 * j)) & 255u; t[4 + j] = (r.y >> (8 * j)) & 255u; }
+    } else if constexpr (PV == 4) {
+        const uint32_t r = *reinterpret_cast<const uint32_t*>(p);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) t[j] = (r >> (8 * j)) & 255u;
+    } else t[0] = *p;
+#pragma unroll
+    for (int j = 0; j < PV; ++j) if (t[j] == 255) t[j] = -1;
+}
+template <int PV>
+__device__ inline void load_lab_idx(const int64_t* p, int64_t ignore, int c, int (&ti)[PV]) {
+    int64_t t[PV];
+    load_lab<PV>(p, t);
+#pragma unroll
+    for (int j = 0; j < PV; ++j) ti[j] = (t[j] != ignore && (uint64_t)t[j] < (uint64_t)c) ? (int)t[j] : -1;
+}
+// MUFU-based exp / log / reciprocal.  Arguments of the exp are <= 0 (max-subtracted), so the absolute error
+// of a softmax probability is < 3e-8; lg2.approx is within 2^-22 absolute on the sum (>= 1).
+// The .ftz forms skip the denormal fix-up code of __expf/__logf: results below 2^-126 flush to zero, the
+// arguments of log and rcp are sums >= 1.
+__device__ inline float fast_exp(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x * 1.4426950408889634f));
+    return r;
+}
+__device__ inline float fast_log(float x) {
+    float r;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r * 0.6931471805599453f;
+}
+__device__ inline float fast_rcp(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+template <int PV>
+__device__ inline void store_codes(uint8_t* p, const uint32_t (&cd)[PV]) {
+    if constexpr (PV == 4) *reinterpret_cast<uint32_t*>(p) = cd[0] | (cd[1] << 8) | (cd[2] << 16) | (cd[3] << 24);
+    else p[0] = (uint8_t)cd[0];
+}
+
 __device__ inline double block_sum_d(double v) {
     __shared__ double sh[32];
     return block_sum<double>(v, sh);
@@ -48,14 +101,20 @@ __device__ inline double block_sum_d(double v) {
 // ---- cross entropy --------------------------------------------------------------------------
 template <int PV>
 __global__ void __launch_bounds__(256) ce_wsum_kernel(const int64_t* __restrict__ labels, int64_t groups, int c,
-                                                      const float* __restrict__ cw, int64_t ignore, double* __restrict__ ws) {
+                                                      const float* __restrict__ cw, int64_t ignore, double* __restrict__ ws,
+                                                      uint8_t* __restrict__ codes) {
     float acc = 0.f;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < groups; i += (int64_t)gridDim.x * blockDim.x) {
         int64_t t[PV];
+        uint32_t cd[PV];
         load_lab<PV>(labels + i * PV, t);
 #pragma unroll
-        for (int j = 0; j < PV; ++j)
-            if (t[j] != ignore && t[j] >= 0 && t[j] < c) acc += cw ? cw[t[j]] : 1.f;
+        for (int j = 0; j < PV; ++j) {
+            const bool valid = t[j] != ignore && t[j] >= 0 && t[j] < c;
+            if (valid) acc += cw ? cw[t[j]] : 1.f;
+            cd[j] = valid ? (uint32_t)t[j] : 255u;
+        }
+        if (codes) store_codes<PV>(codes + i * PV, cd);
     }
     const double s = block_sum_d((double)acc);
     if (threadIdx.x == 0) ws[kWsWeight + blockIdx.x] = s;
@@ -67,7 +126,8 @@ template <int PV, int CT, int MODE>
 __global__ void __launch_bounds__(256) ce_kernel(const float* __restrict__ logits, const int64_t* __restrict__ labels,
                                                  int c, int64_t hw, int64_t groups, const float* __restrict__ cw, int64_t ignore,
                                                  int nwpart, int use_denom, const float* __restrict__ coef_pix,
-                                                 float* __restrict__ out_pix, float* __restrict__ dlogits, double* __restrict__ ws) {
+                                                 float* __restrict__ out_pix, float* __restrict__ dlogits, double* __restrict__ ws,
+                                                 const uint8_t* __restrict__ codes) {
     double inv_denom = 1.0;
     if (MODE == 0 && use_denom) {
         // every CTA re-reduces the (<= 1184) weight partials: cheaper than one more launch
@@ -87,8 +147,9 @@ __global__ void __launch_bounds__(256) ce_kernel(const float* __restrict__ logit
         const uint32_t iu = (uint32_t)i, nu = iu / (uint32_t)gpi;      // 32-bit: groups < 2^31 (checked on the host)
         const int64_t n = nu, q = (int64_t)(iu - nu * (uint32_t)gpi) * PV;
         const float* zp = logits + n * c * hw + q;
-        int64_t t[PV];
-        load_lab<PV>(labels + n * hw + q, t);
+        int t[PV];
+        if (codes) load_codes<PV>(codes + n * hw + q, t);
+        else load_lab_idx<PV>(labels + n * hw + q, ignore, c, t);
         float z[CT > 0 ? CT : 1][PV];
         float mx[PV], se[PV], zt[PV];
 #pragma unroll
@@ -107,7 +168,7 @@ __global__ void __launch_bounds__(256) ce_kernel(const float* __restrict__ logit
 #pragma unroll
                     for (int j = 0; j < PV; ++j) {
                         if (t[j] == k) zt[j] = z[k][j];
-                        z[k][j] = expf(z[k][j] - mx[j]);          // z now holds exp(z - max): reused by the gradient
+                        z[k][j] = fast_exp(z[k][j] - mx[j]);      // z now holds exp(z - max): reused by the gradient
                         se[j] += z[k][j];
                     }
                 }
@@ -123,28 +184,24 @@ __global__ void __launch_bounds__(256) ce_kernel(const float* __restrict__ logit
                 load_px<PV>(zp + k * hw, v);
 #pragma unroll
                 for (int j = 0; j < PV; ++j) {
-                    se[j] += expf(v[j] - mx[j]);
+                    se[j] += fast_exp(v[j] - mx[j]);
                     if (t[j] == k) zt[j] = v[j];
                 }
             }
         }
         float wt[PV], lp[PV], up[PV];
-        bool vld[PV];
         if (MODE == 2) load_px<PV>(coef_pix + n * hw + q, up);
 #pragma unroll
         for (int j = 0; j < PV; ++j) {
-            const bool valid = t[j] != ignore && t[j] >= 0 && t[j] < c;
-            vld[j] = valid;
-            wt[j] = valid ? (cw ? cw[t[j]] : 1.f) : 0.f;
-            const float lse = mx[j] + logf(se[j]);
-            lp[j] = valid ? wt[j] * (lse - zt[j]) : 0.f;
+            wt[j] = t[j] >= 0 ? (cw ? cw[t[j]] : 1.f) : 0.f;
+            lp[j] = t[j] >= 0 ? wt[j] * ((mx[j] + fast_log(se[j])) - zt[j]) : 0.f;
             lacc += lp[j];
             if (MODE == 0) up[j] = invd;
         }
         if (MODE == 1) { store_px<PV>(out_pix + n * hw + q, lp); continue; }
         float rse[PV];
 #pragma unroll
-        for (int j = 0; j < PV; ++j) rse[j] = 1.f / se[j];
+        for (int j = 0; j < PV; ++j) { rse[j] = fast_rcp(se[j]); wt[j] = t[j] >= 0 ? wt[j] * up[j] : 0.f; }   // exactly 0 on ignored pixels
         if (dlogits) {
             float* gp = dlogits + n * c * hw + q;
             if constexpr (CT > 0) {
@@ -155,7 +212,7 @@ __global__ void __launch_bounds__(256) ce_kernel(const float* __restrict__ logit
 #pragma unroll
                         for (int j = 0; j < PV; ++j) {
                             const float sm = z[k][j] * rse[j];
-                            g[j] = vld[j] ? wt[j] * (sm - (t[j] == k ? 1.f : 0.f)) * up[j] : 0.f;
+                            g[j] = wt[j] * (t[j] == k ? sm - 1.f : sm);
                         }
                         store_px<PV>(gp + k * hw, g);
                     }
@@ -165,8 +222,8 @@ __global__ void __launch_bounds__(256) ce_kernel(const float* __restrict__ logit
                     load_px<PV>(zp + k * hw, v);
 #pragma unroll
                     for (int j = 0; j < PV; ++j) {
-                        const float sm = expf(v[j] - mx[j]) / se[j];
-                        g[j] = vld[j] ? wt[j] * (sm - (t[j] == k ? 1.f : 0.f)) * up[j] : 0.f;
+                        const float sm = fast_exp(v[j] - mx[j]) * rse[j];
+                        g[j] = wt[j] * (t[j] == k ? sm - 1.f : sm);
                     }
                     store_px<PV>(gp + k * hw, g);
                 }
@@ -197,16 +254,37 @@ inline int loss_grid(int64_t groups) {
     return (int)g;
 }
 
+// Grid = exactly the CTAs that are resident at once (SMs x occupancy), each striding over the pixel groups:
+// with a fixed 8 CTAs/SM the register-heavy variants (3 resident) ran 2.67 waves and lost the last third.
+int resident_grid(const void* kernel, size_t smem, int64_t groups) {
+    static std::mutex mu;
+    static std::map<std::pair<const void*, size_t>, int> cache;
+    int occ = 0;
+    {
+        std::lock_guard<std::mutex> lk(mu);
+        auto it = cache.find({kernel, smem});
+        if (it != cache.end()) occ = it->second;
+        else {
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, 256, smem) != cudaSuccess || occ < 1) { (void)cudaGetLastError(); occ = 1; }
+            if (occ > 8) occ = 8;
+            cache[{kernel, smem}] = occ;
+        }
+    }
+    int64_t g = cdiv64(groups, 256);
+    if (g < 1) g = 1;
+    if (g > (int64_t)kNumSMs * occ) g = (int64_t)kNumSMs * occ;
+    return (int)g;
+}
+
 template <int MODE>
 int ce_dispatch(const float* logits, const int64_t* labels, int n, int c, int64_t hw, const float* cw, int64_t ignore,
                 int nwpart, int use_denom, const float* coef, float* out_pix, float* dlogits, double* ws, int* grid_out,
-                cudaStream_t st) {
+                cudaStream_t st, const uint8_t* codes = nullptr) {
     const bool v8 = hw % 8 == 0 && c <= 4, v4 = hw % 4 == 0;
     const int64_t groups = (int64_t)n * hw / (v8 ? 8 : (v4 ? 4 : 1));
     if (!groups_ok(groups)) return set_error(MSX_ERR_UNSUPPORTED, "loss: more than 2^31 pixel groups");
-    const int g = loss_grid(groups);
-    *grid_out = g;
-#define MSX_CE_LAUNCH(PV, CT) { ProfScope ps__(K_LOSS, st, (double)n * hw * (MODE == 1 ? 4.0 * c + 12.0 : (MODE == 2 ? 8.0 * c + 12.0 : (dlogits ? 8.0 * c + 8.0 : 4.0 * c + 8.0))), 0); ce_kernel<PV, CT, MODE><<<g, 256, 0, st>>>(logits, labels, c, hw, groups, cw, ignore, nwpart, use_denom, coef, out_pix, dlogits, ws); }
+    int g = 1;
+#define MSX_CE_LAUNCH(PV, CT) { g = resident_grid((const void*)ce_kernel<PV, CT, MODE>, 0, groups); ProfScope ps__(K_LOSS, st, (double)n * hw * (MODE == 1 ? 4.0 * c + 12.0 : (MODE == 2 ? 8.0 * c + 12.0 : (dlogits ? 8.0 * c + 8.0 : 4.0 * c + 8.0))), 0); ce_kernel<PV, CT, MODE><<<g, 256, 0, st>>>(logits, labels, c, hw, groups, cw, ignore, nwpart, use_denom, coef, out_pix, dlogits, ws, codes); }
     if (v8) {
         if (c <= 2) MSX_CE_LAUNCH(8, 2) else MSX_CE_LAUNCH(8, 4)
     } else if (v4) {
@@ -215,6 +293,7 @@ int ce_dispatch(const float* logits, const int64_t* labels, int n, int c, int64_
         if (c <= 2) MSX_CE_LAUNCH(1, 2) else if (c <= 4) MSX_CE_LAUNCH(1, 4) else if (c <= 8) MSX_CE_LAUNCH(1, 8) else MSX_CE_LAUNCH(1, 0)
     }
 #undef MSX_CE_LAUNCH
+    *grid_out = g;
     MSX_LAUNCH_CHECK();
     return MSX_OK;
 }
@@ -250,6 +329,7 @@ __global__ void __launch_bounds__(256) kd_kl_reg_kernel(const float* __restrict_
                     ms[j] = fmaxf(ms[j], a[k][j]); mt[j] = fmaxf(mt[j], b[k][j]);
                 }
             }
+        // a, b become the max-shifted logits; ea, eb their exponentials (kept for softmax and gradient)
         float ea[CT][PV], eb[CT][PV];
 #pragma unroll
         for (int k = 0; k < CT; ++k)
@@ -257,13 +337,13 @@ __global__ void __launch_bounds__(256) kd_kl_reg_kernel(const float* __restrict_
 #pragma unroll
                 for (int j = 0; j < PV; ++j) {
                     a[k][j] -= ms[j]; b[k][j] -= mt[j];
-                    ea[k][j] = expf(a[k][j]); eb[k][j] = expf(b[k][j]);
+                    ea[k][j] = fast_exp(a[k][j]); eb[k][j] = fast_exp(b[k][j]);
                     es[j] += ea[k][j]; et[j] += eb[k][j];
                 }
             }
-        float ls[PV], lt[PV], rs[PV], rt[PV];
+        float dl[PV], rs[PV], rt[PV];      // dl = log(sum_s) - log(sum_t): logq - logp = (b - a) + dl
 #pragma unroll
-        for (int j = 0; j < PV; ++j) { ls[j] = logf(es[j]); lt[j] = logf(et[j]); rs[j] = 1.f / es[j]; rt[j] = 1.f / et[j]; }
+        for (int j = 0; j < PV; ++j) { dl[j] = fast_log(es[j]) - fast_log(et[j]); rs[j] = fast_rcp(es[j]) * gscale; rt[j] = fast_rcp(et[j]); }
 #pragma unroll
         for (int k = 0; k < CT; ++k)
             if (k < c) {
@@ -271,8 +351,8 @@ __global__ void __launch_bounds__(256) kd_kl_reg_kernel(const float* __restrict_
 #pragma unroll
                 for (int j = 0; j < PV; ++j) {
                     const float qq = eb[k][j] * rt[j];
-                    if (qq > 0.f) lacc += qq * ((b[k][j] - lt[j]) - (a[k][j] - ls[j]));
-                    g[j] = (ea[k][j] * rs[j] - qq) * gscale;
+                    if (qq > 0.f) lacc = fmaf(qq, (b[k][j] - a[k][j]) + dl[j], lacc);
+                    g[j] = fmaf(ea[k][j], rs[j], -qq * gscale);
                 }
                 if (ds) store_px<PV>(ds + n * c * hw + q + k * hw, g);
             }
@@ -369,9 +449,9 @@ __global__ void __launch_bounds__(256) dice_bce_reduce_kernel(const float* __res
                                                               double* __restrict__ ws) {
     float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
     auto body = [&](float x, float y) {
-        const float e = expf(-fabsf(x));                        // one exp serves softplus and sigmoid
-        const float sp = fmaxf(x, 0.f) + log1pf(e);
-        const float r = 1.f / (1.f + e);
+        const float e = fast_exp(-fabsf(x));                    // one exp serves softplus and sigmoid
+        const float sp = fmaxf(x, 0.f) + fast_log(1.f + e);     // 1 + e in [1, 2]: absolute error < 2e-7
+        const float r = fast_rcp(1.f + e);
         const float p = x >= 0.f ? r : e * r;
         a0 += sp - x * y; a1 += p * y; a2 += p; a3 += y;
     };
@@ -416,7 +496,7 @@ __global__ void __launch_bounds__(256) dice_bce_grad_kernel(const float* __restr
     const float num = (float)ws[kWsScalars + 0], den = (float)ws[kWsScalars + 1];
     const float inv_cnt = 1.f / (float)count, inv_den2 = 1.f / (den * den);
     auto grad = [&](float x, float y) {
-        const float e = expf(-fabsf(x)), r = 1.f / (1.f + e);
+        const float e = fast_exp(-fabsf(x)), r = fast_rcp(1.f + e);
         const float p = x >= 0.f ? r : e * r;
         const float ddice_dp = -(2.f * y * den - num) * inv_den2;
         return (p - y) * inv_cnt + ddice_dp * p * (1.f - p);
@@ -624,6 +704,8 @@ using namespace msx;
 extern "C" {
 
 size_t msx_ws_bytes_loss(void) { return (size_t)kWsDoubles * sizeof(double) + 256 * sizeof(unsigned int); }
+static size_t ce_codes_offset() { return (msx_ws_bytes_loss() + 255) & ~(size_t)255; }
+size_t msx_ws_bytes_ce(int64_t pixels) { return ce_codes_offset() + (size_t)((pixels + 15) & ~(int64_t)15); }
 
 int msx_ce_loss_fwd_bwd(const float* logits, const int64_t* labels, int32_t n, int32_t c, int64_t hw,
                         const float* class_weights, int64_t ignore_index, int reduction, float* loss_out, float* dlogits,
@@ -636,15 +718,18 @@ int msx_ce_loss_fwd_bwd(const float* logits, const int64_t* labels, int32_t n, i
     double* w = static_cast<double*>(ws);
     const int use_denom = reduction == MSX_REDUCE_MEAN;
     int nw = 0, nl = 0;
+    uint8_t* codes = nullptr;
     if (use_denom) {
+        // With the larger msx_ws_bytes_ce() workspace the pre-pass also leaves one-byte label codes behind.
+        if (c <= 255 && ws_bytes >= msx_ws_bytes_ce((int64_t)n * hw)) codes = static_cast<uint8_t*>(ws) + ce_codes_offset();
         const bool v4 = hw % 4 == 0;
         const int64_t groups = (int64_t)n * hw / (v4 ? 4 : 1);
         nw = loss_grid(groups);
-        if (v4) { ProfScope ps__(K_LOSS, st, 0, 0); ce_wsum_kernel<4><<<nw, 256, 0, st>>>(labels, groups, c, class_weights, ignore_index, w); }
-        else { ProfScope ps__(K_LOSS, st, 0, 0); ce_wsum_kernel<1><<<nw, 256, 0, st>>>(labels, groups, c, class_weights, ignore_index, w); }
+        if (v4) { ProfScope ps__(K_LOSS, st, 0, 0); ce_wsum_kernel<4><<<nw, 256, 0, st>>>(labels, groups, c, class_weights, ignore_index, w, codes); }
+        else { ProfScope ps__(K_LOSS, st, 0, 0); ce_wsum_kernel<1><<<nw, 256, 0, st>>>(labels, groups, c, class_weights, ignore_index, w, codes); }
         MSX_LAUNCH_CHECK();
     }
-    MSX_TRY(ce_dispatch<0>(logits, labels, n, c, hw, class_weights, ignore_index, nw, use_denom, nullptr, nullptr, dlogits, w, &nl, st));
+    MSX_TRY(ce_dispatch<0>(logits, labels, n, c, hw, class_weights, ignore_index, nw, use_denom, nullptr, nullptr, dlogits, w, &nl, st, codes));
     { ProfScope ps__(K_MISC, st, 0, 0); ce_finalize_kernel<<<1, 256, 0, st>>>(w, nw, nl, use_denom, loss_out); }
     MSX_LAUNCH_CHECK();
     return MSX_OK;
@@ -708,19 +793,19 @@ int msx_kd_loss_fwd_bwd(const float* student, const float* teacher, int32_t n, i
         const bool v8 = hw % 8 == 0 && c <= 4, v4 = hw % 4 == 0;
         const int64_t groups = (int64_t)n * hw / (v8 ? 8 : (v4 ? 4 : 1));
         MSX_REQUIRE(groups_ok(groups), "kd_loss: more than 2^31 pixel groups");
-        g = loss_grid(groups);
+        g = 1;
         const float gscale = (float)((double)temperature / total);      // T^2/(NCHW) * 1/T
         {
             ProfScope ps__(K_LOSS, st, (double)total * (dstudent ? 12.0 : 8.0), 0);
-#define MSX_KD(PV, CT) kd_kl_reg_kernel<PV, CT><<<g, 256, 0, st>>>(student, teacher, c, hw, groups, 1.f / temperature, gscale, dstudent, w)
+#define MSX_KD(PV, CT) g = resident_grid((const void*)kd_kl_reg_kernel<PV, CT>, 0, groups), kd_kl_reg_kernel<PV, CT><<<g, 256, 0, st>>>(student, teacher, c, hw, groups, 1.f / temperature, gscale, dstudent, w)
             if (v8) {
                 if (c <= 2) MSX_KD(8, 2); else MSX_KD(8, 4);
             } else if (v4) {
                 if (c <= 2) MSX_KD(4, 2); else if (c <= 4) MSX_KD(4, 4); else if (c <= 8) MSX_KD(4, 8);
-                else kd_kl_kernel<4><<<g, 256, 0, st>>>(student, teacher, c, hw, groups, 1.f / temperature, gscale, dstudent, w);
+                else g = resident_grid((const void*)kd_kl_kernel<4>, 0, groups), kd_kl_kernel<4><<<g, 256, 0, st>>>(student, teacher, c, hw, groups, 1.f / temperature, gscale, dstudent, w);
             } else {
                 if (c <= 2) MSX_KD(1, 2); else if (c <= 4) MSX_KD(1, 4); else if (c <= 8) MSX_KD(1, 8);
-                else kd_kl_kernel<1><<<g, 256, 0, st>>>(student, teacher, c, hw, groups, 1.f / temperature, gscale, dstudent, w);
+                else g = resident_grid((const void*)kd_kl_kernel<1>, 0, groups), kd_kl_kernel<1><<<g, 256, 0, st>>>(student, teacher, c, hw, groups, 1.f / temperature, gscale, dstudent, w);
             }
 #undef MSX_KD
         }
@@ -743,13 +828,15 @@ int msx_dice_bce_loss_fwd_bwd(const float* logits, const void* targets, int labe
     if (ws_bytes < msx_ws_bytes_loss()) return set_error(MSX_ERR_WORKSPACE, "dice_bce: workspace too small");
     cudaStream_t st = as_stream(stream);
     double* w = static_cast<double*>(ws);
-    int g = loss_grid(pixels);
+    int g = labels_are_float ? resident_grid((const void*)dice_bce_reduce_kernel<true>, 0, (pixels + 3) / 4)
+                             : resident_grid((const void*)dice_bce_reduce_kernel<false>, 0, (pixels + 3) / 4);
     if (g > kLossMaxBlocks / 2) g = kLossMaxBlocks / 2;
     if (labels_are_float) { ProfScope ps__(K_LOSS, st, (double)pixels * (labels_are_float ? 8.0 : 12.0), 0); dice_bce_reduce_kernel<true><<<g, 256, 0, st>>>(logits, targets, pixels, w); }
     else { ProfScope ps__(K_LOSS, st, (double)pixels * (labels_are_float ? 8.0 : 12.0), 0); dice_bce_reduce_kernel<false><<<g, 256, 0, st>>>(logits, targets, pixels, w); }
     { ProfScope ps__(K_MISC, st, 0, 0); dice_bce_finalize_kernel<<<1, 256, 0, st>>>(w, g, pixels, eps, loss_out); }
     if (dlogits) {
-        const int g2 = loss_grid((pixels + 3) / 4);
+        const int g2 = labels_are_float ? resident_grid((const void*)dice_bce_grad_kernel<true>, 0, (pixels + 3) / 4)
+                                        : resident_grid((const void*)dice_bce_grad_kernel<false>, 0, (pixels + 3) / 4);
         if (labels_are_float) { ProfScope ps__(K_LOSS, st, (double)pixels * (labels_are_float ? 12.0 : 16.0), 0); dice_bce_grad_kernel<true><<<g2, 256, 0, st>>>(logits, targets, pixels, w, dlogits); }
         else { ProfScope ps__(K_LOSS, st, (double)pixels * (labels_are_float ? 12.0 : 16.0), 0); dice_bce_grad_kernel<false><<<g2, 256, 0, st>>>(logits, targets, pixels, w, dlogits); }
     }
@@ -770,8 +857,8 @@ int msx_confmat_update(const float* logits, const int64_t* labels, int32_t n, in
     MSX_REQUIRE(c >= 1 && c <= 64, "confmat: num_classes %d not in [1,64]", c);
     const bool v4 = hw % 4 == 0;
     const int64_t groups = (int64_t)n * hw / (v4 ? 4 : 1);
-    const int g = loss_grid(groups);
     const size_t smem = (c <= 4 ? (size_t)c * c * 256 : (size_t)c * c) * sizeof(unsigned int);
+    const int g = v4 ? resident_grid((const void*)confmat_kernel<4>, smem, groups) : resident_grid((const void*)confmat_kernel<1>, smem, groups);
     auto* cm = reinterpret_cast<unsigned long long*>(confmat);
     if (v4) { ProfScope ps__(K_CONFMAT, as_stream(stream), (double)n * hw * (4.0 * c + 8.0), 0); confmat_kernel<4><<<g, 256, smem, as_stream(stream)>>>(logits, labels, c, hw, groups, ignore_index, cm, bad_label_flag); }
     else { ProfScope ps__(K_CONFMAT, as_stream(stream), (double)n * hw * (4.0 * c + 8.0), 0); confmat_kernel<1><<<g, 256, smem, as_stream(stream)>>>(logits, labels, c, hw, groups, ignore_index, cm, bad_label_flag); }

@@ -74,7 +74,7 @@ class CrossEntropyLoss(nn.Module):
         w = None if self.weight is None else self.weight.to(dev)
         if self.reduction == 'none':
             return _CENone.apply(logits, labels, w, self.ignore_index)
-        ws = L.workspace(lib.msx_ws_bytes_loss(), dev)
+        ws = L.workspace(lib.msx_ws_bytes_ce(n * hw), dev)
         red = L.REDUCE[self.reduction]
 
         def run(loss, grad):

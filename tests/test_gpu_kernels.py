@@ -319,6 +319,29 @@ def test_ce_vs_oracle_shapes(shape):
     assert rel(per, refp) < 1e-6 and rel(zz.grad, zd.grad) < 1e-5
 
 
+@pytest.mark.parametrize('shape', [(2, 2, 8, 16), (3, 3, 6, 6), (2, 5, 5, 3), (1, 12, 4, 8)])
+def test_ce_label_code_workspace_is_bit_identical(shape):
+    """msx_ws_bytes_ce() workspace (one-byte label codes) vs the small workspace: same bits, incl. ignored,
+    out-of-range and class-weighted pixels."""
+    from medical_segmentation_pytorch_b200 import _lib as L
+    torch.manual_seed(7)
+    n, c, h, w = shape
+    z = (torch.randn(shape) * 3).to(DEV)
+    t = torch.randint(0, c, (n, h, w))
+    t[torch.rand(n, h, w) < 0.2] = 255
+    t[0, 0, 0] = c + 3                      # out of range: treated as ignored by both paths
+    t = t.to(DEV)
+    cw = (torch.rand(c) + 0.5).to(DEV)
+    res = []
+    for nbytes in (L.lib.msx_ws_bytes_loss(), L.lib.msx_ws_bytes_ce(n * h * w)):
+        ws = torch.zeros(nbytes, dtype=torch.uint8, device=DEV)
+        loss, grad = torch.empty((), device=DEV), torch.empty_like(z)
+        L.check(L.lib.msx_ce_loss_fwd_bwd(L.ptr(z), L.ptr(t), n, c, h * w, L.ptr(cw), 255, L.REDUCE['mean'],
+                                          L.ptr(loss), L.ptr(grad), L.ptr(ws), ws.numel(), L.stream()))
+        res.append((loss.cpu(), grad.cpu()))
+    assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
+
+
 def test_ce_all_ignored_is_nan_with_zero_grad():
     import medical_segmentation_pytorch_b200 as msx
     fn = msx.get_loss_fn(Cfg(), DEV)

@@ -18,7 +18,7 @@ class Cfg:
 
 
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-for n in (16, 256):
+for n in [int(v) for v in os.environ.get('MB_N', '16,256').split(',')]:
     h = 352
     px = n * h * h
     z = torch.randn(n, 2, h, h, device=dev, requires_grad=True)
