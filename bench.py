@@ -112,6 +112,38 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def loss_metric_leg(msx, _lib, dev, pk, n=256, h=352, reps=5):
+    """north_star's second figure: algorithmic GB/s of the loss / metric kernels (SURVEY 8d bytes per pixel) on a
+    working set far beyond L2 (n x h x h pixels), all launches of one call summed, L2 evicted by reads between calls."""
+    import torch
+    class Cfg:
+        num_class, ignore_index, class_weights, loss_type, reduction, ohem_thrs = 2, 255, None, 'ce', 'mean', 0.7
+        kd_loss_type, kd_temperature = 'kl_div', 4.0
+    px = n * h * h
+    z = torch.randn(n, 2, h, h, device=dev, requires_grad=True)          # requires_grad: the fused kernels also emit the gradient
+    z1 = torch.randn(n, 1, h, h, device=dev, requires_grad=True)
+    zt = torch.randn(n, 2, h, h, device=dev)
+    t = (torch.rand(n, h, h, device=dev) > 0.8).long()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    ce, dice, metric = msx.get_loss_fn(Cfg, dev), msx.DiceBCELoss(), msx.get_seg_metrics(Cfg, 'iou').to(dev)
+    jobs = {'ce_fwd_bwd': (lambda: ce(z, t), 24), 'kd_kl_fwd_bwd': (lambda: msx.kd_loss_fn(Cfg, z, zt), 24),
+            'dice_bce_fwd_bwd': (lambda: dice(z1, t), 28), 'confmat_update': (lambda: metric.update(z.detach(), t), 16)}
+    out = {'pixels': px, 'peak_GBps': pk['hbm_gbs'], 'how': f'{reps} calls each, per-launch CUDA events, every launch of the call counted'}
+    for name, (fn, bpp) in jobs.items():
+        fn()
+        torch.cuda.synchronize()
+        _lib.profile_collect()
+        _lib.lib.msx_profile_enable(1)
+        for _ in range(reps):
+            flush.sum()
+            fn()
+        prof = _lib.profile_collect()
+        _lib.lib.msx_profile_enable(0)
+        ms = sum(v['ms'] for v in prof.values()) / reps
+        out[name] = {'bytes_per_px': bpp, 'us': ms * 1e3, 'GBps': px * bpp / ms / 1e6, 'frac': px * bpp / ms / 1e6 / pk['hbm_gbs']}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
@@ -305,6 +337,7 @@ def main():
                          'avg_launch_us': tv['ms'] / tv['launches'] * 1e3, 'launches_per_step': tv['launches'] // args.profile_steps,
                          'share_of_step': tv['ms'] / tot_ms,
                          'how': f'{args.profile_steps} extra step(s) after the timed region with per-launch CUDA events (msx_profile_*)'})
+    loss_metric = loss_metric_leg(msx, _lib, dev, pk) if world == 1 else None
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
         cpu_baseline, _ = cpu_reference_leg(args.model, 2, 1, batch=2, hw=S)
@@ -325,6 +358,7 @@ def main():
                            'tensor_frac': value / world * gflop_img / 1e3 / pk['tf'],
                            'hbm_frac': value / world * gb_img * (1 if bf16 else 2) / pk['hbm_gbs']},
         'kernels': kernels,
+        'loss_metric_gbs': loss_metric,
     }
     print(json.dumps(line), flush=True)
     leave()

@@ -89,9 +89,27 @@ size_t msx_ws_bytes_ce(int64_t pixels);   /* msx_ws_bytes_loss() + room for one-
 /* Pack fp32 master weights (reference layout) into the [tap][N][K] operand of the given pass. */
 int msx_conv_pack_weights(const msx_conv_desc* d, int mode, const float* w_master, void* packed, void* stream);
 
+/* Pack plan: every conv weight of a model (both passes) repacked by ONE launch per step instead of one launch
+ * per conv and pass.  No counterpart in the reference (its convs read the master weights directly); the
+ * callers are models/unet.py:30-41 / models/ducknet.py:38-50 forward, once before the first layer.
+ * An item names a master weight [cout,cin,kh,kw] (Conv2d) or [cin,cout,kh,kw] (ConvTranspose2d, transposed=1),
+ * the pass (MSX_PACK_FPROP / MSX_PACK_DGRAD) and the destination (>= taps*round16(N)*round8(K) elements, N/K the
+ * operand dims of that pass).  build copies a device table (synchronously: start-up work, not to be called
+ * under stream capture); run launches the kernel.  Convs then take w_master = NULL and the pre-packed
+ * operand as w_packed in msx_conv2d_fwd/bwd and msx_conv_bn_act_fwd/bwd. */
+typedef struct msx_pack_item {
+    const float* w_master;
+    void* packed;
+    int32_t cout, cin, kh, kw, transposed, mode;
+} msx_pack_item;
+size_t msx_conv_pack_plan_bytes(const msx_pack_item* host_items, int32_t count);
+int msx_conv_pack_plan_build(const msx_pack_item* host_items, int32_t count, void* table, size_t table_bytes, int32_t* chunks_out);
+int msx_conv_pack_plan_run(int dtype, const void* table, int32_t count, int32_t chunks, void* stream);
+
 /* Plain convolution (no BN): ResidualBlock.upper_branch conv1x1, models/ducknet.py:93,104.
  * bias may be NULL.  fwd: y = op(x, W) (+bias).  bwd: dx (nullable), dw (fp32, reference layout),
- * dbias (nullable). w_packed: scratch of msx_conv_packed_bytes. */
+ * dbias (nullable). w_packed: scratch of msx_conv_packed_bytes; with w_master == NULL it must already hold the
+ * operand of the pass that reads it (fwd: MSX_PACK_FPROP, bwd: MSX_PACK_DGRAD), see msx_conv_pack_plan_*. */
 int msx_conv2d_fwd(const msx_conv_desc* d, const void* x, const float* w_master, const float* bias,
                    void* w_packed, void* y, void* stream);
 int msx_conv2d_bwd(const msx_conv_desc* d, const void* x, const float* w_master, const void* dy,

@@ -12,6 +12,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, 'libmsx.so')
 
 F32, BF16 = 0, 1
+PACK_FPROP, PACK_DGRAD = 0, 1
 ENGINE_AUTO, ENGINE_SIMT, ENGINE_TCGEN05 = 0, 1, 2
 REDUCE = {'mean': 0, 'sum': 1, 'none': 2}
 
@@ -20,6 +21,11 @@ class ConvDesc(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         'n', 'h', 'w', 'cin', 'oh', 'ow', 'cout', 'kh', 'kw', 'stride', 'dil', 'pad_h', 'pad_w',
         'ldx', 'ldy', 'transposed', 'dtype', 'engine')]
+
+
+class PackItem(C.Structure):
+    _fields_ = [('w_master', C.c_void_p), ('packed', C.c_void_p)] + [(n, C.c_int32) for n in (
+        'cout', 'cin', 'kh', 'kw', 'transposed', 'mode')]
 
 
 class MsxError(RuntimeError):
@@ -49,6 +55,9 @@ def _load():
         'msx_ws_bytes_loss': (sz, []),
         'msx_ws_bytes_ce': (sz, [i64]),
         'msx_conv_pack_weights': (C.c_int, [dp, C.c_int, p, p, p]),
+        'msx_conv_pack_plan_bytes': (sz, [p, i32]),
+        'msx_conv_pack_plan_build': (C.c_int, [p, i32, p, sz, p]),
+        'msx_conv_pack_plan_run': (C.c_int, [C.c_int, p, i32, i32, p]),
         'msx_conv2d_fwd': (C.c_int, [dp, p, p, p, p, p, p]),
         'msx_conv2d_bwd': (C.c_int, [dp, p, p, p, p, p, p, p, p, sz, p]),
         'msx_conv_bn_act_fwd': (C.c_int, [dp, p, p, p, p, p, p, p, p, f32, f32, C.c_int, C.c_int,

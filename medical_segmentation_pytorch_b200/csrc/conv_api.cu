@@ -6,6 +6,9 @@ struct GatherGeom;
 int validate_desc(const msx_conv_desc* d);
 size_t conv_packed_elems(const msx_conv_desc* d);
 int conv_pack_launch(const msx_conv_desc* d, int mode, const float* w, void* packed, cudaStream_t st);
+size_t conv_pack_plan_bytes(const msx_pack_item* items, int count);
+int conv_pack_plan_build(const msx_pack_item* items, int count, void* table, size_t table_bytes, int* chunks_out);
+int conv_pack_plan_run(int dtype, const void* table, int count, int chunks, double bytes, cudaStream_t st);
 int conv_gather_simt(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
                      void* dst, cudaStream_t st);
 size_t conv_wgrad_ws_bytes(const msx_conv_desc* d);
@@ -66,22 +69,40 @@ int msx_conv_pack_weights(const msx_conv_desc* d, int mode, const float* w_maste
     return conv_pack_launch(d, mode, w_master, packed, as_stream(stream));
 }
 
+size_t msx_conv_pack_plan_bytes(const msx_pack_item* host_items, int32_t count) {
+    if (!host_items || count <= 0) return 0;
+    return conv_pack_plan_bytes(host_items, count);
+}
+int msx_conv_pack_plan_build(const msx_pack_item* host_items, int32_t count, void* table, size_t table_bytes, int32_t* chunks_out) {
+    MSX_REQUIRE(host_items && count > 0 && table && chunks_out, "pack_plan_build: bad arguments");
+    int chunks = 0;
+    MSX_TRY(conv_pack_plan_build(host_items, count, table, table_bytes, &chunks));
+    *chunks_out = chunks;
+    return MSX_OK;
+}
+int msx_conv_pack_plan_run(int dtype, const void* table, int32_t count, int32_t chunks, void* stream) {
+    MSX_REQUIRE(table && count > 0 && chunks > 0, "pack_plan_run: bad arguments");
+    MSX_REQUIRE(dtype == MSX_F32 || dtype == MSX_BF16, "pack_plan_run: bad dtype");
+    // algorithmic bytes: every chunk reads <= 1024 pairs x taps floats and writes as many elements (upper bound)
+    return conv_pack_plan_run(dtype, table, count, chunks, 0.0, as_stream(stream));
+}
+
 int msx_conv2d_fwd(const msx_conv_desc* d, const void* x, const float* w_master, const float* bias, void* w_packed,
                    void* y, void* stream) {
     MSX_TRY(validate_desc(d));
-    MSX_REQUIRE(x && w_master && w_packed && y, "conv2d_fwd: null pointer");
+    MSX_REQUIRE(x && w_packed && y, "conv2d_fwd: null pointer");
     cudaStream_t st = as_stream(stream);
-    MSX_TRY(conv_pack_launch(d, MSX_PACK_FPROP, w_master, w_packed, st));
+    if (w_master) MSX_TRY(conv_pack_launch(d, MSX_PACK_FPROP, w_master, w_packed, st));   // NULL: w_packed is pre-packed
     return conv_gather(d, true, x, w_packed, bias, y, st);
 }
 
 int msx_conv2d_bwd(const msx_conv_desc* d, const void* x, const float* w_master, const void* dy, void* w_packed,
                    void* dx, float* dw, float* dbias, void* ws, size_t ws_bytes, void* stream) {
     MSX_TRY(validate_desc(d));
-    MSX_REQUIRE(x && w_master && dy && w_packed, "conv2d_bwd: null pointer");
+    MSX_REQUIRE(x && dy && w_packed, "conv2d_bwd: null pointer");
     cudaStream_t st = as_stream(stream);
     if (dx) {
-        MSX_TRY(conv_pack_launch(d, MSX_PACK_DGRAD, w_master, w_packed, st));
+        if (w_master) MSX_TRY(conv_pack_launch(d, MSX_PACK_DGRAD, w_master, w_packed, st));
         MSX_TRY(conv_gather(d, false, dy, w_packed, nullptr, dx, st));
     }
     if (dw) MSX_TRY(conv_wgrad(d, x, dy, dw, ws, ws_bytes, st));
@@ -96,12 +117,12 @@ int msx_conv_bn_act_fwd(const msx_conv_desc* d, const void* x, const float* w_ma
                         void* w_packed, void* y_raw, void* z, int32_t ldz, float* save_mean, float* save_invstd,
                         void* ws, size_t ws_bytes, void* stream) {
     MSX_TRY(validate_desc(d));
-    MSX_REQUIRE(x && w_master && gamma && beta && w_packed && y_raw && z && save_mean && save_invstd, "conv_bn_act_fwd: null pointer");
+    MSX_REQUIRE(x && gamma && beta && w_packed && y_raw && z && save_mean && save_invstd, "conv_bn_act_fwd: null pointer");
     MSX_REQUIRE(training || (running_mean && running_var), "conv_bn_act_fwd: eval mode needs running statistics");
     if (ws_bytes < bn_partials_bytes(d->cout)) return set_error(MSX_ERR_WORKSPACE, "conv_bn_act_fwd: workspace %zu < %zu", ws_bytes, bn_partials_bytes(d->cout));
     cudaStream_t st = as_stream(stream);
     const int64_t pixels = (int64_t)d->n * d->oh * d->ow;
-    MSX_TRY(conv_pack_launch(d, MSX_PACK_FPROP, w_master, w_packed, st));
+    if (w_master) MSX_TRY(conv_pack_launch(d, MSX_PACK_FPROP, w_master, w_packed, st));
     MSX_TRY(conv_gather(d, true, x, w_packed, bias, y_raw, st));
     if (training) {
         int nblk = 0;
@@ -119,7 +140,7 @@ int msx_conv_bn_act_bwd(const msx_conv_desc* d, const void* x, const float* w_ma
                         const float* save_invstd, int relu, void* w_packed, void* dy_scratch, void* dx, float* dw,
                         float* dbias, float* dgamma, float* dbeta, void* ws, size_t ws_bytes, void* stream) {
     MSX_TRY(validate_desc(d));
-    MSX_REQUIRE(x && w_master && y_raw && dz && gamma && beta && save_mean && save_invstd && w_packed && dy_scratch,
+    MSX_REQUIRE(x && y_raw && dz && gamma && beta && save_mean && save_invstd && w_packed && dy_scratch,
                 "conv_bn_act_bwd: null pointer");
     if (ws_bytes < ws_conv_bytes(d)) return set_error(MSX_ERR_WORKSPACE, "conv_bn_act_bwd: workspace %zu < %zu", ws_bytes, ws_conv_bytes(d));
     cudaStream_t st = as_stream(stream);
@@ -127,7 +148,7 @@ int msx_conv_bn_act_bwd(const msx_conv_desc* d, const void* x, const float* w_ma
     MSX_TRY(bn_bwd_launch(d->dtype, y_raw, d->ldy, dz, lddz, pixels, d->cout, gamma, beta, save_mean, save_invstd, relu,
                           dy_scratch, d->ldy, dgamma, dbeta, ws, ws_bytes, st));
     if (dx) {
-        MSX_TRY(conv_pack_launch(d, MSX_PACK_DGRAD, w_master, w_packed, st));
+        if (w_master) MSX_TRY(conv_pack_launch(d, MSX_PACK_DGRAD, w_master, w_packed, st));
         MSX_TRY(conv_gather(d, false, dy_scratch, w_packed, nullptr, dx, st));
     }
     if (dw) MSX_TRY(conv_wgrad(d, x, dy_scratch, dw, ws, ws_bytes, st));

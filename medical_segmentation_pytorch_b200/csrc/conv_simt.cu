@@ -11,6 +11,8 @@
 // zero padded, in the activation dtype.
 #include "common.cuh"
 
+#include <vector>
+
 namespace msx {
 
 struct GatherGeom {
@@ -282,7 +284,104 @@ __global__ void pack_weights_kernel(const float* __restrict__ w, int A, int B, i
     }
 }
 
+// ---- all weights of a model in one launch ---------------------------------------------------
+// A step packs every conv weight twice (fprop and dgrad operand).  Per-conv launches of the kernel above were
+// ~540 launches / step for DUCK-Net; the table-driven kernel below does the same work in one.
+// Work unit = one (n, k) pair of one item: the thread reads that pair's `taps` master values (contiguous when
+// k runs along the master's inner axis) and writes one element of every tap plane.
+struct PackItemDev {
+    const float* w;
+    void* out;
+    int A, B, taps, n_is_a, Np, Kp;
+};
+struct PackChunkDev { int item, first_pair; };
+constexpr int kPackPairsPerCta = 1024;
+
+template <typename T>
+__global__ void __launch_bounds__(256) pack_many_kernel(const PackItemDev* __restrict__ items, const PackChunkDev* __restrict__ chunks) {
+    const PackChunkDev ch = chunks[blockIdx.x];
+    const PackItemDev it = items[ch.item];
+    const int pairs = it.Np * it.Kp;
+    const int Nn = it.n_is_a ? it.A : it.B, Kk = it.n_is_a ? it.B : it.A;
+    T* out = static_cast<T*>(it.out);
+    const int end = min(ch.first_pair + kPackPairsPerCta, pairs);
+    for (int i = ch.first_pair + threadIdx.x; i < end; i += 256) {
+        const int n = i / it.Kp, k = i - n * it.Kp;
+        if (n < Nn && k < Kk) {
+            const int a = it.n_is_a ? n : k, b = it.n_is_a ? k : n;
+            const float* src = it.w + ((int64_t)a * it.B + b) * it.taps;
+            for (int tap = 0; tap < it.taps; ++tap) out[(int64_t)tap * pairs + i] = from_float<T>(src[tap]);
+        } else {
+            for (int tap = 0; tap < it.taps; ++tap) out[(int64_t)tap * pairs + i] = from_float<T>(0.f);
+        }
+    }
+}
+
 }  // namespace
+
+static void pack_item_dims(const msx_pack_item& h, PackItemDev& d) {
+    const bool fwd_pass = h.mode == MSX_PACK_FPROP;
+    const int Nc = fwd_pass ? h.cout : h.cin, K = fwd_pass ? h.cin : h.cout;
+    d.w = h.w_master;
+    d.out = h.packed;
+    d.A = h.transposed ? h.cin : h.cout;
+    d.B = h.transposed ? h.cout : h.cin;
+    d.taps = h.kh * h.kw;
+    d.n_is_a = (h.transposed ? !fwd_pass : fwd_pass) ? 1 : 0;
+    d.Np = round_up(Nc, 16);
+    d.Kp = round_up(K, 8);
+}
+
+static int pack_plan_chunks(const msx_pack_item* items, int count) {
+    int64_t chunks = 0;
+    for (int i = 0; i < count; ++i) {
+        PackItemDev d;
+        pack_item_dims(items[i], d);
+        chunks += ((int64_t)d.Np * d.Kp + kPackPairsPerCta - 1) / kPackPairsPerCta;
+    }
+    return chunks > INT32_MAX ? -1 : (int)chunks;
+}
+
+size_t conv_pack_plan_bytes(const msx_pack_item* items, int count) {
+    const int chunks = pack_plan_chunks(items, count);
+    if (chunks < 0) return 0;
+    return (size_t)count * sizeof(PackItemDev) + (size_t)chunks * sizeof(PackChunkDev) + 256;
+}
+
+// Writes the table through a synchronous copy: building a plan is start-up work, not part of a step.
+int conv_pack_plan_build(const msx_pack_item* items, int count, void* table, size_t table_bytes, int* chunks_out) {
+    const int chunks = pack_plan_chunks(items, count);
+    if (chunks < 0) return set_error(MSX_ERR_UNSUPPORTED, "pack_plan: too many chunks");
+    if (table_bytes < conv_pack_plan_bytes(items, count)) return set_error(MSX_ERR_WORKSPACE, "pack_plan: table %zu < %zu bytes", table_bytes, conv_pack_plan_bytes(items, count));
+    std::vector<PackItemDev> hi(count);
+    std::vector<PackChunkDev> hc;
+    hc.reserve(chunks);
+    for (int i = 0; i < count; ++i) {
+        const msx_pack_item& h = items[i];
+        if (!h.w_master || !h.packed || h.cout <= 0 || h.cin <= 0 || h.kh <= 0 || h.kw <= 0 || (h.mode != MSX_PACK_FPROP && h.mode != MSX_PACK_DGRAD))
+            return set_error(MSX_ERR_INVALID, "pack_plan: bad item %d", i);
+        pack_item_dims(h, hi[i]);
+        const int pairs = hi[i].Np * hi[i].Kp;
+        for (int f = 0; f < pairs; f += kPackPairsPerCta) hc.push_back({i, f});
+    }
+    char* base = static_cast<char*>(table);
+    MSX_CHECK_CUDA(cudaMemcpy(base, hi.data(), hi.size() * sizeof(PackItemDev), cudaMemcpyHostToDevice));
+    const size_t off = ((size_t)count * sizeof(PackItemDev) + 15) & ~(size_t)15;
+    MSX_CHECK_CUDA(cudaMemcpy(base + off, hc.data(), hc.size() * sizeof(PackChunkDev), cudaMemcpyHostToDevice));
+    *chunks_out = chunks;
+    return MSX_OK;
+}
+
+int conv_pack_plan_run(int dtype, const void* table, int count, int chunks, double bytes, cudaStream_t st) {
+    const char* base = static_cast<const char*>(table);
+    const size_t off = ((size_t)count * sizeof(PackItemDev) + 15) & ~(size_t)15;
+    MSX_DISPATCH_DTYPE(dtype, T, {
+        ProfScope ps__(K_PACK, st, bytes, 0);
+        pack_many_kernel<T><<<chunks, 256, 0, st>>>(reinterpret_cast<const PackItemDev*>(base), reinterpret_cast<const PackChunkDev*>(base + off));
+    });
+    MSX_LAUNCH_CHECK();
+    return MSX_OK;
+}
 
 // --------------------------------------------------------------------------------------------
 int validate_desc(const msx_conv_desc* d) {

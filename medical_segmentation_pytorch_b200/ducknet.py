@@ -1,7 +1,7 @@
 """DUCK-Net with the reference constructor, forward signature and state_dict (models/ducknet.py:15-179)."""
 import torch.nn as nn
 
-from . import ops
+from . import ops, packplan
 from .modules import (Act, Activation, ConvBNAct, add, compute_dtype, conv1x1, conv_plain, fanout, sum_bn_act)
 
 
@@ -133,7 +133,12 @@ class DuckNet(nn.Module):
     def forward(self, x):
         if x.shape[2] % 32 or x.shape[3] % 32:
             raise ValueError('DuckNet input height/width must be multiples of 32')
-        img = ops.to_nhwc(x, compute_dtype(self))
+        dt = compute_dtype(self)
+        with packplan.active(self, dt, x.device, skip=(self.seg_head,)):     # all conv weights packed by one launch
+            return self._forward(x, dt)
+
+    def _forward(self, x, dt):
+        img = ops.to_nhwc(x, dt)
         x1, s1, xc = self.down_stage1([img], img)
         skips = [s1]
         for stage in (self.down_stage2, self.down_stage3, self.down_stage4, self.down_stage5):

@@ -12,6 +12,7 @@ import ctypes as C
 import torch
 
 from . import _lib as L
+from . import packplan
 from ._lib import lib
 
 
@@ -184,9 +185,11 @@ class ConvBNActFn(torch.autograd.Function):
         d = _desc(g, x, cp, oh, ow)
         wsb = lib.msx_ws_bytes_conv(C.byref(d))
         ws = L.workspace(wsb, dev)
-        pk = L.scratch('pack', lib.msx_conv_packed_bytes(C.byref(d)), dev)
+        pre = packplan.lookup(_f32(weight))          # pre-packed by the model's plan: pass w_master = NULL
+        pk = pre[0] if pre else L.scratch('pack', lib.msx_conv_packed_bytes(C.byref(d)), dev)
+        ctx.pk_b = pre[1] if pre else None
         L.check(lib.msx_conv_bn_act_fwd(
-            C.byref(d), L.ptr(x), L.ptr(_f32(weight)), L.ptr(_f32(bias)), L.ptr(_f32(gamma)), L.ptr(_f32(beta)),
+            C.byref(d), L.ptr(x), None if pre else L.ptr(weight), L.ptr(_f32(bias)), L.ptr(_f32(gamma)), L.ptr(_f32(beta)),
             L.ptr(rm), L.ptr(rv), L.ptr(nbt), eps, momentum, int(training), int(relu),
             L.ptr(pk), L.ptr(y), L.ptr(z), ld_of(z), L.ptr(mean), L.ptr(invstd), L.ptr(ws), ws.numel(), L.stream()))
         ctx.g, ctx.relu, ctx.d = g, relu, d
@@ -206,9 +209,9 @@ class ConvBNActFn(torch.autograd.Function):
         db = _pgrad(bias) if bias is not None else None
         dgamma, dbeta = _pgrad(gamma), _pgrad(beta)
         ws = L.workspace(lib.msx_ws_bytes_conv(C.byref(d)), dev)
-        pk = L.scratch('pack', lib.msx_conv_packed_bytes(C.byref(d)), dev)
+        pk = ctx.pk_b if ctx.pk_b is not None else L.scratch('pack', lib.msx_conv_packed_bytes(C.byref(d)), dev)
         L.check(lib.msx_conv_bn_act_bwd(
-            C.byref(d), L.ptr(x), L.ptr(weight), L.ptr(y), L.ptr(dz), ld_of(dz), L.ptr(gamma), L.ptr(beta),
+            C.byref(d), L.ptr(x), None if ctx.pk_b is not None else L.ptr(weight), L.ptr(y), L.ptr(dz), ld_of(dz), L.ptr(gamma), L.ptr(beta),
             L.ptr(mean), L.ptr(invstd), int(ctx.relu), L.ptr(pk), L.ptr(dy), L.ptr(dx), L.ptr(dw), L.ptr(db),
             L.ptr(dgamma), L.ptr(dbeta), L.ptr(ws), ws.numel(), L.stream()))
         # notify in arena order (reverse registration): bn.bias, bn.weight, conv.bias, conv.weight
@@ -228,9 +231,10 @@ class Conv2dFn(torch.autograd.Function):
         cp = rup(g.cout)
         y = torch.empty(n, oh, ow, cp, dtype=x.dtype, device=x.device)
         d = _desc(g, x, cp, oh, ow)
-        pk = L.scratch('pack', lib.msx_conv_packed_bytes(C.byref(d)), x.device)
-        L.check(lib.msx_conv2d_fwd(C.byref(d), L.ptr(x), L.ptr(_f32(weight)), None, L.ptr(pk), L.ptr(y), L.stream()))
-        ctx.d = d
+        pre = packplan.lookup(_f32(weight))
+        pk = pre[0] if pre else L.scratch('pack', lib.msx_conv_packed_bytes(C.byref(d)), x.device)
+        L.check(lib.msx_conv2d_fwd(C.byref(d), L.ptr(x), None if pre else L.ptr(weight), None, L.ptr(pk), L.ptr(y), L.stream()))
+        ctx.d, ctx.pk_b = d, (pre[1] if pre else None)
         ctx.save_for_backward(x, weight)
         return y
 
@@ -245,8 +249,8 @@ class Conv2dFn(torch.autograd.Function):
         dx = _grad_like_input(x) if ctx.needs_input_grad[0] else None
         dw = _pgrad(weight)
         ws = L.workspace(lib.msx_ws_bytes_conv(C.byref(d)), x.device)
-        pk = L.scratch('pack', lib.msx_conv_packed_bytes(C.byref(d)), x.device)
-        L.check(lib.msx_conv2d_bwd(C.byref(d), L.ptr(x), L.ptr(weight), L.ptr(dy), L.ptr(pk), L.ptr(dx), L.ptr(dw), None,
+        pk = ctx.pk_b if ctx.pk_b is not None else L.scratch('pack', lib.msx_conv_packed_bytes(C.byref(d)), x.device)
+        L.check(lib.msx_conv2d_bwd(C.byref(d), L.ptr(x), None if ctx.pk_b is not None else L.ptr(weight), L.ptr(dy), L.ptr(pk), L.ptr(dx), L.ptr(dw), None,
                                    L.ptr(ws), ws.numel(), L.stream()))
         return dx, _pdone(weight, dw), None
 

@@ -2,7 +2,7 @@
 import torch
 import torch.nn as nn
 
-from . import ops
+from . import ops, packplan
 from .modules import Act, ConvBNAct, DeConvBNAct, compute_dtype, conv1x1
 
 
@@ -64,6 +64,10 @@ class UNet(nn.Module):
         if x.shape[2] % 16 or x.shape[3] % 16:
             raise ValueError('UNet input height/width must be multiples of 16')
         dt = compute_dtype(self)
+        with packplan.active(self, dt, x.device, skip=(self.seg_head,)):     # all conv weights packed by one launch
+            return self._forward(x, dt)
+
+    def _forward(self, x, dt):
         a = ops.to_nhwc(x, dt)
         n, _, h, w = x.shape
         skips, bufs = [], []

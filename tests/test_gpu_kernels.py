@@ -422,3 +422,56 @@ def test_full_size_properties():
     assert float(g[:, 0][mask == 255].abs().max()) == 0.0                            # ignored pixels get no gradient
     want = torch.nn.functional.cross_entropy(z.detach(), mask, ignore_index=255)     # same-device library check of the scalar
     assert abs(float(loss) - float(want)) < 1e-5
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_pack_plan_matches_per_conv_pack(dtype):
+    """msx_conv_pack_plan_* (one launch for many weights) writes the same bytes as msx_conv_pack_weights per conv and pass."""
+    import ctypes as C
+    from medical_segmentation_pytorch_b200 import _lib as L
+    torch.manual_seed(3)
+    geoms = [(17, 3, 3, 3, 0), (34, 17, 1, 7, 0), (5, 40, 7, 1, 0), (24, 24, 1, 1, 0), (16, 32, 3, 3, 1), (130, 68, 3, 3, 0), (8, 8, 2, 2, 0)]
+    es = 2 if dtype == torch.bfloat16 else 4
+    items, want = [], []
+    for cout, cin, kh, kw, tr in geoms:
+        w = torch.randn((cin, cout, kh, kw) if tr else (cout, cin, kh, kw), device=DEV)
+        d = L.ConvDesc(n=1, h=8, w=8, cin=cin, oh=8 + 2 * ((kh - 1) // 2) - kh + 1, ow=8 + 2 * ((kw - 1) // 2) - kw + 1, cout=cout, kh=kh, kw=kw,
+                       stride=1, dil=1, pad_h=(kh - 1) // 2, pad_w=(kw - 1) // 2,
+                       ldx=(cin + 7) // 8 * 8, ldy=(cout + 7) // 8 * 8, transposed=0, dtype=L.dtype_code(dtype), engine=0)
+        if tr:                       # stride-2 ConvTranspose2d 3x3 (DeConvBNAct): 8x8 -> 16x16
+            d.stride, d.oh, d.ow, d.transposed = 2, 16, 16, 1
+        nbytes = L.lib.msx_conv_packed_bytes(C.byref(d))
+        for mode in (L.PACK_FPROP, L.PACK_DGRAD):
+            ref = torch.full((nbytes,), 0x5a, dtype=torch.uint8, device=DEV)
+            L.check(L.lib.msx_conv_pack_weights(C.byref(d), mode, L.ptr(w), L.ptr(ref), L.stream()))
+            out = torch.full((nbytes,), 0x5a, dtype=torch.uint8, device=DEV)
+            items.append(L.PackItem(w_master=w.data_ptr(), packed=out.data_ptr(), cout=cout, cin=cin, kh=kh, kw=kw, transposed=tr, mode=mode))
+            want.append((ref, out, w))
+    arr = (L.PackItem * len(items))(*items)
+    nb = L.lib.msx_conv_pack_plan_bytes(arr, len(items))
+    table = torch.empty(nb, dtype=torch.uint8, device=DEV)
+    chunks = C.c_int32(0)
+    L.check(L.lib.msx_conv_pack_plan_build(arr, len(items), L.ptr(table), nb, C.byref(chunks)))
+    for _ in range(2):
+        L.check(L.lib.msx_conv_pack_plan_run(L.dtype_code(dtype), L.ptr(table), len(items), chunks.value, L.stream()))
+    for i, (ref, out, _) in enumerate(want):
+        assert torch.equal(ref, out), (i, es)
+
+
+def test_model_forward_repacks_changed_weights():
+    """The per-forward pack plan must see in-place weight updates (optimizer steps, load_state_dict)."""
+    import medical_segmentation_pytorch_b200 as msx
+    torch.manual_seed(0)
+    m = msx.UNet(num_class=2, base_channel=8).to(DEV).eval()
+    x = torch.randn(1, 3, 32, 32, device=DEV)
+    with torch.no_grad():
+        y0 = m(x).clone()
+        for p in m.parameters():
+            if p.dim() == 4:
+                p.mul_(0.5)
+        y1 = m(x).clone()
+        m2 = msx.UNet(num_class=2, base_channel=8).to(DEV).eval()
+        m2.load_state_dict(m.state_dict())
+        y2 = m2(x)
+    assert not torch.equal(y0, y1)
+    assert torch.equal(y1, y2)
