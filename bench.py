@@ -157,6 +157,7 @@ def main():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--profile-steps', type=int, default=2)
     ap.add_argument('--ncu', action='store_true', help='short eager run for an ncu launch list: 1 warm-up + 1 step, no graph / e2e / profile pass')
+    ap.add_argument('--no-branch-streams', action='store_true', help='run sibling DUCK branches one after another on one stream')
     ap.add_argument('--no-graph', action='store_true', help='launch every kernel from Python instead of replaying one CUDA graph per step')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'b200' else args.warmup
@@ -168,7 +169,8 @@ def main():
     import torch
     import torch.distributed as dist
     import medical_segmentation_pytorch_b200 as msx
-    from medical_segmentation_pytorch_b200 import _lib
+    from medical_segmentation_pytorch_b200 import _lib, ops as msx_ops
+    msx_ops.set_branch_streams(not args.no_branch_streams)
     from medical_segmentation_pytorch_b200.flat import FlatBuffers, FlatParams
     from medical_segmentation_pytorch_b200.synth import synth_batch
 
@@ -288,6 +290,7 @@ def main():
     # profiled pass: per-launch CUDA events on the launching stream, algorithmic bytes/flops per launch
     prof = {}
     if args.profile_steps > 0:                                   # every rank steps (collectives), rank 0 records
+        msx_ops.set_branch_streams(0)                            # kernels timed one at a time, not overlapped with siblings
         if rank == 0:
             _lib.lib.msx_profile_enable(1)
         for _ in range(args.profile_steps):
@@ -295,6 +298,7 @@ def main():
         if rank == 0:
             prof = _lib.profile_collect()
             _lib.lib.msx_profile_enable(0)
+        msx_ops.set_branch_streams(not args.no_branch_streams)
     barrier()
 
     def leave():
@@ -337,7 +341,7 @@ def main():
                          'avg_launch_us': tv['ms'] / tv['launches'] * 1e3, 'launches_per_step': tv['launches'] // args.profile_steps,
                          'share_of_step': tv['ms'] / tot_ms,
                          'how': f'{args.profile_steps} extra step(s) after the timed region with per-launch CUDA events (msx_profile_*)'})
-    loss_metric = loss_metric_leg(msx, _lib, dev, pk) if world == 1 else None
+    loss_metric = loss_metric_leg(msx, _lib, dev, pk) if world == 1 and not args.ncu else None
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
         cpu_baseline, _ = cpu_reference_leg(args.model, 2, 1, batch=2, hw=S)

@@ -121,11 +121,16 @@ def dtype_code(dt):
 
 # ---- per-device scratch ----------------------------------------------------------------------
 _scratch = {}
+LANE_OF_STREAM = {}
 
 
 def scratch(kind, nbytes, device):
-    """Grow-only byte buffers shared by all calls on a device (calls are ordered on one stream)."""
-    key = (kind, device.index if device.index is not None else torch.cuda.current_device())
+    """Grow-only byte buffers shared by all calls of one lane of a device.  Lane 0 is whatever stream the caller
+    runs on (calls there are ordered); DUCK-Net's sibling branches run on side streams registered in LANE_OF_STREAM
+    (ops.run_branches), each with its own buffers.  Keyed by lane, not stream, so that an eager warm-up and a later
+    graph capture (which runs on another stream) find the same buffers."""
+    lane = LANE_OF_STREAM.get(torch.cuda.current_stream().cuda_stream, 0) if LANE_OF_STREAM else 0
+    key = (kind, device.index if device.index is not None else torch.cuda.current_device(), lane)
     buf = _scratch.get(key)
     if buf is None or buf.numel() < nbytes:
         if torch.cuda.is_current_stream_capturing():

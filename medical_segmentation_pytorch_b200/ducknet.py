@@ -74,13 +74,15 @@ class DUCK(nn.Module):
         call, models/ducknet.py:39-43,84); with up2x, xs[0] is nearest-upsampled 2x first."""
         x = sum_bn_act(xs, self.in_bn[0], self.in_bn[1].relu, up2x=up2x)
         f = fanout(x, 9)                                    # nine first-layer convs read the same tensor
-        x1 = _chain(self.branch1, f[0])
-        x2 = _chain(self.branch2, f[1])
-        x3 = self.branch3(f[2], f[3])
-        x4 = self.branch4[1](self.branch4[0](f[4], f[5]))
-        x5 = self.branch5[2](self.branch5[1](self.branch5[0](f[6], f[7])))
-        x6 = _chain(self.branch6, f[8])
-        return sum_bn_act([x1, x2, x3, x4, x5, x6], self.out_bn[0], self.out_bn[1].relu)
+        outs = ops.run_branches([
+            (lambda: _chain(self.branch1, f[0]), f[0:1]),
+            (lambda: _chain(self.branch2, f[1]), f[1:2]),
+            (lambda: self.branch3(f[2], f[3]), f[2:4]),
+            (lambda: self.branch4[1](self.branch4[0](f[4], f[5])), f[4:6]),
+            (lambda: self.branch5[2](self.branch5[1](self.branch5[0](f[6], f[7]))), f[6:8]),     # longest chain: stays on the caller's stream
+            (lambda: _chain(self.branch6, f[8]), f[8:9]),
+        ], main_job=4)
+        return sum_bn_act(outs, self.out_bn[0], self.out_bn[1].relu)
 
 
 class DownsampleBlock(nn.Module):

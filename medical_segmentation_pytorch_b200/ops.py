@@ -255,6 +255,51 @@ class Conv2dFn(torch.autograd.Function):
         return dx, _pdone(weight, dw), None
 
 
+# ---- sibling branches on side streams ---------------------------------------------------------
+_BRANCH_STREAMS = [int(__import__('os').environ.get('MSX_BRANCH_STREAMS', '1'))]
+_STREAM_POOL = {}
+
+
+def set_branch_streams(on):
+    """Run independent branches of a block (DUCK's six, models/ducknet.py:66-74) on side streams (default on)."""
+    _BRANCH_STREAMS[0] = int(bool(on))
+
+
+def run_branches(jobs, main_job=0):
+    """jobs: (callable returning an Act, [input Acts produced on the current stream]).  Job ``main_job``
+    stays on the current stream, the others each get a pooled side stream forked from it and joined back
+    before returning, so that small layers of sibling branches overlap instead of queueing behind each other.
+    torch.autograd replays the same streams in backward.  Results are identical to the serial order: every
+    kernel is deterministic and the branches share no buffers (scratch is per stream)."""
+    if not _BRANCH_STREAMS[0] or len(jobs) < 2 or not torch.cuda.is_available():
+        return [j() for j, _ in jobs]
+    main = torch.cuda.current_stream()
+    if L.LANE_OF_STREAM.get(main.cuda_stream, 0) != 0:
+        return [j() for j, _ in jobs]                 # already on a side stream: no nested forking
+    key = (main.device.index, main.cuda_stream)
+    pool = _STREAM_POOL.setdefault(key, [])
+    while len(pool) < len(jobs) - 1:
+        pool.append(torch.cuda.Stream(device=main.device))
+        L.LANE_OF_STREAM[pool[-1].cuda_stream] = len(pool)   # scratch lane of this side stream (lane 0 = caller's stream)
+    fork = main.record_event()
+    outs, k = [None] * len(jobs), 0
+    for i, (job, inputs) in enumerate(jobs):
+        if i == main_job:
+            continue
+        s = pool[k]
+        k += 1
+        s.wait_event(fork)
+        for a in inputs:
+            a.t.record_stream(s)                     # allocated on main, read (also by the backward) on the side stream
+        with torch.cuda.stream(s):
+            outs[i] = job()
+        outs[i].t.record_stream(main)                # consumed on the main stream after the join
+    outs[main_job] = jobs[main_job][0]()
+    for s in pool[:k]:
+        main.wait_stream(s)
+    return outs
+
+
 def _ptr_arrays(ts):
     n = len(ts)
     ptrs = (C.c_void_p * n)(*[t.data_ptr() for t in ts])

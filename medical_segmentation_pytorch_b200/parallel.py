@@ -89,15 +89,18 @@ class DistributedDataParallelB200(nn.Module):
                 pass                                   # not inside backward (tests drive finish() themselves)
         bk = self.buckets[p._msx_bucket]
         bk['pending'] -= 1
+        if self.is_cuda:                               # gradients of one bucket may be produced on several streams
+            cur = torch.cuda.current_stream()
+            bk.setdefault('streams', {})[cur.cuda_stream] = cur
         if bk['pending'] == 0:
             self._launch(bk)
 
     def _launch(self, bk):
         view = self.flat.grad[bk['lo']:bk['hi']]
         if self.is_cuda:
-            ev = torch.cuda.Event()
-            ev.record(torch.cuda.current_stream())
-            self.comm_stream.wait_event(ev)
+            streams = bk.pop('streams', None) or {0: torch.cuda.current_stream()}
+            for s in streams.values():                 # everything enqueued so far on each producing stream
+                self.comm_stream.wait_event(s.record_event())
             with torch.cuda.stream(self.comm_stream):
                 op = dist.ReduceOp.AVG if self._avg_native else dist.ReduceOp.SUM
                 bk['work'] = dist.all_reduce(view, op=op, group=self.pg, async_op=True)

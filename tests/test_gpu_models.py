@@ -199,3 +199,40 @@ def test_unet32_fp32_config0_shape_runs_and_is_consistent():
     assert all(torch.isfinite(g).all() for g in g32)
     want = torch.nn.functional.cross_entropy(m(x).detach(), t, ignore_index=255)
     assert torch.isfinite(want)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('bf16', [False, True])
+def test_ducknet_branch_streams_bit_identical(bf16):
+    """Sibling DUCK branches on side streams (ops.run_branches) vs one stream: same loss, logits and gradients, bit for bit,
+    over two consecutive steps (the second reuses freed blocks of the first)."""
+    import medical_segmentation_pytorch_b200 as msx
+    from medical_segmentation_pytorch_b200 import ops
+    dev = torch.device('cuda')
+    res = []
+    try:
+        for on in (0, 1):
+            ops.set_branch_streams(on)
+            torch.manual_seed(5)
+            m = msx.DuckNet(num_class=2, base_channel=8).to(dev).train()
+            x = torch.randn(2, 3, 64, 64, device=dev)
+            t = torch.randint(0, 2, (2, 64, 64), device=dev)
+            loss_fn = msx.get_loss_fn(Cfg(), dev)
+            outs = []
+            for _ in range(2):
+                for p in m.parameters():
+                    p.grad = None
+                with torch.autocast('cuda', dtype=torch.bfloat16, enabled=bf16):
+                    y = m(x)
+                loss = loss_fn(y, t)
+                loss.backward()
+                torch.cuda.synchronize()
+                outs.append((loss.detach().clone(), y.detach().clone(), [p.grad.clone() for p in m.parameters()],
+                             [b.clone() for b in m.buffers()]))
+            res.append(outs)
+    finally:
+        ops.set_branch_streams(1)
+    for a, b in zip(res[0], res[1]):
+        assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+        assert all(torch.equal(g, h) for g, h in zip(a[2], b[2]))
+        assert all(torch.equal(g, h) for g, h in zip(a[3], b[3]))
