@@ -171,6 +171,7 @@ def main():
     import medical_segmentation_pytorch_b200 as msx
     from medical_segmentation_pytorch_b200 import _lib, ops as msx_ops
     msx_ops.set_branch_streams(not args.no_branch_streams)
+    msx_ops.set_wgrad_stream(not args.no_branch_streams)
     from medical_segmentation_pytorch_b200.flat import FlatBuffers, FlatParams
     from medical_segmentation_pytorch_b200.synth import synth_batch
 
@@ -291,6 +292,7 @@ def main():
     prof = {}
     if args.profile_steps > 0:                                   # every rank steps (collectives), rank 0 records
         msx_ops.set_branch_streams(0)                            # kernels timed one at a time, not overlapped with siblings
+        msx_ops.set_wgrad_stream(0)
         if rank == 0:
             _lib.lib.msx_profile_enable(1)
         for _ in range(args.profile_steps):
@@ -299,6 +301,7 @@ def main():
             prof = _lib.profile_collect()
             _lib.lib.msx_profile_enable(0)
         msx_ops.set_branch_streams(not args.no_branch_streams)
+        msx_ops.set_wgrad_stream(not args.no_branch_streams)
     barrier()
 
     def leave():

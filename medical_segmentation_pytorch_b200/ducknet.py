@@ -22,8 +22,8 @@ class ResidualBlock(nn.Module):
     def forward(self, x_up, x_low=None):
         if x_low is None:
             x_up, x_low = fanout(x_up, 2)
-        up = conv_plain(x_up, self.upper_branch)
-        low = self.lower_branch[1](self.lower_branch[0](x_low))
+        up, low = ops.run_branches([(lambda: conv_plain(x_up, self.upper_branch), [x_up]),
+                                    (lambda: self.lower_branch[1](self.lower_branch[0](x_low)), [x_low])], main_job=1)
         return sum_bn_act([up, low], self.bn[0], self.bn[1].relu)        # add fused into the BN statistics pass
 
 
@@ -94,11 +94,12 @@ class DownsampleBlock(nn.Module):
         self.conv2 = ConvBNAct(in_channels, out_channels, 2, 2, act_type=act_type)
 
     def forward(self, x1_parts, x2):
-        x2 = self.conv2(x2)
-        skip = self.duck(x1_parts)
-        s_conv, s_skip = fanout(skip, 2)
-        x1 = self.conv1(s_conv)
-        return x1, s_skip, x2
+        def main_path():
+            skip = self.duck(x1_parts)
+            s_conv, s_skip = fanout(skip, 2)
+            return self.conv1(s_conv), s_skip
+        x2n, (x1, s_skip) = ops.run_branches([(lambda: self.conv2(x2), [x2]), (main_path, [])], main_job=1)
+        return x1, s_skip, x2n
 
 
 class UpsampleBlock(nn.Module):

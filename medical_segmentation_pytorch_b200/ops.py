@@ -208,16 +208,47 @@ class ConvBNActFn(torch.autograd.Function):
         dw = _pgrad(weight)
         db = _pgrad(bias) if bias is not None else None
         dgamma, dbeta = _pgrad(gamma), _pgrad(beta)
-        ws = L.workspace(lib.msx_ws_bytes_conv(C.byref(d)), dev)
         pk = ctx.pk_b if ctx.pk_b is not None else L.scratch('pack', lib.msx_conv_packed_bytes(C.byref(d)), dev)
-        L.check(lib.msx_conv_bn_act_bwd(
-            C.byref(d), L.ptr(x), None if ctx.pk_b is not None else L.ptr(weight), L.ptr(y), L.ptr(dz), ld_of(dz), L.ptr(gamma), L.ptr(beta),
-            L.ptr(mean), L.ptr(invstd), int(ctx.relu), L.ptr(pk), L.ptr(dy), L.ptr(dx), L.ptr(dw), L.ptr(db),
-            L.ptr(dgamma), L.ptr(dbeta), L.ptr(ws), ws.numel(), L.stream()))
+        side = _wgrad_stream() if _WGRAD_STREAM[0] else None
+        if side is None:
+            ws = L.workspace(lib.msx_ws_bytes_conv(C.byref(d)), dev)
+            L.check(lib.msx_conv_bn_act_bwd(
+                C.byref(d), L.ptr(x), None if ctx.pk_b is not None else L.ptr(weight), L.ptr(y), L.ptr(dz), ld_of(dz), L.ptr(gamma), L.ptr(beta),
+                L.ptr(mean), L.ptr(invstd), int(ctx.relu), L.ptr(pk), L.ptr(dy), L.ptr(dx), L.ptr(dw), L.ptr(db),
+                L.ptr(dgamma), L.ptr(dbeta), L.ptr(ws), ws.numel(), L.stream()))
+        else:
+            # the same three steps as the composite, with the weight gradient (tensor-core bound, nothing downstream
+            # in the backward chain needs it) on a side stream where it overlaps the data gradient and the next
+            # layers' bandwidth-bound BN kernels
+            n_, oh_, ow_, cpy = y.shape
+            ws = L.workspace(lib.msx_ws_bytes_bn(ctx.g.cout), dev)
+            L.check(lib.msx_bn_act_bwd(L.dtype_code(y.dtype), L.ptr(y), cpy, L.ptr(dz), ld_of(dz), n_ * oh_ * ow_, ctx.g.cout,
+                                       L.ptr(gamma), L.ptr(beta), L.ptr(mean), L.ptr(invstd), int(ctx.relu), L.ptr(dy), cpy,
+                                       L.ptr(dgamma), L.ptr(dbeta), L.ptr(ws), ws.numel(), L.stream()))
+            main = torch.cuda.current_stream()
+            side.wait_event(main.record_event())
+            x.record_stream(side)
+            dy.record_stream(side)
+            with torch.cuda.stream(side):
+                ws2 = L.workspace(lib.msx_ws_bytes_conv(C.byref(d)), dev)          # the side stream's own lane
+                L.check(lib.msx_conv2d_bwd(C.byref(d), L.ptr(x), None, L.ptr(dy), L.ptr(pk), None, L.ptr(dw), None,
+                                           L.ptr(ws2), ws2.numel(), L.stream()))
+            if dx is not None or db is not None:
+                ws = L.workspace(lib.msx_ws_bytes_conv(C.byref(d)), dev)
+                L.check(lib.msx_conv2d_bwd(C.byref(d), L.ptr(x), None if ctx.pk_b is not None else L.ptr(weight), L.ptr(dy), L.ptr(pk),
+                                           L.ptr(dx), None, L.ptr(db), L.ptr(ws), ws.numel(), L.stream()))
+            if getattr(weight, '_msx_grad', None) is dw:
+                _defer_join(side)                     # arena gradient: joined once, at the end of the backward pass
+            else:
+                main.wait_stream(side)                # handed back to autograd, which assumes this node's stream
         # notify in arena order (reverse registration): bn.bias, bn.weight, conv.bias, conv.weight
         dbeta, dgamma = _pdone(beta, dbeta), _pdone(gamma, dgamma)
         db = _pdone(bias, db) if bias is not None else None
-        dw = _pdone(weight, dw)
+        if side is not None:
+            with torch.cuda.stream(side):             # DDP records the stream the gradient is produced on
+                dw = _pdone(weight, dw)
+        else:
+            dw = _pdone(weight, dw)
         return (dx, dw, db, dgamma, dbeta) + (None,) * 9
 
 
@@ -271,16 +302,16 @@ def run_branches(jobs, main_job=0):
     before returning, so that small layers of sibling branches overlap instead of queueing behind each other.
     torch.autograd replays the same streams in backward.  Results are identical to the serial order: every
     kernel is deterministic and the branches share no buffers (scratch is per stream)."""
-    if not _BRANCH_STREAMS[0] or len(jobs) < 2 or not torch.cuda.is_available():
+    if not _BRANCH_STREAMS[0] or not 2 <= len(jobs) <= 7 or not torch.cuda.is_available():
         return [j() for j, _ in jobs]
     main = torch.cuda.current_stream()
-    if L.LANE_OF_STREAM.get(main.cuda_stream, 0) != 0:
-        return [j() for j, _ in jobs]                 # already on a side stream: no nested forking
     key = (main.device.index, main.cuda_stream)
-    pool = _STREAM_POOL.setdefault(key, [])
+    pool = _STREAM_POOL.setdefault(key, [])                  # side streams of THIS stream: forks may nest
     while len(pool) < len(jobs) - 1:
         pool.append(torch.cuda.Stream(device=main.device))
-        L.LANE_OF_STREAM[pool[-1].cuda_stream] = len(pool)   # scratch lane of this side stream (lane 0 = caller's stream)
+        # scratch lane = position in the fork tree (lane 0 = a stream the library did not create; < 8 siblings per fork),
+        # so that an eager warm-up and a graph capture on another stream land on the same buffers
+        L.LANE_OF_STREAM[pool[-1].cuda_stream] = L.LANE_OF_STREAM.get(main.cuda_stream, 0) * 8 + len(pool)
     fork = main.record_event()
     outs, k = [None] * len(jobs), 0
     for i, (job, inputs) in enumerate(jobs):
@@ -298,6 +329,45 @@ def run_branches(jobs, main_job=0):
     for s in pool[:k]:
         main.wait_stream(s)
     return outs
+
+
+# ---- weight gradients on a side stream ---------------------------------------------------------
+_WGRAD_STREAM = [int(__import__('os').environ.get('MSX_WGRAD_STREAM', '1'))]
+_PENDING_JOIN = {}
+
+
+def set_wgrad_stream(on):
+    """ConvBNAct backward: run the weight-gradient kernels on a side stream of the current stream (default on)."""
+    _WGRAD_STREAM[0] = int(bool(on))
+
+
+def _wgrad_stream():
+    main = torch.cuda.current_stream()
+    key = ('wgrad', main.device.index, main.cuda_stream)
+    s = _STREAM_POOL.get(key)
+    if s is None:
+        s = _STREAM_POOL[key] = torch.cuda.Stream(device=main.device)
+        L.LANE_OF_STREAM[s.cuda_stream] = L.LANE_OF_STREAM.get(main.cuda_stream, 0) * 8 + 7     # sibling slot 7: run_branches uses 1..6
+    return s
+
+
+def _join_wgrad_streams():
+    cur = torch.cuda.current_stream()
+    for s in _PENDING_JOIN.values():
+        cur.wait_stream(s)
+    _PENDING_JOIN.clear()
+
+
+def _defer_join(side):
+    """Make the stream that called backward() wait for ``side`` when the backward pass ends (engine callback);
+    outside a backward pass (a Function's backward called by hand) join at once."""
+    if not _PENDING_JOIN:
+        try:
+            torch.autograd.Variable._execution_engine.queue_callback(_join_wgrad_streams)
+        except RuntimeError:
+            torch.cuda.current_stream().wait_stream(side)
+            return
+    _PENDING_JOIN[side.cuda_stream] = side
 
 
 def _ptr_arrays(ts):

@@ -204,7 +204,8 @@ def test_unet32_fp32_config0_shape_runs_and_is_consistent():
 @pytest.mark.gpu
 @pytest.mark.parametrize('bf16', [False, True])
 def test_ducknet_branch_streams_bit_identical(bf16):
-    """Sibling DUCK branches on side streams (ops.run_branches) vs one stream: same loss, logits and gradients, bit for bit,
+    """Sibling DUCK branches and weight gradients on side streams (ops.run_branches, ops._wgrad_stream) vs one stream:
+    same loss, logits and gradients, bit for bit,
     over two consecutive steps (the second reuses freed blocks of the first)."""
     import medical_segmentation_pytorch_b200 as msx
     from medical_segmentation_pytorch_b200 import ops
@@ -213,6 +214,7 @@ def test_ducknet_branch_streams_bit_identical(bf16):
     try:
         for on in (0, 1):
             ops.set_branch_streams(on)
+            ops.set_wgrad_stream(on)
             torch.manual_seed(5)
             m = msx.DuckNet(num_class=2, base_channel=8).to(dev).train()
             x = torch.randn(2, 3, 64, 64, device=dev)
@@ -232,6 +234,7 @@ def test_ducknet_branch_streams_bit_identical(bf16):
             res.append(outs)
     finally:
         ops.set_branch_streams(1)
+        ops.set_wgrad_stream(1)
     for a, b in zip(res[0], res[1]):
         assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
         assert all(torch.equal(g, h) for g, h in zip(a[2], b[2]))
