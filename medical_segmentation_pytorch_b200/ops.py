@@ -288,6 +288,7 @@ class Conv2dFn(torch.autograd.Function):
 
 # ---- sibling branches on side streams ---------------------------------------------------------
 _BRANCH_STREAMS = [int(__import__('os').environ.get('MSX_BRANCH_STREAMS', '1'))]
+_BRANCH_MAX_ELEMS = [int(__import__('os').environ.get('MSX_BRANCH_MAX_ELEMS', '0'))]      # 0: no limit
 _STREAM_POOL = {}
 
 
@@ -302,7 +303,8 @@ def run_branches(jobs, main_job=0):
     before returning, so that small layers of sibling branches overlap instead of queueing behind each other.
     torch.autograd replays the same streams in backward.  Results are identical to the serial order: every
     kernel is deterministic and the branches share no buffers (scratch is per stream)."""
-    if not _BRANCH_STREAMS[0] or not 2 <= len(jobs) <= 7 or not torch.cuda.is_available():
+    big = _BRANCH_MAX_ELEMS[0] and any(a.t.numel() > _BRANCH_MAX_ELEMS[0] for _, ins in jobs for a in ins)
+    if not _BRANCH_STREAMS[0] or big or not 2 <= len(jobs) <= 7 or not torch.cuda.is_available():
         return [j() for j, _ in jobs]
     main = torch.cuda.current_stream()
     key = (main.device.index, main.cuda_stream)
