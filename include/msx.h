@@ -120,7 +120,10 @@ int msx_conv2d_bwd(const msx_conv_desc* d, const void* x, const float* w_master,
  *   y_raw = op(x, W) (+bias);  training: batch statistics (biased var for normalisation, unbiased
  *   for running_var, eps, momentum) else running statistics;  z = relu(gamma*(y-mean)*invstd+beta).
  * save_mean / save_invstd (fp32[round_up(cout,8)]) are kept for backward.  relu: 1/0.
- * z is written with pixel stride ldz (zero-copy concat). */
+ * z is written with pixel stride ldz (zero-copy concat).
+ * Inference (core/seg_trainer.py:97-146 validate, tools/test_speed.py): with training = 0 and y_raw = NULL no raw
+ * conv output is produced; the eval-mode BN affine and the ReLU are applied in the conv epilogue from the fp32
+ * accumulators (no backward can follow such a call: it needs y_raw). */
 int msx_conv_bn_act_fwd(const msx_conv_desc* d, const void* x, const float* w_master, const float* bias,
                         const float* gamma, const float* beta,
                         float* running_mean, float* running_var, int64_t* num_batches_tracked,

@@ -145,6 +145,16 @@ inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s
         else return msx::set_error(MSX_ERR_INVALID, "unknown dtype %d", (int)(dtype)); \
     } while (0)
 
+// What a gather-form conv kernel does to an accumulator column c before storing it:
+//   v += bias[c] (ConvTranspose2d bias);  v = v * scale[c] + shift[c] (eval-mode BatchNorm folded to an affine);  ReLU.
+// All pointers nullable; columns >= the logical channel count store zeros.
+struct ConvEpilogue {
+    const float* bias;
+    const float* scale;
+    const float* shift;
+    int relu;
+};
+
 // ---- internal cross-file entry points -------------------------------------------------------
 // channel-reduction partial sums: [nblk][2][cp] doubles
 size_t bn_partials_bytes(int channels);
@@ -155,6 +165,10 @@ int bn_finalize_launch(const double* partials, int nblk, int channels, int64_t c
                        int64_t* num_batches_tracked, cudaStream_t st);
 int bn_eval_stats_launch(int channels, const float* running_mean, const float* running_var, float eps,
                          float* mean, float* invstd, cudaStream_t st);
+// eval-mode BN as y*scale + shift (scale = gamma*invstd, shift = beta - mean*scale [+ bias*scale]); arrays of round_up(channels, 8)
+int bn_eval_affine_launch(int channels, const float* running_mean, const float* running_var, float eps,
+                          const float* gamma, const float* beta, const float* conv_bias,
+                          float* mean, float* invstd, float* scale, float* shift, cudaStream_t st);
 int bn_apply_launch(int dtype, const void* x, int ldx, void* z, int ldz, int64_t pixels, int channels,
                     const float* mean, const float* invstd, const float* gamma, const float* beta, int relu,
                     cudaStream_t st);

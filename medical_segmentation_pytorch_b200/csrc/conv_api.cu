@@ -9,14 +9,14 @@ int conv_pack_launch(const msx_conv_desc* d, int mode, const float* w, void* pac
 size_t conv_pack_plan_bytes(const msx_pack_item* items, int count);
 int conv_pack_plan_build(const msx_pack_item* items, int count, void* table, size_t table_bytes, int* chunks_out);
 int conv_pack_plan_run(int dtype, const void* table, int count, int chunks, double bytes, cudaStream_t st);
-int conv_gather_simt(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
+int conv_gather_simt(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const ConvEpilogue& ep,
                      void* dst, cudaStream_t st);
 size_t conv_wgrad_ws_bytes(const msx_conv_desc* d);
 int conv_wgrad_simt(const msx_conv_desc* d, const void* x, const void* dy, float* dw, void* ws, size_t ws_bytes,
                     cudaStream_t st);
 // tcgen05 engine (conv_tc.cu)
 bool conv_tc_supported(const msx_conv_desc* d, bool fwd_pass);
-int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
+int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const ConvEpilogue& ep,
                    void* dst, cudaStream_t st);
 
 size_t conv_wgrad_tc_ws_bytes(const msx_conv_desc* d);
@@ -31,13 +31,17 @@ static int conv_wgrad(const msx_conv_desc* d, const void* x, const void* dy, flo
     return conv_wgrad_simt(d, x, dy, dw, ws, ws_bytes, st);
 }
 
-static int conv_gather(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
+static int conv_gather(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const ConvEpilogue& ep,
                        void* dst, cudaStream_t st) {
     const bool want_tc = d->engine == MSX_ENGINE_TCGEN05 || (d->engine == MSX_ENGINE_AUTO && d->dtype == MSX_BF16);
-    if (want_tc && conv_tc_supported(d, fwd_pass)) return conv_gather_tc(d, fwd_pass, src, packed, bias, dst, st);
+    if (want_tc && conv_tc_supported(d, fwd_pass)) return conv_gather_tc(d, fwd_pass, src, packed, ep, dst, st);
     if (d->engine == MSX_ENGINE_TCGEN05)
         return set_error(MSX_ERR_UNSUPPORTED, "conv: tcgen05 engine requested for a shape/dtype it does not support");
-    return conv_gather_simt(d, fwd_pass, src, packed, bias, dst, st);
+    return conv_gather_simt(d, fwd_pass, src, packed, ep, dst, st);
+}
+static int conv_gather(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
+                       void* dst, cudaStream_t st) {
+    return conv_gather(d, fwd_pass, src, packed, ConvEpilogue{bias, nullptr, nullptr, 0}, dst, st);
 }
 
 static size_t ws_conv_bytes(const msx_conv_desc* d) {
@@ -117,12 +121,23 @@ int msx_conv_bn_act_fwd(const msx_conv_desc* d, const void* x, const float* w_ma
                         void* w_packed, void* y_raw, void* z, int32_t ldz, float* save_mean, float* save_invstd,
                         void* ws, size_t ws_bytes, void* stream) {
     MSX_TRY(validate_desc(d));
-    MSX_REQUIRE(x && gamma && beta && w_packed && y_raw && z && save_mean && save_invstd, "conv_bn_act_fwd: null pointer");
+    MSX_REQUIRE(x && gamma && beta && w_packed && z && save_mean && save_invstd, "conv_bn_act_fwd: null pointer");
     MSX_REQUIRE(training || (running_mean && running_var), "conv_bn_act_fwd: eval mode needs running statistics");
+    MSX_REQUIRE(y_raw || !training, "conv_bn_act_fwd: y_raw may only be NULL in eval mode");
     if (ws_bytes < bn_partials_bytes(d->cout)) return set_error(MSX_ERR_WORKSPACE, "conv_bn_act_fwd: workspace %zu < %zu", ws_bytes, bn_partials_bytes(d->cout));
     cudaStream_t st = as_stream(stream);
     const int64_t pixels = (int64_t)d->n * d->oh * d->ow;
     if (w_master) MSX_TRY(conv_pack_launch(d, MSX_PACK_FPROP, w_master, w_packed, st));
+    if (!y_raw) {
+        // inference (no backward will follow): eval-mode BN is an affine per channel, applied with the ReLU in the
+        // conv epilogue straight from the fp32 accumulators - no raw conv output, no BN pass
+        float* scale = static_cast<float*>(ws);
+        float* shift = scale + round_up(d->cout, 8);
+        MSX_TRY(bn_eval_affine_launch(d->cout, running_mean, running_var, eps, gamma, beta, bias, save_mean, save_invstd, scale, shift, st));
+        msx_conv_desc dz = *d;
+        dz.ldy = ldz;
+        return conv_gather(&dz, true, x, w_packed, ConvEpilogue{nullptr, scale, shift, relu}, z, st);
+    }
     MSX_TRY(conv_gather(d, true, x, w_packed, bias, y_raw, st));
     if (training) {
         int nblk = 0;

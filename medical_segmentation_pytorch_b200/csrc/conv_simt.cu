@@ -49,7 +49,7 @@ __device__ inline bool map_coord(int o, int tap, int mul_d, int mul_t, int off, 
 
 template <typename T, int TN>
 __global__ void __launch_bounds__(256) conv_gather_kernel(const T* __restrict__ src, const T* __restrict__ wp,
-                                                          const float* __restrict__ bias, T* __restrict__ dst, GatherGeom g) {
+                                                          const ConvEpilogue ep, T* __restrict__ dst, GatherGeom g) {
     constexpr int BM = 64, BK = 16, BN = 16 * TN;
     __shared__ __align__(16) float As[BK][BM + 4];
     __shared__ __align__(16) float Bs[BK][BN + 4];
@@ -121,19 +121,27 @@ __global__ void __launch_bounds__(256) conv_gather_kernel(const T* __restrict__ 
     const int ncp = round_up(g.Nc, 8);
     const int nb = n0 + tx * TN;
     if (nb >= ncp) return;
-    float bv[TN];
+    float bv[TN], sc[TN], sh[TN];
 #pragma unroll
-    for (int j = 0; j < TN; ++j) bv[j] = (bias && nb + j < g.Nc) ? bias[nb + j] : 0.f;
+    for (int j = 0; j < TN; ++j) {
+        const bool in = nb + j < g.Nc;
+        bv[j] = (ep.bias && in) ? ep.bias[nb + j] : 0.f;
+        sc[j] = ep.scale ? (in ? ep.scale[nb + j] : 0.f) : 1.f;
+        sh[j] = (ep.scale && in) ? ep.shift[nb + j] : 0.f;
+    }
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
         const int64_t p = m0 + ty * 4 + i;
         if (p >= M) continue;
-        if constexpr (TN == 4) {
-            float o[4] = {acc[i][0] + bv[0], acc[i][1] + bv[1], acc[i][2] + bv[2], acc[i][3] + bv[3]};
-            store4(dst + p * g.ldd + nb, o);
-        } else {
-            store2(dst + p * g.ldd + nb, acc[i][0] + bv[0], acc[i][1] + bv[1]);
+        float o[TN];
+#pragma unroll
+        for (int j = 0; j < TN; ++j) {
+            o[j] = acc[i][j] + bv[j];
+            if (ep.scale) o[j] = fmaf(o[j], sc[j], sh[j]);
+            if (ep.relu) o[j] = fmaxf(o[j], 0.f);
         }
+        if constexpr (TN == 4) store4(dst + p * g.ldd + nb, o);
+        else store2(dst + p * g.ldd + nb, o[0], o[1]);
     }
 }
 
@@ -439,7 +447,7 @@ int conv_pack_launch(const msx_conv_desc* d, int mode, const float* w, void* pac
 }
 
 // fwd_pass: module forward (x->y) else data gradient (dy->dx).
-int conv_gather_simt(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
+int conv_gather_simt(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const ConvEpilogue& ep,
                      void* dst, cudaStream_t st) {
     GatherGeom g;
     g.N = d->n;
@@ -457,10 +465,10 @@ int conv_gather_simt(const msx_conv_desc* d, bool fwd_pass, const void* src, con
     MSX_DISPATCH_DTYPE(d->dtype, T, {
         if (ncp <= 32) {
             dim3 grid((unsigned)cdiv64(M, 64), (ncp + 31) / 32);
-            { ProfScope ps__(K_CONV_SIMT, st, (double)M * (g.K + g.Nc) * (double)sizeof(T), 2.0 * (double)M * g.Nc * g.K * g.kh * g.kw); conv_gather_kernel<T, 2><<<grid, 256, 0, st>>>(static_cast<const T*>(src), static_cast<const T*>(packed), bias, static_cast<T*>(dst), g); }
+            { ProfScope ps__(K_CONV_SIMT, st, (double)M * (g.K + g.Nc) * (double)sizeof(T), 2.0 * (double)M * g.Nc * g.K * g.kh * g.kw); conv_gather_kernel<T, 2><<<grid, 256, 0, st>>>(static_cast<const T*>(src), static_cast<const T*>(packed), ep, static_cast<T*>(dst), g); }
         } else {
             dim3 grid((unsigned)cdiv64(M, 64), (ncp + 63) / 64);
-            { ProfScope ps__(K_CONV_SIMT, st, (double)M * (g.K + g.Nc) * (double)sizeof(T), 2.0 * (double)M * g.Nc * g.K * g.kh * g.kw); conv_gather_kernel<T, 4><<<grid, 256, 0, st>>>(static_cast<const T*>(src), static_cast<const T*>(packed), bias, static_cast<T*>(dst), g); }
+            { ProfScope ps__(K_CONV_SIMT, st, (double)M * (g.K + g.Nc) * (double)sizeof(T), 2.0 * (double)M * g.Nc * g.K * g.kh * g.kw); conv_gather_kernel<T, 4><<<grid, 256, 0, st>>>(static_cast<const T*>(src), static_cast<const T*>(packed), ep, static_cast<T*>(dst), g); }
         }
     });
     MSX_LAUNCH_CHECK();

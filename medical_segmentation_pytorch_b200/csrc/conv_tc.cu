@@ -59,6 +59,26 @@ struct TcParams {
 // ---- PTX wrappers -----------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// bias / eval-BN affine / ReLU on NV accumulator columns starting at logical column col0 (uniform branches)
+template <int NV>
+__device__ __forceinline__ void epilogue_cols(uint32_t (&v)[NV], int col0, int Nc, const ConvEpilogue& ep) {
+    if (ep.bias) {
+#pragma unroll
+        for (int j = 0; j < NV; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + (col0 + j < Nc ? ep.bias[col0 + j] : 0.f));
+    }
+    if (ep.scale) {
+#pragma unroll
+        for (int j = 0; j < NV; ++j) {
+            float f = col0 + j < Nc ? fmaf(__uint_as_float(v[j]), ep.scale[col0 + j], ep.shift[col0 + j]) : 0.f;
+            if (ep.relu) f = fmaxf(f, 0.f);
+            v[j] = __float_as_uint(f);
+        }
+    } else if (ep.relu) {
+#pragma unroll
+        for (int j = 0; j < NV; ++j) v[j] = __float_as_uint(fmaxf(__uint_as_float(v[j]), 0.f));
+    }
+}
+
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
 }
@@ -164,7 +184,7 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t row_bytes
 
 __global__ void __launch_bounds__(kHaloThreads, 1)
 conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CUtensorMap tmB,
-               bf16* __restrict__ dst, const float* __restrict__ bias, const __grid_constant__ TcParams p) {
+               bf16* __restrict__ dst, const ConvEpilogue ep, const __grid_constant__ TcParams p) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;             // swizzle atoms need 1024 B alignment
     const uint32_t sA = base, sB = base + p.stages * p.a_stage;
@@ -278,10 +298,7 @@ conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CU
                 tmem_ld32(taddr + c0, v);
                 tmem_ld_wait();
                 if (valid) {
-                    if (bias) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + (n0 + c0 + j < p.Nc ? bias[n0 + c0 + j] : 0.f));
-                    }
+                    epilogue_cols<32>(v, n0 + c0, p.Nc, ep);
 #pragma unroll
                     for (int q = 0; q < 4; ++q)
                         if (c0 + 8 * q < ncols)
@@ -295,10 +312,7 @@ conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CU
                 tmem_ld16(taddr + c0, v);
                 tmem_ld_wait();
                 if (valid) {
-                    if (bias) {
-#pragma unroll
-                        for (int j = 0; j < 16; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + (n0 + c0 + j < p.Nc ? bias[n0 + c0 + j] : 0.f));
-                    }
+                    epilogue_cols<16>(v, n0 + c0, p.Nc, ep);
 #pragma unroll
                     for (int q = 0; q < 2; ++q)
                         if (c0 + 8 * q < ncols)
@@ -348,7 +362,7 @@ __device__ __forceinline__ uint64_t umma_desc_halo(uint32_t saddr, uint32_t sbo_
 template <int TAPS, int KSTEPS>
 __global__ void __launch_bounds__(kHaloThreads, 1)
 conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    bf16* __restrict__ dst, const float* __restrict__ bias, const HaloParams p) {
+                    bf16* __restrict__ dst, const ConvEpilogue ep, const HaloParams p) {
     extern __shared__ uint8_t smem_raw[];
     const int taps = p.kh * p.kw;
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -459,10 +473,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 tmem_ld32(taddr + c0, v);
                 tmem_ld_wait();
                 if (valid) {
-                    if (bias) {
-#pragma unroll
-                        for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + (c0 + j < p.Nc ? bias[c0 + j] : 0.f));
-                    }
+                    epilogue_cols<32>(v, c0, p.Nc, ep);
 #pragma unroll
                     for (int q = 0; q < 4; ++q)
                         if (c0 + 8 * q < ncols)
@@ -476,10 +487,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 tmem_ld16(taddr + c0, v);
                 tmem_ld_wait();
                 if (valid) {
-                    if (bias) {
-#pragma unroll
-                        for (int j = 0; j < 16; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + (c0 + j < p.Nc ? bias[c0 + j] : 0.f));
-                    }
+                    epilogue_cols<16>(v, c0, p.Nc, ep);
 #pragma unroll
                     for (int q = 0; q < 2; ++q)
                         if (c0 + 8 * q < ncols)
@@ -978,7 +986,7 @@ int conv_wgrad_tc(const msx_conv_desc* d, const void* x, const void* dy, float* 
     return wgrad_reduce_launch(static_cast<const float*>(ws), p.splits, taps, A, B, p.Apad, p.Bpad, dw, st);
 }
 
-static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
+static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const ConvEpilogue& ep,
                                void* dst, cudaStream_t st, bool* used) {
     *used = false;
     const int mode = halo_mode();
@@ -1031,7 +1039,7 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     const size_t smem = 1024 + bres + (size_t)p.stages * p.a_stage + 16 * kMaxStages + 16 * kMaxAcc + 96;
     const int grid = p.total_tiles < kNumSMs ? p.total_tiles : kNumSMs;
     const double M = (double)p.N * p.H * p.W;
-    typedef void (*HaloKernel)(const CUtensorMap, const CUtensorMap, bf16*, const float*, const HaloParams);
+    typedef void (*HaloKernel)(const CUtensorMap, const CUtensorMap, bf16*, const ConvEpilogue, const HaloParams);
     HaloKernel kern = nullptr;
 #define MSX_HALO_CASE(T, K) if (taps == T && p.ksteps == K) kern = conv_tc_halo_kernel<T, K>;
     MSX_HALO_CASE(9, 1) MSX_HALO_CASE(9, 2) MSX_HALO_CASE(9, 3) MSX_HALO_CASE(9, 4)
@@ -1050,7 +1058,7 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     }
     {
         ProfScope ps__(K_CONV_TC, st, M * (K + Nc) * 2.0, 2.0 * M * Nc * K * taps);
-        kern<<<grid, kHaloThreads, smem, st>>>(tmA, tmB, static_cast<bf16*>(dst), bias, p);
+        kern<<<grid, kHaloThreads, smem, st>>>(tmA, tmB, static_cast<bf16*>(dst), ep, p);
     }
     MSX_LAUNCH_CHECK();
     note_conv_engine(MSX_ENGINE_TCGEN05);
@@ -1115,12 +1123,12 @@ static unsigned build_taps(const msx_conv_desc* d, bool f_form, int pa, int pb, 
     return mask;
 }
 
-int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
+int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const ConvEpilogue& ep,
                    void* dst, cudaStream_t st) {
     const bool f_form = d->transposed ? !fwd_pass : fwd_pass;
     if (d->stride == 1 && !d->transposed) {
         bool used = false;
-        MSX_TRY(conv_gather_tc_halo(d, fwd_pass, src, packed, bias, dst, st, &used));
+        MSX_TRY(conv_gather_tc_halo(d, fwd_pass, src, packed, ep, dst, st, &used));
         if (used) return MSX_OK;
     }
     TcParams p;
@@ -1177,7 +1185,7 @@ int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const
         const double Mg = (double)p.N * p.H * p.W, Ms = (double)p.N * Hs * Ws / nphase;
         {
             ProfScope ps__(K_CONV_TC, st, (Mg * Nc + Ms * K) * 2.0, 2.0 * Mg * Nc * K * p.taps.n);
-            conv_tc_kernel<<<grid, kHaloThreads, smem, st>>>(maps, tmB, static_cast<bf16*>(dst), bias, p);
+            conv_tc_kernel<<<grid, kHaloThreads, smem, st>>>(maps, tmB, static_cast<bf16*>(dst), ep, p);
         }
         MSX_LAUNCH_CHECK();
     }

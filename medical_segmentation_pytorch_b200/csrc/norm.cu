@@ -176,6 +176,19 @@ __global__ void bn_eval_stats_kernel(int cp, int channels, const float* rm, cons
     invstd[c] = (float)(1.0 / sqrt((double)rv[c] + (double)eps));
 }
 
+__global__ void bn_eval_affine_kernel(int cp, int channels, const float* rm, const float* rv, float eps, const float* gamma,
+                                      const float* beta, const float* conv_bias, float* mean, float* invstd, float* scale, float* shift) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= cp) return;
+    if (c >= channels) { mean[c] = 0.f; invstd[c] = 0.f; scale[c] = 0.f; shift[c] = 0.f; return; }
+    const float is = (float)(1.0 / sqrt((double)rv[c] + (double)eps));
+    const float sc = is * gamma[c];                       // the same product bn_apply forms
+    mean[c] = rm[c];
+    invstd[c] = is;
+    scale[c] = sc;
+    shift[c] = fmaf((conv_bias ? conv_bias[c] : 0.f) - rm[c], sc, beta[c]);
+}
+
 // ---- apply --------------------------------------------------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(256) bn_apply_kernel(const T* __restrict__ x, int ldx, T* __restrict__ z, int ldz,
@@ -369,10 +382,19 @@ struct SumArgs {
 };
 template <typename T, bool STATS>
 __global__ void __launch_bounds__(256) sum_stats_kernel(SumArgs a, int up2x, int H, int W, T* __restrict__ s, int lds,
-                                                        int64_t pixels, int cp, int vch, double* __restrict__ partials) {
+                                                        int64_t pixels, int cp, int vch, double* __restrict__ partials,
+                                                        const float* __restrict__ scale = nullptr, const float* __restrict__ shift = nullptr,
+                                                        int relu = 0) {
     constexpr int VEC = Vec<T>::N;
     __shared__ double sh[STATS ? 2 * VEC * 256 : 1];
     const ChanThread t = chan_thread<VEC>(cp, vch);
+    // inference: eval-mode BN affine (+ReLU) applied to the sum before it is stored (STATS == false only)
+    float asc[VEC], ash[VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+        asc[j] = (!STATS && scale && t.active) ? scale[t.c0 + j] : 1.f;
+        ash[j] = (!STATS && scale && t.active) ? shift[t.c0 + j] : 0.f;
+    }
     double acc[2 * VEC];
     float fs[VEC], fq[VEC];
     int pending = 0;
@@ -406,6 +428,13 @@ __global__ void __launch_bounds__(256) sum_stats_kernel(SumArgs a, int up2x, int
 #pragma unroll
                             for (int j = 0; j < VEC; ++j) v[j] += u[i][j];
                         }
+                }
+            }
+            if (!STATS && scale) {
+#pragma unroll
+                for (int j = 0; j < VEC; ++j) {
+                    v[j] = fmaf(v[j], asc[j], ash[j]);
+                    if (relu) v[j] = fmaxf(v[j], 0.f);
                 }
             }
             Vec<T>::store(s + p * lds + t.c0, v);
@@ -616,6 +645,14 @@ int bn_eval_stats_launch(int channels, const float* rm, const float* rv, float e
     return MSX_OK;
 }
 
+int bn_eval_affine_launch(int channels, const float* rm, const float* rv, float eps, const float* gamma, const float* beta,
+                          const float* conv_bias, float* mean, float* invstd, float* scale, float* shift, cudaStream_t st) {
+    const int cp = round_up(channels, 8);
+    { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_eval_affine_kernel<<<(cp + 127) / 128, 128, 0, st>>>(cp, channels, rm, rv, eps, gamma, beta, conv_bias, mean, invstd, scale, shift); }
+    MSX_LAUNCH_CHECK();
+    return MSX_OK;
+}
+
 int bn_apply_launch(int dtype, const void* x, int ldx, void* z, int ldz, int64_t pixels, int channels,
                     const float* mean, const float* invstd, const float* gamma, const float* beta, int relu,
                     cudaStream_t st) {
@@ -690,8 +727,30 @@ int msx_sum_bn_act_fwd(int dtype, int n_in, const void* const* host_xs, const in
     int ldsrc = host_ldxs[0];
     int nblk = 0;
     const bool need_sum = n_in > 1 || up2x_first;
+    if (need_sum && !training && s == nullptr) {
+        // inference: one kernel sums the inputs, applies the eval-mode BN affine and the ReLU and writes z
+        MSX_REQUIRE(running_mean && running_var, "sum_bn_act: eval mode needs running statistics");
+        MSX_TRY(check_ld(ldz, channels, "sum_bn_act z"));
+        float* scale = reinterpret_cast<float*>(ws);
+        float* shift = scale + round_up(channels, 8);
+        MSX_TRY(bn_eval_affine_launch(channels, running_mean, running_var, eps, gamma, beta, nullptr, save_mean, save_invstd, scale, shift, st));
+        SumArgs a;
+        a.n = n_in;
+        for (int i = 0; i < n_in; ++i) {
+            MSX_TRY(check_ld(host_ldxs[i], channels, "sum_bn_act x"));
+            a.x[i] = host_xs[i];
+            a.ld[i] = host_ldxs[i];
+        }
+        MSX_DISPATCH_DTYPE(dtype, T, {
+            const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
+            { ProfScope ps__(K_SUM, st, (double)pixels * channels * (double)sizeof(T) * (n_in + 1.0), 0); sum_stats_kernel<T, false><<<dim3(stream_grid(pixels, c.lanes), c.nchunk), 256, 0, st>>>(
+                a, up2x_first, h, w, static_cast<T*>(z), ldz, pixels, c.cp, c.vch, nullptr, scale, shift, relu); }
+        });
+        MSX_LAUNCH_CHECK();
+        return MSX_OK;
+    }
     if (need_sum) {
-        MSX_REQUIRE(s != nullptr, "sum_bn_act: sum buffer required for n_in>1 or upsampling");
+        MSX_REQUIRE(s != nullptr, "sum_bn_act: sum buffer required for n_in>1 or upsampling (training, or a backward may follow)");
         MSX_TRY(check_ld(lds, channels, "sum_bn_act s"));
         SumArgs a;
         a.n = n_in;

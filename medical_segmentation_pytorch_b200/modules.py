@@ -56,8 +56,11 @@ def conv_bn_act(x, conv, bn, relu, slot=None):
     if not hasattr(conv, '_msx_geom'):
         conv._msx_geom = _geom_of(conv)
     momentum = 0.1 if bn.momentum is None else bn.momentum
+    # inference: eval mode and nothing that could be differentiated -> BN + ReLU run in the conv epilogue
+    infer = not bn.training and not (torch.is_grad_enabled() and (x.t.requires_grad or conv.weight.requires_grad or bn.weight.requires_grad
+                                                                  or bn.bias.requires_grad or (conv.bias is not None and conv.bias.requires_grad)))
     z = ops.ConvBNActFn.apply(x.t, conv.weight, conv.bias, bn.weight, bn.bias, bn.running_mean, bn.running_var,
-                              bn.num_batches_tracked, conv._msx_geom, bn.eps, momentum, bn.training, relu, slot)
+                              bn.num_batches_tracked, conv._msx_geom, bn.eps, momentum, bn.training, relu, slot, infer)
     return Act(z, conv.out_channels)
 
 
@@ -71,8 +74,10 @@ def sum_bn_act(xs, bn, relu=1, up2x=False, slot=None):
     """(sum of Acts) -> BN -> ReLU; xs[0] may be at half resolution when up2x."""
     c = xs[0].c
     momentum = 0.1 if bn.momentum is None else bn.momentum
+    infer = not bn.training and not (torch.is_grad_enabled() and (bn.weight.requires_grad or bn.bias.requires_grad
+                                                                  or any(a.t.requires_grad for a in xs)))
     z = ops.SumBNActFn.apply(bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.num_batches_tracked, c, bn.eps,
-                             momentum, bn.training, relu, up2x, slot, *[a.t for a in xs])
+                             momentum, bn.training, relu, up2x, slot, infer, *[a.t for a in xs])
     return Act(z, c)
 
 

@@ -173,12 +173,15 @@ class ConvBNActFn(torch.autograd.Function):
     """ConvBNAct / DeConvBNAct (models/modules.py:73-108) -> msx_conv_bn_act_{fwd,bwd}."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, gamma, beta, rm, rv, nbt, g, eps, momentum, training, relu, slot):
+    def forward(ctx, x, weight, bias, gamma, beta, rm, rv, nbt, g, eps, momentum, training, relu, slot, infer=False):
         n, h, w, _ = x.shape
         oh, ow = g.out_hw(h, w)
         cp = rup(g.cout)
         dev = x.device
-        y = torch.empty(n, oh, ow, cp, dtype=x.dtype, device=dev)
+        # inference (eval mode, nothing to differentiate): no raw conv output; BN affine + ReLU run in the conv epilogue
+        # infer: the caller saw that no backward can follow (ctx.needs_input_grad ignores torch.no_grad())
+        fused_eval = _EVAL_FUSION[0] and not training and infer
+        y = None if fused_eval else torch.empty(n, oh, ow, cp, dtype=x.dtype, device=dev)
         z = _out_tensor(slot, n, oh, ow, cp, x.dtype, dev)
         mean = torch.empty(cp, dtype=torch.float32, device=dev)
         invstd = torch.empty(cp, dtype=torch.float32, device=dev)
@@ -249,7 +252,7 @@ class ConvBNActFn(torch.autograd.Function):
                 dw = _pdone(weight, dw)
         else:
             dw = _pdone(weight, dw)
-        return (dx, dw, db, dgamma, dbeta) + (None,) * 9
+        return (dx, dw, db, dgamma, dbeta) + (None,) * 10
 
 
 class Conv2dFn(torch.autograd.Function):
@@ -333,6 +336,14 @@ def run_branches(jobs, main_job=0):
     return outs
 
 
+_EVAL_FUSION = [int(__import__('os').environ.get('MSX_EVAL_FUSION', '1'))]
+
+
+def set_eval_fusion(on):
+    """Inference: apply eval-mode BN + ReLU in the conv epilogue (default on) instead of as separate passes."""
+    _EVAL_FUSION[0] = int(bool(on))
+
+
 # ---- weight gradients on a side stream ---------------------------------------------------------
 _WGRAD_STREAM = [int(__import__('os').environ.get('MSX_WGRAD_STREAM', '1'))]
 _PENDING_JOIN = {}
@@ -383,19 +394,20 @@ class SumBNActFn(torch.autograd.Function):
     """(sum of inputs, first optionally nearest-2x upsampled) -> BN -> ReLU -> msx_sum_bn_act_fwd / msx_bn_act_bwd."""
 
     @staticmethod
-    def forward(ctx, gamma, beta, rm, rv, nbt, c, eps, momentum, training, relu, up2x, slot, *xs):
+    def forward(ctx, gamma, beta, rm, rv, nbt, c, eps, momentum, training, relu, up2x, slot, infer, *xs):
         ref = xs[1] if up2x else xs[0]
         n, h, w, cp = ref.shape
         dev, dt = ref.device, ref.dtype
         need_sum = len(xs) > 1 or up2x
-        s = torch.empty(n, h, w, cp, dtype=dt, device=dev) if need_sum else None
+        fused_eval = _EVAL_FUSION[0] and infer and not training and need_sum     # sum + BN affine + ReLU in one kernel
+        s = torch.empty(n, h, w, cp, dtype=dt, device=dev) if need_sum and not fused_eval else None
         z = _out_tensor(slot, n, h, w, cp, dt, dev)
         mean = torch.empty(cp, dtype=torch.float32, device=dev)
         invstd = torch.empty(cp, dtype=torch.float32, device=dev)
         ptrs, lds = _ptr_arrays(xs)
         ws = L.workspace(lib.msx_ws_bytes_bn(c), dev)
         L.check(lib.msx_sum_bn_act_fwd(
-            L.dtype_code(dt), len(xs), ptrs, lds, int(up2x), n, h, w, c, L.ptr(s), cp if need_sum else 0,
+            L.dtype_code(dt), len(xs), ptrs, lds, int(up2x), n, h, w, c, L.ptr(s), cp if s is not None else 0,
             L.ptr(_f32(gamma)), L.ptr(_f32(beta)), L.ptr(rm), L.ptr(rv), L.ptr(nbt), eps, momentum, int(training), int(relu),
             L.ptr(z), ld_of(z), L.ptr(mean), L.ptr(invstd), L.ptr(ws), ws.numel(), L.stream()))
         ctx.c, ctx.relu, ctx.up2x, ctx.nx = c, relu, up2x, len(xs)
@@ -422,10 +434,10 @@ class SumBNActFn(torch.autograd.Function):
             L.check(lib.msx_upsample2x_bwd(code, L.ptr(ds), cp, n, h, w, ctx.c, L.ptr(da), ld_of(da), L.stream()))
             grads[0] = da
         for i in range(ctx.nx):
-            if not ctx.needs_input_grad[12 + i]:
+            if not ctx.needs_input_grad[13 + i]:
                 grads[i] = None
         dbeta, dgamma = _pdone(beta, dbeta), _pdone(gamma, dgamma)
-        return (dgamma, dbeta) + (None,) * 10 + tuple(grads)
+        return (dgamma, dbeta) + (None,) * 11 + tuple(grads)
 
 
 def sum_n(ts, c):

@@ -475,3 +475,78 @@ def test_model_forward_repacks_changed_weights():
         y2 = m2(x)
     assert not torch.equal(y0, y1)
     assert torch.equal(y1, y2)
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize('kind', ['conv3', 'conv17', 'conv_d2', 'conv_s2', 'deconv', 'conv136'])
+def test_inference_epilogue_fusion_matches_unfused_eval(kind, dtype):
+    """Eval-mode ConvBNAct / DeConvBNAct under no_grad (BN affine + ReLU in the conv epilogue, y_raw = NULL) vs the
+    unfused eval path (taken when a gradient may be needed) and vs float64 conv -> BN(running stats) -> ReLU."""
+    from medical_segmentation_pytorch_b200 import modules
+    torch.manual_seed(11)
+    n, H = 2, 16
+    if kind == 'deconv':
+        cin, cout = 16, 8
+        m = modules.DeConvBNAct(cin, cout)
+        conv, bn = m.up_conv[0], m.up_conv[1]
+    else:
+        cin, cout, k, s, d = {'conv3': (3, 17, 3, 1, 1), 'conv17': (17, 17, 3, 1, 1), 'conv_d2': (24, 24, 3, 1, 2),
+                              'conv_s2': (17, 34, 3, 2, 1), 'conv136': (136, 136, 3, 1, 1)}[kind]
+        m = modules.ConvBNAct(cin, cout, k, s, d)
+        conv, bn = m[0], m[1]
+    with torch.no_grad():
+        bn.running_mean.copy_(torch.randn(cout) * 0.5)
+        bn.running_var.copy_(torch.rand(cout) + 0.5)
+        bn.weight.copy_(torch.randn(cout))
+        bn.bias.copy_(torch.randn(cout))
+        if dtype == torch.bfloat16:
+            conv.weight.copy_(conv.weight.bfloat16().float())
+    m = m.to(DEV).eval()
+    x = torch.randn(n, cin, H, H)
+    if dtype == torch.bfloat16:
+        x = x.bfloat16().float()
+    with torch.no_grad():
+        fused = m(to_act(x, dtype))
+    unfused = m(to_act(x, dtype, requires_grad=True))          # eval mode, but a backward could follow: keeps y_raw
+    xd = x.double()
+    cd = conv.double().cpu()
+    yref = cd(xd)
+    conv.float()
+    zref = torch.relu((yref - bn.running_mean.cpu().double()[None, :, None, None]) / torch.sqrt(bn.running_var.cpu().double() + bn.eps)[None, :, None, None]
+                      * bn.weight.detach().cpu().double()[None, :, None, None] + bn.bias.detach().cpu().double()[None, :, None, None])
+    assert float(fused.t[..., cout:].float().abs().sum()) == 0.0          # padded channels stay zero
+    e_f, e_u = rel(from_act(fused.t, cout), zref), rel(from_act(unfused.t.detach(), cout), zref)
+    print(f'eval fusion {kind} {dtype}: fused {e_f:.2e} unfused {e_u:.2e}')
+    tol = 1e-5 if dtype == torch.float32 else 8e-3
+    assert e_f < tol and e_u < tol
+    assert e_f <= 1.2 * e_u + 1e-6                                         # never less accurate than the two-pass path
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize('n_in,up2x', [(2, False), (6, False), (2, True)])
+def test_inference_sum_bn_relu_single_kernel(n_in, up2x, dtype):
+    """Eval-mode (sum of inputs [first nearest-2x upsampled]) -> BN -> ReLU under no_grad runs as ONE kernel (s = NULL);
+    compared with the two-pass eval path and with float64."""
+    from medical_segmentation_pytorch_b200 import modules
+    torch.manual_seed(5)
+    n, c, H = 2, 20, 12
+    bn = torch.nn.BatchNorm2d(c)
+    with torch.no_grad():
+        bn.running_mean.copy_(torch.randn(c) * 0.5)
+        bn.running_var.copy_(torch.rand(c) + 0.5)
+        bn.weight.copy_(torch.randn(c))
+        bn.bias.copy_(torch.randn(c))
+    bn = bn.to(DEV).eval()
+    xs = [torch.randn(n, c, H // 2 if (up2x and i == 0) else H, H // 2 if (up2x and i == 0) else H) for i in range(n_in)]
+    if dtype == torch.bfloat16:
+        xs = [x.bfloat16().float() for x in xs]
+    with torch.no_grad():
+        fused = modules.sum_bn_act([to_act(x, dtype) for x in xs], bn, 1, up2x=up2x)
+    unfused = modules.sum_bn_act([to_act(x, dtype, requires_grad=True) for x in xs], bn, 1, up2x=up2x)
+    tot = sum((F.interpolate(x.double(), scale_factor=2, mode='nearest') if (up2x and i == 0) else x.double()) for i, x in enumerate(xs))
+    b = lambda t: t.detach().cpu().double()[None, :, None, None]          # noqa: E731
+    zref = torch.relu((tot - b(bn.running_mean)) / torch.sqrt(b(bn.running_var) + bn.eps) * b(bn.weight) + b(bn.bias))
+    e_f, e_u = rel(from_act(fused.t, c), zref), rel(from_act(unfused.t.detach(), c), zref)
+    assert float(fused.t[..., c:].float().abs().sum()) == 0.0
+    tol = 1e-6 if dtype == torch.float32 else 6e-3
+    assert e_f < tol and e_u < tol and e_f <= 1.2 * e_u + 1e-7
