@@ -186,6 +186,14 @@ int msx_bn_act_bwd_static(int dtype, const void* s, int32_t lds, const void* dz,
                           const float* gamma, const float* beta, const float* save_mean, const float* save_invstd,
                           int relu, void* ds, int32_t ldds, float* dgamma, float* dbeta, void* stream);
 
+/* Forward-only helpers of the distillation teacher (smp.Unet over a torchvision ResNet, un-vendored dependencies
+ * segmentation-models-pytorch 0.3.2 / torchvision; call site models/__init__.py:43-58, core/seg_trainer.py:70-72):
+ * out = [relu](sum_i xs[i]) with xs[0] optionally nearest-2x upsampled first.  n_in = 2, relu = 1 is a residual
+ * block's `relu(out + identity)`; n_in = 1, up2x_first = 1 is the decoder's F.interpolate(scale_factor=2, 'nearest')
+ * written straight into its slice of the concat buffer (ldout). */
+int msx_sum_act(int dtype, int n_in, const void* const* host_xs, const int32_t* host_ldxs, int up2x_first,
+                int32_t n, int32_t h, int32_t w, int32_t channels, int relu, void* out, int32_t ldout, void* stream);
+
 /* backward of the nearest-2x upsample: da[n,y,x,:] = sum of the 2x2 block of ds. */
 int msx_upsample2x_bwd(int dtype, const void* ds, int32_t ldds, int32_t n, int32_t h, int32_t w,
                        int32_t channels, void* da, int32_t ldda, void* stream);

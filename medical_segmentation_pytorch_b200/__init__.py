@@ -11,6 +11,7 @@ from .metrics import Dice, JaccardIndex, get_seg_metrics
 from .optim import FusedOptimizer, ModelEma, get_ema_model, get_optimizer
 from .parallel import (DistributedDataParallelB200, de_parallel, destroy_ddp_process, is_parallel, parallel_model,
                        sampler_set_epoch, set_device)
+from .teacher import SmpUnet
 from .unet import UNet
 
 
@@ -27,7 +28,26 @@ def get_model(config):
     raise NotImplementedError(f"Unsupport model type: {config.model}")
 
 
-__all__ = ['UNet', 'DuckNet', 'get_model', 'get_loss_fn', 'kd_loss_fn', 'get_seg_metrics', 'parallel_model',
+def get_teacher_model(config, device):
+    """models/__init__.py:42-62: the frozen distillation teacher, ``smp.Unet`` over a ResNet encoder (the only
+    decoder/encoder family built here), loaded from ``config.teacher_ckpt['state_dict']`` and put in eval mode."""
+    import os
+    import torch
+    if not config.kd_training:
+        return None
+    if not os.path.isfile(config.teacher_ckpt):
+        raise ValueError(f'Could not find teacher checkpoint at path {config.teacher_ckpt}.')
+    if config.teacher_decoder != 'unet':
+        raise ValueError(f"Unsupported teacher decoder type: {config.teacher_decoder}")
+    model = SmpUnet(encoder_name=config.teacher_encoder, encoder_weights=None, in_channels=config.num_channel,
+                    classes=config.num_class)
+    ckpt = torch.load(config.teacher_ckpt, map_location=torch.device('cpu'))
+    model.load_state_dict(ckpt['state_dict'])
+    del ckpt
+    return model.to(device).eval()
+
+
+__all__ = ['UNet', 'DuckNet', 'SmpUnet', 'get_model', 'get_teacher_model', 'get_loss_fn', 'kd_loss_fn', 'get_seg_metrics', 'parallel_model',
            'de_parallel', 'is_parallel', 'set_device', 'destroy_ddp_process', 'sampler_set_epoch', 'get_optimizer',
            'get_ema_model', 'FusedOptimizer', 'ModelEma', 'CrossEntropyLoss', 'OhemCELoss', 'DiceBCELoss',
            'JaccardIndex', 'Dice', 'DistributedDataParallelB200', 'MsxError']

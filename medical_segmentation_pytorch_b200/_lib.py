@@ -70,6 +70,7 @@ def _load():
         'msx_bn_act_bwd': (C.c_int, [C.c_int, p, i32, p, i32, i64, i32, p, p, p, p, C.c_int, p, i32, p, p, p, sz, p]),
         'msx_bn_act_bwd_static': (C.c_int, [C.c_int, p, i32, p, i32, i64, i32, p, p, p, p, C.c_int, p, i32, p, p, p]),
         'msx_sum_n': (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(i32), i64, i32, p, i32, p]),
+        'msx_sum_act': (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(i32), C.c_int, i32, i32, i32, i32, C.c_int, p, i32, p]),
         'msx_upsample2x_bwd': (C.c_int, [C.c_int, p, i32, i32, i32, i32, i32, p, i32, p]),
         'msx_maxpool3s2_fwd': (C.c_int, [C.c_int, p, i32, i32, i32, i32, i32, p, i32, p, i32, p]),
         'msx_maxpool3s2_bwd': (C.c_int, [C.c_int, p, i32, p, i32, i32, i32, i32, i32, p, i32, p]),

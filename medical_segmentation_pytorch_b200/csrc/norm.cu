@@ -430,10 +430,10 @@ __global__ void __launch_bounds__(256) sum_stats_kernel(SumArgs a, int up2x, int
                         }
                 }
             }
-            if (!STATS && scale) {
+            if (!STATS && (scale || relu)) {
 #pragma unroll
                 for (int j = 0; j < VEC; ++j) {
-                    v[j] = fmaf(v[j], asc[j], ash[j]);
+                    if (scale) v[j] = fmaf(v[j], asc[j], ash[j]);
                     if (relu) v[j] = fmaxf(v[j], 0.f);
                 }
             }
@@ -794,6 +794,28 @@ int msx_sum_n(int dtype, int n_in, const void* const* host_xs, const int32_t* ho
         const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
         { ProfScope ps__(K_SUM, as_stream(stream), (double)pixels * channels * (double)sizeof(T) * (n_in + 1.0), 0); sum_stats_kernel<T, false><<<dim3(stream_grid(pixels, c.lanes), c.nchunk), 256, 0, as_stream(stream)>>>(
             a, 0, 1, 1, static_cast<T*>(out), ldout, pixels, c.cp, c.vch, nullptr); }
+    });
+    MSX_LAUNCH_CHECK();
+    return MSX_OK;
+}
+
+int msx_sum_act(int dtype, int n_in, const void* const* host_xs, const int32_t* host_ldxs, int up2x_first,
+                int32_t n, int32_t h, int32_t w, int32_t channels, int relu, void* out, int32_t ldout, void* stream) {
+    MSX_REQUIRE(n_in >= 1 && n_in <= 8 && host_xs && host_ldxs && out, "sum_act: bad arguments");
+    MSX_REQUIRE(!up2x_first || (h % 2 == 0 && w % 2 == 0), "sum_act: nearest-2x needs even h, w (got %dx%d)", h, w);
+    MSX_TRY(check_ld(ldout, channels, "sum_act out"));
+    SumArgs a;
+    a.n = n_in;
+    for (int i = 0; i < n_in; ++i) {
+        MSX_TRY(check_ld(host_ldxs[i], channels, "sum_act x"));
+        a.x[i] = host_xs[i];
+        a.ld[i] = host_ldxs[i];
+    }
+    const int64_t pixels = (int64_t)n * h * w;
+    MSX_DISPATCH_DTYPE(dtype, T, {
+        const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
+        { ProfScope ps__(K_SUM, as_stream(stream), (double)pixels * channels * (double)sizeof(T) * (n_in + 1.0), 0); sum_stats_kernel<T, false><<<dim3(stream_grid(pixels, c.lanes), c.nchunk), 256, 0, as_stream(stream)>>>(
+            a, up2x_first, h, w, static_cast<T*>(out), ldout, pixels, c.cp, c.vch, nullptr, nullptr, nullptr, relu); }
     });
     MSX_LAUNCH_CHECK();
     return MSX_OK;

@@ -127,3 +127,16 @@ def test_bucketed_allreduce_world2_gloo():
         p.join(60)
         assert p.exitcode == 0
     assert all(ok and reset for _, ok, reset in res)
+
+
+def test_teacher_state_dict_matches_the_oracle_layout():
+    """The product teacher's parameter holders carry smp/torchvision names, shapes and order, so a reference teacher
+    checkpoint loads unchanged (models/__init__.py:52-53)."""
+    import medical_segmentation_pytorch_b200 as msx
+    from oracle.ref_teacher import SmpUnetRef
+    for enc in ('resnet18', 'resnet101'):
+        a, b = msx.SmpUnet(enc, None, 3, 2), SmpUnetRef(enc, 3, 2)
+        sa, sb = a.state_dict(), b.state_dict()
+        assert list(sa.keys()) == list(sb.keys())
+        assert all(sa[k].shape == sb[k].shape and sa[k].dtype == sb[k].dtype for k in sb)
+        a.load_state_dict(sb)

@@ -95,3 +95,20 @@ def test_dice_bce_is_the_stated_composite():
     want = torch.nn.functional.binary_cross_entropy_with_logits(z, t) + \
         (1 - (2 * (torch.sigmoid(z) * t).sum() + 1.0) / (torch.sigmoid(z).sum() + t.sum() + 1.0))
     assert abs(ref_loss.dice_bce_loss(z, t).item() - want.item()) < 1e-14
+
+
+def test_teacher_oracle_param_counts_and_keys():
+    """smp.Unet(resnet18) = 14.33 M parameters (reference README.md:113) - the one known answer the teacher restatement
+    can be pinned by; resnet101 = 42,500,160 encoder + 9,012,928 decoder + 290 head."""
+    import torch
+    from oracle.ref_teacher import SmpUnetRef
+    r18 = SmpUnetRef('resnet18', 3, 2)
+    assert sum(p.numel() for p in r18.parameters()) == 14_328_354
+    r101 = SmpUnetRef('resnet101', 3, 2)
+    assert sum(p.numel() for p in r101.encoder.parameters()) == 42_500_160
+    assert sum(p.numel() for p in r101.decoder.parameters()) == 9_012_928
+    assert sum(p.numel() for p in r101.segmentation_head.parameters()) == 290
+    with torch.no_grad():
+        assert r18.eval()(torch.zeros(1, 3, 64, 64)).shape == (1, 2, 64, 64)
+    keys = list(r101.state_dict().keys())
+    assert keys[0] == 'encoder.conv1.weight' and 'decoder.blocks.0.conv1.0.weight' in keys and keys[-1] == 'segmentation_head.0.bias'
