@@ -16,6 +16,7 @@ int conv_wgrad_simt(const msx_conv_desc* d, const void* x, const void* dy, float
                     cudaStream_t st);
 // tcgen05 engine (conv_tc.cu)
 bool conv_tc_supported(const msx_conv_desc* d, bool fwd_pass);
+bool conv_tc_gather_supported(const msx_conv_desc* d, bool fwd_pass);
 int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const ConvEpilogue& ep,
                    void* dst, cudaStream_t st);
 
@@ -34,7 +35,7 @@ static int conv_wgrad(const msx_conv_desc* d, const void* x, const void* dy, flo
 static int conv_gather(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const ConvEpilogue& ep,
                        void* dst, cudaStream_t st) {
     const bool want_tc = d->engine == MSX_ENGINE_TCGEN05 || (d->engine == MSX_ENGINE_AUTO && d->dtype == MSX_BF16);
-    if (want_tc && conv_tc_supported(d, fwd_pass)) return conv_gather_tc(d, fwd_pass, src, packed, ep, dst, st);
+    if (want_tc && conv_tc_gather_supported(d, fwd_pass)) return conv_gather_tc(d, fwd_pass, src, packed, ep, dst, st);
     if (d->engine == MSX_ENGINE_TCGEN05)
         return set_error(MSX_ERR_UNSUPPORTED, "conv: tcgen05 engine requested for a shape/dtype it does not support");
     return conv_gather_simt(d, fwd_pass, src, packed, ep, dst, st);

@@ -33,7 +33,8 @@ constexpr int kMaxStages = 8;
 constexpr int kMaxAcc = 8;
 constexpr uint32_t kSmemBudget = 200 * 1024;
 
-constexpr int kTapMax = 16;
+constexpr int kTapMax = 49;          // tap table capacity (7x7); wgrad / dgrad stay within kTapMaxTrain
+constexpr int kTapMaxTrain = 16;
 struct TapTable {          // one entry per (source phase, shift, weight tap) the pass visits
     int n;
     signed char map[kTapMax], dx[kTapMax], dy[kTapMax], wtap[kTapMax];
@@ -926,13 +927,22 @@ void wgrad_plan(const msx_conv_desc* d, WgParams& p) {
 bool conv_tc_supported(const msx_conv_desc* d, bool fwd_pass) {
     (void)fwd_pass;
     if (d->dtype != MSX_BF16 || encode_fn() == nullptr) return false;
-    if (d->kh * d->kw > kTapMax) return false;
+    if (d->kh * d->kw > kTapMaxTrain) return false;
     if (d->stride == 1) return !d->transposed && d->oh == d->h && d->ow == d->w;      // 'same' convs of the reference
     if (d->stride != 2 || d->dil != 1 || d->kh < 2 || d->kw < 2) return false;
     // stride 2 (Conv2d 3x3 p1 / 2x2 p0, ConvTranspose2d 3x3 p1 op1): fine side even and exactly twice the coarse side
     const int fh = d->transposed ? d->oh : d->h, fw = d->transposed ? d->ow : d->w;
     const int ch = d->transposed ? d->h : d->oh, cw = d->transposed ? d->w : d->ow;
     return fh % 2 == 0 && fw % 2 == 0 && fh == 2 * ch && fw == 2 * cw;
+}
+
+// Forward gather only: additionally the 7x7 stride-2 stem of a ResNet encoder (49 taps through the four phase views);
+// its data / weight gradients are never needed (frozen teacher), so the training-side limit stays at 16 taps.
+bool conv_tc_gather_supported(const msx_conv_desc* d, bool fwd_pass) {
+    if (conv_tc_supported(d, fwd_pass)) return true;
+    if (!fwd_pass || d->dtype != MSX_BF16 || encode_fn() == nullptr || d->transposed) return false;
+    if (d->kh * d->kw > kTapMax || d->stride != 2 || d->dil != 1 || d->kh < 2 || d->kw < 2) return false;
+    return d->h % 2 == 0 && d->w % 2 == 0 && d->h == 2 * d->oh && d->w == 2 * d->ow;
 }
 
 size_t conv_wgrad_tc_ws_bytes(const msx_conv_desc* d) {

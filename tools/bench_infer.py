@@ -18,7 +18,9 @@ ap.add_argument('--iters', type=int, default=30)
 args = ap.parse_args()
 dev = torch.device('cuda')
 torch.manual_seed(1)
-if args.model.startswith('ducknet'):
+if args.model.startswith('teacher'):
+    model = msx.SmpUnet('resnet' + args.model[7:], None, 3, 2)
+elif args.model.startswith('ducknet'):
     model = msx.DuckNet(num_class=2, base_channel=int(args.model[7:]))
 else:
     model = msx.UNet(num_class=2, base_channel=int(args.model[4:]))
