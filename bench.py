@@ -157,6 +157,8 @@ def main():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--profile-steps', type=int, default=2)
     ap.add_argument('--ncu', action='store_true', help='short eager run for an ncu launch list: 1 warm-up + 1 step, no graph / e2e / profile pass')
+    ap.add_argument('--kd', default=None, metavar='ENCODER', help="BASELINE config 5: add a frozen smp.Unet(<ENCODER>, e.g. resnet101) teacher forward "
+                    "and the KL distillation term (T = 4, coefficient 1) to every step")
     ap.add_argument('--no-branch-streams', action='store_true', help='run sibling DUCK branches one after another on one stream')
     ap.add_argument('--no-graph', action='store_true', help='launch every kernel from Python instead of replaying one CUDA graph per step')
     args = ap.parse_args()
@@ -187,6 +189,7 @@ def main():
 
     class Cfg:
         num_class, ignore_index, class_weights, loss_type, reduction = 2, 255, None, 'ce', 'mean'
+        kd_loss_type, kd_temperature = 'kl_div', 4.0               # configs/base_config.py:102-104
 
     torch.manual_seed(1)                                           # configs/base_config.py:75 random_seed = 1
     model = (msx.DuckNet if arch == 'ducknet' else msx.UNet)(num_class=2, n_channel=3, base_channel=base).to(dev)
@@ -197,6 +200,7 @@ def main():
     opt = msx.FusedOptimizer(model, 'adam', lr=0.1 * 0.01 * world)  # utils/optimizer.py:15 with my_config.py:23
     ema = msx.ModelEma(model)
     loss_fn = msx.get_loss_fn(Cfg, dev)
+    teacher = msx.SmpUnet(args.kd, None, 3, 2).to(dev).eval() if args.kd else None     # random-init (no checkpoints offline)
     xh, th = synth_batch(B, S, S, seed=1 + rank)
     xh, th = xh.pin_memory(), th.pin_memory()
     xd, td = xh.to(dev), th.to(dev)
@@ -205,7 +209,12 @@ def main():
     def step(x, t):
         opt.zero_grad()
         with torch.autocast('cuda', dtype=torch.bfloat16, enabled=bf16):
-            loss = loss_fn(net(x), t)
+            preds = net(x)
+            loss = loss_fn(preds, t)
+            if teacher is not None:                                 # core/seg_trainer.py:69-75
+                with torch.no_grad():
+                    tp = teacher(x)
+                loss = loss + 1.0 * msx.kd_loss_fn(Cfg, preds, tp.detach())
         loss.backward()
         opt.step()
         it[0] += 1
@@ -336,7 +345,7 @@ def main():
         traffic, traffic_note = None, None
         try:
             tr = json.load(open(os.path.join(ROOT, 'profiles', 'ncu_traffic.json'))).get(top)
-            if tr:
+            if tr and args.model == 'ducknet17' and not args.kd:      # the capture is of the headline workload's top kernel
                 traffic, traffic_note = tr['traffic_bytes'], f"{tr['kernel']} {tr['shape']}: algorithmic {tr['algorithmic_bytes']} B; {tr['source']}"
         except Exception:
             pass
@@ -352,7 +361,7 @@ def main():
         'metric': 'train_imgs_per_sec', 'value': value, 'unit': 'img/s', 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
         'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
         'dtype': 'bf16' if bf16 else 'f32', 'data': 'synthetic',
-        'config': {'workload': f'{args.model} training step (fwd+CE+bwd+Adam+EMA copy), {S}x{S}, batch {B}/GPU, num_class 2, per-GPU BN',
+        'config': {'workload': f'{args.model} training step (fwd+CE+' + (f'frozen smp.Unet({args.kd}) teacher fwd+KD(kl,T=4)+' if args.kd else '') + f'bwd+Adam+EMA copy), {S}x{S}, batch {B}/GPU, num_class 2, per-GPU BN',
                    'global_batch': B * world, 'parallelism': f'dp{world}', 'l2': 'per-step working set >> 126 MB L2 (no flush needed)',
                    'seed': 'weights manual_seed(1); data PCG64(1+rank)',
                    'launch': 'one CUDA graph replay per step' if graph is not None else 'eager Python launches' + (f' (graph capture failed: {graph_err})' if graph_err else '')},
