@@ -29,6 +29,7 @@ namespace {
 
 constexpr int kThreads = 192;
 constexpr int kHaloThreads = 320;      // TMA warp + MMA warp + 2 x 4 epilogue warps
+constexpr int kHaloThreads2 = 352;     // halo kernel: + a second MMA-issuing warp (warp 10)
 constexpr int kMaxStages = 8;
 constexpr int kMaxAcc = 8;
 constexpr uint32_t kSmemBudget = 200 * 1024;
@@ -339,17 +340,24 @@ conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CU
 // "Halo" variant for layers whose whole reduction fits one 64-channel chunk and whose weights fit in
 // shared memory (DUCK-Net's 17/34-channel levels, UNet's 32/64: >80 % of the conv bytes).
 // The streaming kernel above re-fetches the A tile once per tap (9x L2->SM traffic for a 3x3).  Here the
-// tile is an 8 (x) by 16 (y) pixel patch and ONE TMA box brings the patch plus its halo, Wh = 16 (or 8)
-// pixels wide, into shared memory.  Because the row pitch of the halo (Wh pixels = Wh*128 B) is a
-// multiple of the 1024 B swizzle period, the A operand of tap (r, s) is the same shared memory seen
-// through a descriptor whose start is shifted by (r'*Wh + s') pixel rows and whose 8-row groups are
-// Wh*128 B apart: the 8 pixels of tile row dy are 8 consecutive halo rows.  All taps' weights stay resident.
+// tile is an 8 (x) by 16 (y) pixel patch and ONE TMA box brings the patch plus its halo, Wh = 8 + tap reach
+// pixels wide, into shared memory.  The 128B swizzle is a function of the absolute shared-memory address
+// (measured), so the A operand of tap (r, s) is the same shared memory seen through a descriptor whose start
+// is shifted by (r'*Wh + s') pixel rows and whose 8-row groups are Wh*128 B apart - whatever Wh is: the 8
+// pixels of tile row dy are 8 consecutive halo rows.  All taps' weights stay resident.
+// Measured cost model of this kernel at 105 tiles per CTA (17->17 and 32->32 layers at 352x352):
+//   one MMA issuer:  t/tile ~ 600 cycles of barrier round trips + ~57 cycles per 128xNx16 MMA with N = 32
+//                    (SS-mode operand fetch: 4 KB of A from shared memory per MMA, not the 16-cycle tensor floor)
+//   two issuers on alternate tiles hide the round trips; what is left is the TMA unit: ~670 cycles per box
+//   plus ~4 cycles per box row (pixel), independent of how many threads issue the copies.
 struct HaloParams {
     int N, H, W, tiles_x, tiles_y, total_tiles;
     int kh, kw, mul_t, off_h, off_w, oy_min, ox_min;
     int Wh, Hh, BN, ksteps, Nc, ncp, ldd;
     int stages, tmem_cols, nacc;   // nacc TMEM accumulators in flight (hides the commit -> epilogue -> release round trip)
     uint32_t a_bytes, a_stage, b_tap_bytes;
+    int issuers;                   // 1 or 2 MMA-issuing warps
+    int dbg;                       // MSX_DBG_HALO ablations (results are wrong): 1 no stores, 2 no MMAs, 4 no TMA loads, 8 no tcgen05.ld
 };
 
 // Start address shifted by whole 128 B pixel rows, base_offset field left 0: measured on B200, the
@@ -361,7 +369,7 @@ __device__ __forceinline__ uint64_t umma_desc_halo(uint32_t saddr, uint32_t sbo_
 }
 
 template <int TAPS, int KSTEPS>
-__global__ void __launch_bounds__(kHaloThreads, 1)
+__global__ void __launch_bounds__(kHaloThreads2, 1)
 conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     bf16* __restrict__ dst, const ConvEpilogue ep, const HaloParams p) {
     extern __shared__ uint8_t smem_raw[];
@@ -392,6 +400,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int tiles_per_img = p.tiles_x * p.tiles_y;
 
     if (warp == 0) {
+        // (a second TMA-issuing warp on alternate tiles was measured: no gain - the per-box cost is in the TMA unit)
         if (lane == 0) {
             mbar_expect_tx(bar_w, taps * p.b_tap_bytes);                       // resident weights, once per CTA
             for (int tap = 0; tap < taps; ++tap) tma_load_3d(sB + tap * p.b_tap_bytes, &tmB, bar_w, 0, 0, tap);
@@ -402,13 +411,19 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 const int ty = rem / p.tiles_x;
                 const int y0 = ty * 16, x0 = (rem - ty * p.tiles_x) * 8;
                 mbar_wait(bar_empty + 8 * stage, phase ^ 1);
-                mbar_expect_tx(bar_full + 8 * stage, p.a_bytes);
-                tma_load_4d(sA + stage * p.a_stage, &tmA, bar_full + 8 * stage, 0, x0 + p.ox_min, y0 + p.oy_min, img);
+                if (p.dbg & 4) mbar_arrive(bar_full + 8 * stage);
+                else {
+                    mbar_expect_tx(bar_full + 8 * stage, p.a_bytes);
+                    tma_load_4d(sA + stage * p.a_stage, &tmA, bar_full + 8 * stage, 0, x0 + p.ox_min, y0 + p.oy_min, img);
+                }
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
         }
-    } else if (warp == 1) {
-        if (lane == 0) {
+    } else if (warp == 1 || warp == 10) {
+        // Two issuers (p.issuers == 2) take alternate tiles: the per-tile barrier round trips of one overlap the
+        // tensor-pipe back-pressure of the other.  Accumulators and stages are per tile, so no ordering between them.
+        const int me = warp == 1 ? 0 : 1;
+        if (lane == 0 && me < p.issuers) {
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((128u >> 4) << 24);
             // The issuing thread is latency bound on its own instruction stream (measured: the issue loop, not
             // TMA, MMA or the epilogue, set the tile rate), so TAPS / KSTEPS are template constants, the loops
@@ -427,14 +442,16 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const uint32_t a_stage16 = p.a_stage >> 4, a_lo0 = ((sA & 0x3FFFFu) >> 4) | (1u << 16);
             mbar_wait(bar_w, 0);
             tc_fence_after();
-            int stage = 0, as = 0;
-            uint32_t phase = 0, aphase = 1;
-            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+            const int step = p.issuers;
+            int stage = me % stages, as = me % nacc;
+            uint32_t phase = (me / stages) & 1, aphase = 1 ^ ((me / nacc) & 1);
+            for (int t = blockIdx.x + me * gridDim.x; t < total; t += step * gridDim.x) {
                 mbar_wait(bar_tempty + 8 * as, aphase);
                 mbar_wait(bar_full + 8 * stage, phase);
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + as * BN;
                 const uint32_t a_lo = a_lo0 + stage * a_stage16;
+                if (!(p.dbg & 2)) {
 #pragma unroll
                 for (int tap = 0; tap < TAPS; ++tap) {
 #pragma unroll
@@ -443,10 +460,16 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         else umma_bf16_lh<1>(tmem_d, a_lo + a_off[tap] + 2 * k, hi_a, b_lo[tap] + 2 * k, hi_b, idesc);
                     }
                 }
-                umma_commit(bar_empty + 8 * stage);
-                umma_commit(bar_tfull + 8 * as);
-                if (++stage == stages) { stage = 0; phase ^= 1; }
-                if (++as == nacc) { as = 0; aphase ^= 1; }
+                }
+                if (p.dbg & 16) { mbar_arrive(bar_empty + 8 * stage); mbar_arrive(bar_tfull + 8 * as); }
+                else {
+                    umma_commit(bar_empty + 8 * stage);
+                    umma_commit(bar_tfull + 8 * as);
+                }
+                stage += step;
+                if (stage >= stages) { stage -= stages; phase ^= 1; }
+                as += step;
+                if (as >= nacc) { as -= nacc; aphase ^= 1; }
             }
         }
     } else {
@@ -462,7 +485,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const int img = t / tiles_per_img, rem = t - img * tiles_per_img;
             const int ty = rem / p.tiles_x;
             const int y = ty * 16 + dy, x = (rem - ty * p.tiles_x) * 8 + dx;
-            const bool valid = y < p.H && x < p.W;
+            const bool valid = y < p.H && x < p.W && !(p.dbg & 1);
             bf16* out = dst + ((int64_t)(img * p.H + y) * p.W + x) * p.ldd;
             const int as = it % p.nacc;
             const uint32_t taddr = tlane + as * p.BN;
@@ -471,8 +494,10 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             int c0 = 0;
             for (; c0 + 32 <= ncols || (c0 < ncols && ncols - c0 > 16); c0 += 32) {
                 uint32_t v[32];
-                tmem_ld32(taddr + c0, v);
-                tmem_ld_wait();
+                if (!(p.dbg & 8)) {
+                    tmem_ld32(taddr + c0, v);
+                    tmem_ld_wait();
+                }
                 if (valid) {
                     epilogue_cols<32>(v, c0, p.Nc, ep);
 #pragma unroll
@@ -1016,7 +1041,10 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     p.kh = d->kh; p.kw = d->kw;
     if (fwd_pass) { p.mul_t = d->dil; p.off_h = -d->pad_h; p.off_w = -d->pad_w; p.oy_min = p.off_h; p.ox_min = p.off_w; }
     else          { p.mul_t = -d->dil; p.off_h = d->pad_h; p.off_w = d->pad_w; p.oy_min = p.off_h - span_h; p.ox_min = p.off_w - span_w; }
-    p.Wh = span_w > 0 ? 16 : 8;
+    // Halo exactly as wide as the taps reach (MSX_HALO_TIGHT=0: padded to 16 pixels).  The 128B swizzle follows the
+    // absolute shared-memory address, so the row pitch need not be a multiple of the 1024 B swizzle period.
+    static const int tight = [] { const char* e = getenv("MSX_HALO_TIGHT"); return e ? atoi(e) : 1; }();
+    p.Wh = tight ? 8 + span_w : (span_w > 0 ? 16 : 8);
     p.Hh = 16 + span_h;
     p.BN = Np; p.ksteps = (Kp + 15) / 16;
     p.Nc = Nc; p.ncp = round_up(Nc, 8); p.ldd = fwd_pass ? d->ldy : d->ldx;
@@ -1029,6 +1057,10 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     if (p.stages < 2) return MSX_OK;
     p.nacc = 512 / p.BN < kMaxAcc ? 512 / p.BN : kMaxAcc;
     if (p.nacc % 2) --p.nacc;                                     // two epilogue groups alternate tiles
+    { const char* e = getenv("MSX_DBG_HALO"); p.dbg = e ? atoi(e) : 0; }
+    { static const int iss = [] { const char* e = getenv("MSX_HALO_ISSUERS"); return e && atoi(e) == 1 ? 1 : 2; }(); p.issuers = p.stages >= 2 && p.nacc >= 2 ? iss : 1; }
+    { const char* e = getenv("MSX_DBG_STAGES"); if (e && atoi(e) >= 2 && atoi(e) < p.stages) p.stages = atoi(e); }
+    { const char* e = getenv("MSX_DBG_NACC"); if (e && atoi(e) >= 2 && atoi(e) < p.nacc) p.nacc = atoi(e) & ~1; }
     int cols = 32;
     while (cols < p.nacc * p.BN) cols <<= 1;
     p.tmem_cols = cols;
@@ -1068,7 +1100,7 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     }
     {
         ProfScope ps__(K_CONV_TC, st, M * (K + Nc) * 2.0, 2.0 * M * Nc * K * taps);
-        kern<<<grid, kHaloThreads, smem, st>>>(tmA, tmB, static_cast<bf16*>(dst), ep, p);
+        kern<<<grid, kHaloThreads2, smem, st>>>(tmA, tmB, static_cast<bf16*>(dst), ep, p);
     }
     MSX_LAUNCH_CHECK();
     note_conv_engine(MSX_ENGINE_TCGEN05);
