@@ -1061,6 +1061,11 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     { static const int iss = [] { const char* e = getenv("MSX_HALO_ISSUERS"); return e && atoi(e) == 1 ? 1 : 2; }(); p.issuers = p.stages >= 2 && p.nacc >= 2 ? iss : 1; }
     { const char* e = getenv("MSX_DBG_STAGES"); if (e && atoi(e) >= 2 && atoi(e) < p.stages) p.stages = atoi(e); }
     { const char* e = getenv("MSX_DBG_NACC"); if (e && atoi(e) >= 2 && atoi(e) < p.nacc) p.nacc = atoi(e) & ~1; }
+    // Two issuers need an even stage (and accumulator) count: then every stage / accumulator belongs to ONE issuer and
+    // its mbarrier phases advance only with that thread's own progress.  With an odd count a stage alternates between
+    // the issuers, one of them can run two phases ahead of the other and a parity wait passes on the wrong phase
+    // (seen as a launch failure in the full step with 3 stages; the unit tests did not catch it).
+    if (p.issuers == 2) p.stages &= ~1;
     int cols = 32;
     while (cols < p.nacc * p.BN) cols <<= 1;
     p.tmem_cols = cols;
