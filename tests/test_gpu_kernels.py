@@ -550,3 +550,29 @@ def test_inference_sum_bn_relu_single_kernel(n_in, up2x, dtype):
     assert float(fused.t[..., c:].float().abs().sum()) == 0.0
     tol = 1e-6 if dtype == torch.float32 else 6e-3
     assert e_f < tol and e_u < tol and e_f <= 1.2 * e_u + 1e-7
+
+
+def test_halo_conv_repeatable_under_concurrency():
+    """The halo kernel's two MMA-issuing warps own disjoint stages / accumulators; a protocol slip shows up as a changed
+    result (or a trap) only at full size and with other kernels competing for the SMs: 30 launches of a 17->17 3x3 conv at
+    16x352x352 while a second stream runs bandwidth kernels, every result bit-identical to the first, and the first equal
+    to the FFMA engine's within bf16 rounding."""
+    ops = _ops()
+    torch.manual_seed(0)
+    n, c, H = 16, 17, 352
+    x = torch.randn(n, H, H, ops.rup(c), device=DEV).bfloat16()
+    x[..., c:] = 0
+    w = torch.nn.Parameter((torch.randn(c, c, 3, 3) / (9 * c) ** 0.5).to(DEV))
+    g_tc, g_simt = ops.ConvGeom(c, c, 3, 3, 1, 1, 1, 1, engine=2), ops.ConvGeom(c, c, 3, 3, 1, 1, 1, 1, engine=1)
+    side = torch.cuda.Stream()
+    noise = torch.randn(64 << 20, device=DEV)
+    with torch.no_grad():
+        ref = ops.Conv2dFn.apply(x, w, g_tc).clone()
+        simt = ops.Conv2dFn.apply(x, w, g_simt)
+        assert rel(ref[..., :c].float().cpu(), simt[..., :c].float().cpu()) < 6e-3
+        for i in range(30):
+            with torch.cuda.stream(side):
+                noise.mul_(1.0001)
+            y = ops.Conv2dFn.apply(x, w, g_tc)
+            assert torch.equal(y, ref), i
+    torch.cuda.synchronize()
