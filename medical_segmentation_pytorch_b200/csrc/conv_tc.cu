@@ -348,8 +348,9 @@ conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CU
 // Measured cost model of this kernel at 105 tiles per CTA (17->17 and 32->32 layers at 352x352):
 //   one MMA issuer:  t/tile ~ 600 cycles of barrier round trips + ~57 cycles per 128xNx16 MMA with N = 32
 //                    (SS-mode operand fetch: 4 KB of A from shared memory per MMA, not the 16-cycle tensor floor)
-//   two issuers on alternate tiles hide the round trips; what is left is the TMA unit: ~670 cycles per box
-//   plus ~4 cycles per box row (pixel), independent of how many threads issue the copies.
+//   two issuers on alternate tiles hide the round trips (17->17 3x3: 113 -> 85 us, 32->32: 109 -> 75 us).  What is left
+//   tracks the number of box rows (~4 cycles per pixel row of the halo box) and the shared-memory traffic of the MMAs;
+//   a second TMA-issuing thread and two-tile boxes (pair mode) did not move it.
 struct HaloParams {
     int N, H, W, tiles_x, tiles_y, total_tiles;
     int kh, kw, mul_t, off_h, off_w, oy_min, ox_min;
@@ -357,6 +358,7 @@ struct HaloParams {
     int stages, tmem_cols, nacc;   // nacc TMEM accumulators in flight (hides the commit -> epilogue -> release round trip)
     uint32_t a_bytes, a_stage, b_tap_bytes;
     int issuers;                   // 1 or 2 MMA-issuing warps
+    int tw, boxes_x, total_boxes;  // tw == 2 (pair mode): one TMA box covers two tiles side by side; issuer / epilogue group j takes tile j
     int dbg;                       // MSX_DBG_HALO ablations (results are wrong): 1 no stores, 2 no MMAs, 4 no TMA loads, 8 no tcgen05.ld
 };
 
@@ -383,7 +385,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < p.stages; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
+        for (int s = 0; s < p.stages; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, p.tw == 2 ? 2 : 1); }   // pair mode: both issuers release a box
         for (int a = 0; a < p.nacc; ++a) { mbar_init(bar_tfull + 8 * a, 1); mbar_init(bar_tempty + 8 * a, 4); }
         mbar_init(bar_w, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -397,7 +399,10 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     tc_fence_after();
     uint32_t tmem_base;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
-    const int tiles_per_img = p.tiles_x * p.tiles_y;
+    // work unit of the producer: one tile (8 x 16 pixels) or, in pair mode, a box of two tiles side by side (16 x 16)
+    const bool pair = p.tw == 2;
+    const int units_x = pair ? p.boxes_x : p.tiles_x, unit_w = pair ? 16 : 8;
+    const int tiles_per_img = units_x * p.tiles_y, total_units = pair ? p.total_boxes : p.total_tiles;
 
     if (warp == 0) {
         // (a second TMA-issuing warp on alternate tiles was measured: no gain - the per-box cost is in the TMA unit)
@@ -406,10 +411,10 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             for (int tap = 0; tap < taps; ++tap) tma_load_3d(sB + tap * p.b_tap_bytes, &tmB, bar_w, 0, 0, tap);
             int stage = 0;
             uint32_t phase = 0;
-            for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
+            for (int t = blockIdx.x; t < total_units; t += gridDim.x) {
                 const int img = t / tiles_per_img, rem = t - img * tiles_per_img;
-                const int ty = rem / p.tiles_x;
-                const int y0 = ty * 16, x0 = (rem - ty * p.tiles_x) * 8;
+                const int ty = rem / units_x;
+                const int y0 = ty * 16, x0 = (rem - ty * units_x) * unit_w;
                 mbar_wait(bar_empty + 8 * stage, phase ^ 1);
                 if (p.dbg & 4) mbar_arrive(bar_full + 8 * stage);
                 else {
@@ -438,14 +443,15 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
             const uint32_t hi_a = (uint32_t)((p.Wh * 128) >> 4) | (1u << 14) | (2u << 29);     // SBO, version 1, SWIZZLE_128B
             const uint32_t hi_b = (uint32_t)(1024 >> 4) | (1u << 14) | (2u << 29);
-            const int nacc = p.nacc, stages = p.stages, total = p.total_tiles, BN = p.BN;
-            const uint32_t a_stage16 = p.a_stage >> 4, a_lo0 = ((sA & 0x3FFFFu) >> 4) | (1u << 16);
+            const int nacc = p.nacc, stages = p.stages, total = total_units, BN = p.BN;
+            // pair mode: both issuers walk every box; issuer `me` computes the tile at x offset 8 * me (64 descriptor units)
+            const uint32_t a_stage16 = p.a_stage >> 4, a_lo0 = (((sA & 0x3FFFFu) >> 4) | (1u << 16)) + (pair ? me * 64 : 0);
             mbar_wait(bar_w, 0);
             tc_fence_after();
-            const int step = p.issuers;
-            int stage = me % stages, as = me % nacc;
-            uint32_t phase = (me / stages) & 1, aphase = 1 ^ ((me / nacc) & 1);
-            for (int t = blockIdx.x + me * gridDim.x; t < total; t += step * gridDim.x) {
+            const int step = pair ? 1 : p.issuers, astep = pair ? 2 : p.issuers;
+            int stage = pair ? 0 : me % stages, as = me % nacc;
+            uint32_t phase = pair ? 0 : (me / stages) & 1, aphase = 1 ^ ((me / nacc) & 1);
+            for (int t = pair ? blockIdx.x : blockIdx.x + me * gridDim.x; t < total; t += step * gridDim.x) {
                 mbar_wait(bar_tempty + 8 * as, aphase);
                 mbar_wait(bar_full + 8 * stage, phase);
                 tc_fence_after();
@@ -468,7 +474,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 }
                 stage += step;
                 if (stage >= stages) { stage -= stages; phase ^= 1; }
-                as += step;
+                as += astep;
                 if (as >= nacc) { as -= nacc; aphase ^= 1; }
             }
         }
@@ -481,10 +487,10 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int ncols = p.ncp;
         const uint32_t tlane = tmem_base + ((uint32_t)(quad * 32) << 16);
         int it = grp;
-        for (int t = blockIdx.x + grp * gridDim.x; t < p.total_tiles; t += 2 * gridDim.x, it += 2) {
+        for (int t = pair ? blockIdx.x : blockIdx.x + grp * gridDim.x; t < total_units; t += (pair ? 1 : 2) * gridDim.x, it += 2) {
             const int img = t / tiles_per_img, rem = t - img * tiles_per_img;
-            const int ty = rem / p.tiles_x;
-            const int y = ty * 16 + dy, x = (rem - ty * p.tiles_x) * 8 + dx;
+            const int ty = rem / units_x;
+            const int y = ty * 16 + dy, x = (rem - ty * units_x) * unit_w + (pair ? grp * 8 : 0) + dx;
             const bool valid = y < p.H && x < p.W && !(p.dbg & 1);
             bf16* out = dst + ((int64_t)(img * p.H + y) * p.W + x) * p.ldd;
             const int as = it % p.nacc;
@@ -1044,28 +1050,41 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     // Halo exactly as wide as the taps reach (MSX_HALO_TIGHT=0: padded to 16 pixels).  The 128B swizzle follows the
     // absolute shared-memory address, so the row pitch need not be a multiple of the 1024 B swizzle period.
     static const int tight = [] { const char* e = getenv("MSX_HALO_TIGHT"); return e ? atoi(e) : 1; }();
-    p.Wh = tight ? 8 + span_w : (span_w > 0 ? 16 : 8);
     p.Hh = 16 + span_h;
     p.BN = Np; p.ksteps = (Kp + 15) / 16;
     p.Nc = Nc; p.ncp = round_up(Nc, 8); p.ldd = fwd_pass ? d->ldy : d->ldx;
-    p.a_bytes = (uint32_t)p.Hh * p.Wh * 128;
-    p.a_stage = (p.a_bytes + 1023u) & ~1023u;
     p.b_tap_bytes = (uint32_t)p.BN * 128;
     const uint32_t bres = ((uint32_t)taps * p.b_tap_bytes + 1023u) & ~1023u;
-    int stages = (int)((kSmemBudget - bres) / p.a_stage);
-    p.stages = stages > kMaxStages ? kMaxStages : stages;
-    if (p.stages < 2) return MSX_OK;
     p.nacc = 512 / p.BN < kMaxAcc ? 512 / p.BN : kMaxAcc;
     if (p.nacc % 2) --p.nacc;                                     // two epilogue groups alternate tiles
     { const char* e = getenv("MSX_DBG_HALO"); p.dbg = e ? atoi(e) : 0; }
-    { static const int iss = [] { const char* e = getenv("MSX_HALO_ISSUERS"); return e && atoi(e) == 1 ? 1 : 2; }(); p.issuers = p.stages >= 2 && p.nacc >= 2 ? iss : 1; }
+    static const int iss = [] { const char* e = getenv("MSX_HALO_ISSUERS"); return e && atoi(e) == 1 ? 1 : 2; }();
+    static const int want_pair = [] { const char* e = getenv("MSX_HALO_PAIR"); return e ? atoi(e) : 0; }();
+    p.issuers = p.nacc >= 2 ? iss : 1;
+    // Pair mode (MSX_HALO_PAIR=1, off by default): one TMA box for two tiles side by side (16 x 16 pixels + halo), issuer
+    // and epilogue group j taking tile j.  Measured: 10 % faster for wide halos (3x3 d2 101 -> 89 us, 1x7 92 -> 81 us at
+    // 17 channels, 352x352), nothing for 3x3 d1, 10 % slower at 64 channels (fewer stages fit); the whole step is unchanged,
+    // so the per-box cost of the TMA unit is not what bounds these layers.  Kept for the next round's layout work.
+    p.boxes_x = (p.tiles_x + 1) / 2;
+    p.total_boxes = p.boxes_x * p.tiles_y * p.N;
+    p.tw = (want_pair && tight && p.issuers == 2 && (p.tiles_x % 2 == 0 || p.tiles_x >= 9)) ? 2 : 1;
+    for (;;) {
+        p.Wh = p.tw == 2 ? 16 + span_w : (tight ? 8 + span_w : (span_w > 0 ? 16 : 8));
+        p.a_bytes = (uint32_t)p.Hh * p.Wh * 128;
+        p.a_stage = (p.a_bytes + 1023u) & ~1023u;
+        int stages = bres + 2 * p.a_stage <= kSmemBudget ? (int)((kSmemBudget - bres) / p.a_stage) : 0;
+        p.stages = stages > kMaxStages ? kMaxStages : stages;
+        if (p.stages >= 2 || p.tw == 1) break;
+        p.tw = 1;                                                 // the wide box does not leave room for two stages
+    }
+    if (p.stages < 2) return MSX_OK;
     { const char* e = getenv("MSX_DBG_STAGES"); if (e && atoi(e) >= 2 && atoi(e) < p.stages) p.stages = atoi(e); }
     { const char* e = getenv("MSX_DBG_NACC"); if (e && atoi(e) >= 2 && atoi(e) < p.nacc) p.nacc = atoi(e) & ~1; }
     // Two issuers need an even stage (and accumulator) count: then every stage / accumulator belongs to ONE issuer and
     // its mbarrier phases advance only with that thread's own progress.  With an odd count a stage alternates between
     // the issuers, one of them can run two phases ahead of the other and a parity wait passes on the wrong phase
     // (seen as a launch failure in the full step with 3 stages; the unit tests did not catch it).
-    if (p.issuers == 2) p.stages &= ~1;
+    if (p.issuers == 2 && p.tw == 1) p.stages &= ~1;               // (pair mode: both issuers share every stage, released by both)
     int cols = 32;
     while (cols < p.nacc * p.BN) cols <<= 1;
     p.tmem_cols = cols;
@@ -1084,7 +1103,8 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
         MSX_TRY(make_map(&tmB, 3, packed, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B));
     }
     const size_t smem = 1024 + bres + (size_t)p.stages * p.a_stage + 16 * kMaxStages + 16 * kMaxAcc + 96;
-    const int grid = p.total_tiles < kNumSMs ? p.total_tiles : kNumSMs;
+    const int units = p.tw == 2 ? p.total_boxes : p.total_tiles;
+    const int grid = units < kNumSMs ? units : kNumSMs;
     const double M = (double)p.N * p.H * p.W;
     typedef void (*HaloKernel)(const CUtensorMap, const CUtensorMap, bf16*, const ConvEpilogue, const HaloParams);
     HaloKernel kern = nullptr;
