@@ -601,7 +601,7 @@ struct WgParams {
     int chunkA, chunkB, groupsB;      // channels per MN group, groups per B tile
     int Ap, Bp;                       // round_up(A, 8), round_up(B, 8): tensor-map channel extents
     int Apad, Bpad;                   // workspace leading dims (a_tiles*128, b_tiles*TN)
-    int stagesB, tmem_cols;
+    int stagesB, tmem_cols, SA;
     uint32_t a_stage, b_stage;
     int64_t pix_tiles;
     int halo, Wh, Hh;                 // halo mode: one x patch (+halo) per pixel tile serves every tap
@@ -620,11 +620,11 @@ __global__ void __launch_bounds__(kThreads, 1)
 wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ PhaseMaps tmG,
                 float* __restrict__ partial, const __grid_constant__ WgParams p) {
     extern __shared__ uint8_t smem_raw[];
-    constexpr int SA = 2;
+    const int SA = p.SA;                                   // dy-tile ring depth (2, or 4 when the tiles are small)
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t sA = base, sB = base + SA * p.a_stage;
     const uint32_t bars = sB + p.stagesB * p.b_stage;
-    const uint32_t barA_full = bars, barA_empty = bars + 16, barB_full = bars + 32, barB_empty = barB_full + 8 * kMaxStages;
+    const uint32_t barA_full = bars, barA_empty = bars + 32, barB_full = bars + 64, barB_empty = barB_full + 8 * kMaxStages;
     const uint32_t bar_done = barB_empty + 8 * kMaxStages, tmem_slot = bar_done + 8;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -949,7 +949,15 @@ void wgrad_plan(const msx_conv_desc* d, WgParams& p) {
             p.tmem_cols = cols2;
         }
     }
-    int sb = (int)((kSmemBudget - 2 * p.a_stage) / p.b_stage);
+    // dy ring: 4 stages when a stage is small (few channels); the stage is as large as the boxes that fill it
+    static const int sa_env = [] { const char* e = getenv("MSX_WGRAD_SA"); return e ? atoi(e) : 4; }();
+    {
+        const int groupsA = (((p.Ap < 128 ? p.Ap : 128) + p.chunkA - 1) / p.chunkA);
+        const uint32_t need = (uint32_t)groupsA * 128u * (p.chunkA * 2);
+        p.SA = (sa_env == 4 && need <= 16 * 1024) ? 4 : 2;
+        if (p.SA == 4) p.a_stage = (need + 1023u) & ~1023u;
+    }
+    int sb = (int)((kSmemBudget - p.SA * p.a_stage) / p.b_stage);
     p.stagesB = sb > kMaxStages ? kMaxStages : (sb < 2 ? 2 : sb);
 }
 
@@ -1015,7 +1023,7 @@ int conv_wgrad_tc(const msx_conv_desc* d, const void* x, const void* dy, float* 
         MSX_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
         attr_set = true;
     }
-    const size_t smem = 1024 + 2 * (size_t)p.a_stage + (size_t)p.stagesB * p.b_stage + 32 + 16 * kMaxStages + 64;
+    const size_t smem = 1024 + (size_t)p.SA * p.a_stage + (size_t)p.stagesB * p.b_stage + 64 + 16 * kMaxStages + 64;
     const int grid = p.a_tiles * p.b_tiles * p.tap_groups * p.splits;
     const int taps = p.kh * p.kw;
     const double Ms = (double)p.N * p.H * p.W, Mb = (double)p.N * Hb * Wb;
