@@ -80,11 +80,20 @@ class ClockSampler:
         return {'sm_mhz': sm[len(sm) // 2] if sm else None, 'sm_max_mhz': mx, 'reasons': sorted(reasons), 'samples': len(sm)}
 
 
+def _synth_batch_fn():
+    """synth.py loaded by file path: the reference arm must not import the package, which would map libmsx.so."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location('msx_synth', os.path.join(ROOT, 'medical_segmentation_pytorch_b200', 'synth.py'))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod.synth_batch
+
+
 def cpu_reference_leg(name, steps, warmup, batch=2, hw=352):
     """The reference's CPU training step (oracle port) on this box's host cores."""
     import torch
-    from medical_segmentation_pytorch_b200.synth import synth_batch
     from oracle.ref_step import CpuTrainer
+    synth_batch = _synth_batch_fn()
     arch, base, _, _ = MODELS[name]
     cores = os.cpu_count() or 1
     threads = max(1, cores // 2) if cores > 16 else cores          # physical cores on SMT hosts
@@ -94,6 +103,41 @@ def cpu_reference_leg(name, steps, warmup, batch=2, hw=352):
     return {'value': batch / sec, 'unit': 'img/s', 'cores': threads, 'kind': 'port',
             'sample': f'{steps} timed step(s) after {warmup} warm-up of {name} batch {batch} at {hw}x{hw} fp32 '
                       f'(oracle/ref_step.py: forward+CE+backward+Adam+EMA copy), {sec:.2f} s/step'}, sec
+
+
+def gpu_eager_leg(name, batch, hw, dev, steps=5, warmup=10):
+    """Same-box library comparator (tools/test_speed.py:29-58 discipline): the reference's step body on the
+    reference's own torch ops (oracle restatement on F.conv2d / F.batch_norm / ...), NCHW, cudnn.benchmark off, under
+    PyTorch eager on this GPU - (i) fp32 with TF32 convolutions (torch's default, which the reference never changes),
+    (ii) torch.autocast(bfloat16).  Runs after the timed region; cuDNN / cuBLAS kernels, none of this repo's."""
+    import torch
+    from oracle.ref_step import CpuTrainer
+    synth_batch = _synth_batch_fn()
+    arch, base, _, _ = MODELS[name]
+    torch.backends.cudnn.benchmark = False
+    out = {'how': f'oracle/ref_step.py on cuda (PyTorch eager, cuDNN/cuBLAS), batch {batch} at {hw}x{hw}, {warmup} warm-up + {steps} timed steps, CUDA events',
+           'cudnn_allow_tf32': bool(torch.backends.cudnn.allow_tf32)}
+    x, t = synth_batch(batch, hw, hw, seed=1)
+    x, t = x.to(dev), t.to(dev)
+    for tag, dt in (('tf32', None), ('bf16', torch.bfloat16)):
+        try:
+            tr = CpuTrainer(arch, base, 2, seed=1, lr=1e-3, device=dev)
+            for _ in range(warmup):
+                tr.train_step(x, t, autocast_dtype=dt, sync=False)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(steps):
+                loss = tr.train_step(x, t, autocast_dtype=dt, sync=False)
+            e1.record()
+            torch.cuda.synchronize()
+            ms = e0.elapsed_time(e1) / steps
+            out[tag] = {'value': batch / (ms / 1e3), 'unit': 'img/s', 'ms_per_step': ms, 'loss': float(loss)}
+            del tr
+            torch.cuda.empty_cache()
+        except Exception as e:                                   # noqa: BLE001 - a comparator must not sink the bench line
+            out[tag] = {'error': f'{type(e).__name__}: {e}'[:200]}
+    return out
 
 
 def run_reference(args):
@@ -144,6 +188,56 @@ def loss_metric_leg(msx, _lib, dev, pk, n=256, h=352, reps=5):
     return out
 
 
+class Workload:
+    """One rank's training step of a BASELINE config: model + loss + fused optimizer + EMA on static input buffers."""
+
+    def __init__(self, msx, name, batch, size, bf16, dev, world, rank, kd=None):
+        import torch
+        from medical_segmentation_pytorch_b200.flat import FlatBuffers, FlatParams
+        from medical_segmentation_pytorch_b200.synth import synth_batch
+        self.torch, self.msx, self.name, self.B, self.S, self.bf16, self.world = torch, msx, name, batch, size, bf16, world
+        arch, base, self.gflop_img, self.gb_img = MODELS[name]
+
+        class Cfg:
+            num_class, ignore_index, class_weights, loss_type, reduction = 2, 255, None, 'ce', 'mean'
+            kd_loss_type, kd_temperature = 'kl_div', 4.0               # configs/base_config.py:102-104
+        self.cfg = Cfg
+        torch.manual_seed(1)                                           # configs/base_config.py:75 random_seed = 1
+        self.model = (msx.DuckNet if arch == 'ducknet' else msx.UNet)(num_class=2, n_channel=3, base_channel=base).to(dev)
+        self.model.train()
+        FlatParams(self.model)
+        FlatBuffers(self.model)
+        self.net = msx.DistributedDataParallelB200(self.model) if world > 1 else self.model
+        self.opt = msx.FusedOptimizer(self.net, 'adam', lr=0.1 * 0.01 * world)   # utils/optimizer.py:15 with my_config.py:23
+        self.ema = msx.ModelEma(self.net)
+        self.loss_fn = msx.get_loss_fn(Cfg, dev)
+        self.teacher = msx.SmpUnet(kd, None, 3, 2).to(dev).eval() if kd else None     # random-init (no checkpoints offline)
+        xh, th = synth_batch(batch, size, size, seed=1 + rank)
+        self.xh, self.th = xh.pin_memory(), th.pin_memory()
+        self.sx, self.st = self.xh.to(dev), self.th.to(dev)             # static input buffers (graph replays read these)
+        self.it = 0
+
+    def step(self):
+        torch, msx = self.torch, self.msx
+        self.opt.zero_grad()
+        with torch.autocast('cuda', dtype=torch.bfloat16, enabled=self.bf16):
+            preds = self.net(self.sx)
+            loss = self.loss_fn(preds, self.st)
+            if self.teacher is not None:                                 # core/seg_trainer.py:69-75
+                with torch.no_grad():
+                    tp = self.teacher(self.sx)
+                loss = loss + 1.0 * msx.kd_loss_fn(self.cfg, preds, tp.detach())
+        loss.backward()
+        self.opt.step()
+        self.it += 1
+        self.ema.update(self.model, self.it)
+        return loss
+
+    def fractions(self, value_per_gpu, pk):
+        return {'tensor_frac': value_per_gpu * self.gflop_img / 1e3 / pk['tf'],
+                'hbm_frac': value_per_gpu * self.gb_img * (1 if self.bf16 else 2) / pk['hbm_gbs']}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
@@ -155,6 +249,8 @@ def main():
     ap.add_argument('--size', type=int, default=352)
     ap.add_argument('--dtype', default='bf16', choices=['bf16', 'fp32'])
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-extras', action='store_true', help='skip the legs that only add context to the line: GPU eager (cuDNN) comparator, '
+                    'eager (no-graph) value, other BASELINE configs, loss/metric GB/s')
     ap.add_argument('--profile-steps', type=int, default=2)
     ap.add_argument('--ncu', action='store_true', help='short eager run for an ncu launch list: 1 warm-up + 1 step, no graph / e2e / profile pass')
     ap.add_argument('--kd', default=None, metavar='ENCODER', help="BASELINE config 5: add a frozen smp.Unet(<ENCODER>, e.g. resnet101) teacher forward "
@@ -164,7 +260,7 @@ def main():
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'b200' else args.warmup
     if args.ncu:
-        args.warmup, args.steps, args.no_graph, args.profile_steps, args.no_cpu_baseline = 1, 1, True, 0, True
+        args.warmup, args.steps, args.no_graph, args.profile_steps, args.no_cpu_baseline, args.no_extras = 1, 1, True, 0, True, True
     if args.impl == 'reference':
         return run_reference(args)
 
@@ -174,8 +270,6 @@ def main():
     from medical_segmentation_pytorch_b200 import _lib, ops as msx_ops
     msx_ops.set_branch_streams(not args.no_branch_streams)
     msx_ops.set_wgrad_stream(not args.no_branch_streams)
-    from medical_segmentation_pytorch_b200.flat import FlatBuffers, FlatParams
-    from medical_segmentation_pytorch_b200.synth import synth_batch
 
     rank, world = int(os.environ.get('RANK', 0)), int(os.environ.get('WORLD_SIZE', 1))
     local = int(os.environ.get('LOCAL_RANK', 0))
@@ -183,43 +277,9 @@ def main():
     dev = torch.device('cuda', local)
     if world > 1:
         dist.init_process_group('nccl', device_id=dev)
-    arch, base, gflop_img, gb_img = MODELS[args.model]
     B, S = args.batch, args.size
     bf16 = args.dtype == 'bf16'
-
-    class Cfg:
-        num_class, ignore_index, class_weights, loss_type, reduction = 2, 255, None, 'ce', 'mean'
-        kd_loss_type, kd_temperature = 'kl_div', 4.0               # configs/base_config.py:102-104
-
-    torch.manual_seed(1)                                           # configs/base_config.py:75 random_seed = 1
-    model = (msx.DuckNet if arch == 'ducknet' else msx.UNet)(num_class=2, n_channel=3, base_channel=base).to(dev)
-    model.train()
-    FlatParams(model)
-    FlatBuffers(model)
-    net = msx.DistributedDataParallelB200(model) if world > 1 else model
-    opt = msx.FusedOptimizer(model, 'adam', lr=0.1 * 0.01 * world)  # utils/optimizer.py:15 with my_config.py:23
-    ema = msx.ModelEma(model)
-    loss_fn = msx.get_loss_fn(Cfg, dev)
-    teacher = msx.SmpUnet(args.kd, None, 3, 2).to(dev).eval() if args.kd else None     # random-init (no checkpoints offline)
-    xh, th = synth_batch(B, S, S, seed=1 + rank)
-    xh, th = xh.pin_memory(), th.pin_memory()
-    xd, td = xh.to(dev), th.to(dev)
-    it = [0]
-
-    def step(x, t):
-        opt.zero_grad()
-        with torch.autocast('cuda', dtype=torch.bfloat16, enabled=bf16):
-            preds = net(x)
-            loss = loss_fn(preds, t)
-            if teacher is not None:                                 # core/seg_trainer.py:69-75
-                with torch.no_grad():
-                    tp = teacher(x)
-                loss = loss + 1.0 * msx.kd_loss_fn(Cfg, preds, tp.detach())
-        loss.backward()
-        opt.step()
-        it[0] += 1
-        ema.update(model, it[0])
-        return loss
+    extras = not args.no_extras and world == 1
 
     def barrier():
         if world > 1:
@@ -239,63 +299,66 @@ def main():
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms)
 
-    # static input buffers: the timed step either launches its ~3.5 k kernels from Python or replays them
-    # as ONE CUDA graph captured after an eager warm-up (F1 of SURVEY §8f: kills the launch overhead)
-    sx, st_ = xd.clone(), td.clone()
-    for _ in range(args.warmup):
-        # .detach(): a live eager loss keeps its autograd graph - and the parameters' AccumulateGrad nodes, which
-        # remember the (default) stream they were created on - alive; the captured backward would then wait on
-        # that uncaptured stream (cudaErrorStreamCaptureIsolation)
-        loss = step(sx, st_).detach()
-    torch.cuda.synchronize()
-    assert torch.isfinite(loss).item(), 'non-finite loss in warm-up'
-    graph, graph_err, launches_per_step = None, None, None
-    if not args.no_graph:
-        try:
-            l0 = _lib.lib.msx_launch_count()
-            graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph):
-                gloss = step(sx, st_)
-            launches_per_step = _lib.lib.msx_launch_count() - l0
-            graph.replay()
-            torch.cuda.synchronize()
-            assert torch.isfinite(gloss).item(), 'non-finite loss from the graph replay'
-        except Exception as e:                                   # noqa: BLE001 - report and fall back to eager launches
-            graph, graph_err = None, f'{type(e).__name__}: {e}'[:300]
-            if os.environ.get('MSX_BENCH_DEBUG'):
-                import traceback
-                traceback.print_exc()
-            torch.cuda.synchronize()
-    if world > 1:                                              # every rank must take the same path
-        flag = torch.tensor([1 if graph is not None else 0], device=dev)
-        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-        if int(flag) == 0:
-            graph = None
+    def capture(wl, warmup):
+        """Eager warm-up, then the whole step as ONE CUDA graph through the package's public helper (msx.capture_step:
+        what a user of the reference's trainer calls to get this number).  Returns (replay | None, error, launches/step)."""
+        for _ in range(warmup):
+            loss = wl.step().detach()
+        torch.cuda.synchronize()
+        assert torch.isfinite(loss).item(), 'non-finite loss in warm-up'
+        replay, err, per_step = None, None, None
+        if not args.no_graph:
+            try:
+                l0 = _lib.lib.msx_launch_count()
+                replay = msx.capture_step(wl.step, warmup=1, optimizers=[wl.opt])
+                per_step = (_lib.lib.msx_launch_count() - l0) // 2           # one eager warm-up + the captured pass
+                replay()
+                torch.cuda.synchronize()
+                assert torch.isfinite(replay.out).item(), 'non-finite loss from the graph replay'
+            except Exception as e:                                   # noqa: BLE001 - report and fall back to eager launches
+                replay, err = None, f'{type(e).__name__}: {e}'[:300]
+                if os.environ.get('MSX_BENCH_DEBUG'):
+                    import traceback
+                    traceback.print_exc()
+                torch.cuda.synchronize()
+        if world > 1:                                              # every rank must take the same path
+            flag = torch.tensor([1 if replay is not None else 0], device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            if int(flag) == 0:
+                replay = None
+        return replay, err, per_step
+
+    wl = Workload(msx, args.model, B, S, bf16, dev, world, rank, args.kd)
+    replay, graph_err, launches_per_step = capture(wl, args.warmup)
 
     def run_step():
-        if graph is not None:
-            graph.replay()
-            return gloss
-        return step(sx, st_)
+        return replay() if replay is not None else wl.step()
 
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     l0 = _lib.lib.msx_launch_count()
     ms = timed(run_step, args.steps)
-    launches = (_lib.lib.msx_launch_count() - l0) if graph is None else launches_per_step * args.steps
+    launches = (_lib.lib.msx_launch_count() - l0) if replay is None else launches_per_step * args.steps
     clocks = sampler.stop() if rank == 0 else None
 
     # end to end: pinned host buffers -> device every step, loss read back every step
     def e2e_step():
-        sx.copy_(xh, non_blocking=True)
-        st_.copy_(th, non_blocking=True)
+        wl.sx.copy_(wl.xh, non_blocking=True)
+        wl.st.copy_(wl.th, non_blocking=True)
         return float(run_step().detach())
     if args.ncu:
         ms_e2e = ms
     else:
         e2e_step()
         ms_e2e = timed(e2e_step, args.steps)
+
+    # the same step WITHOUT the graph: what the reference's own Python loop gets when it drives these modules directly
+    eager_value = None
+    if extras and replay is not None:
+        k = min(args.steps, 5)
+        wl.step().detach()
+        eager_value = B * world * k / (timed(lambda: wl.step().detach(), k) / 1e3)
 
     # profiled pass: per-launch CUDA events on the launching stream, algorithmic bytes/flops per launch
     prof = {}
@@ -305,7 +368,7 @@ def main():
         if rank == 0:
             _lib.lib.msx_profile_enable(1)
         for _ in range(args.profile_steps):
-            step(sx, st_).detach()
+            wl.step().detach()
         if rank == 0:
             prof = _lib.profile_collect()
             _lib.lib.msx_profile_enable(0)
@@ -342,37 +405,69 @@ def main():
         else:
             ach = tv['bytes'] / tv['ms'] / 1e6
             roofline = {'kernel': top, 'bound': 'hbm', 'achieved': ach, 'peak': pk['hbm_gbs'], 'unit': 'GB/s', 'frac': ach / pk['hbm_gbs']}
-        traffic, traffic_note = None, None
+        traffic, traffic_note, traffic_source = None, None, None
         try:
             tr = json.load(open(os.path.join(ROOT, 'profiles', 'ncu_traffic.json'))).get(top)
             if tr and args.model == 'ducknet17' and not args.kd:      # the capture is of the headline workload's top kernel
-                traffic, traffic_note = tr['traffic_bytes'], f"{tr['kernel']} {tr['shape']}: algorithmic {tr['algorithmic_bytes']} B; {tr['source']}"
+                traffic = tr['traffic_bytes']
+                traffic_note = f"{tr['kernel']} {tr['shape']}: algorithmic (unpadded channels) {tr['algorithmic_bytes']} B per launch"
+                traffic_source = f"committed ncu --set full capture ({tr['source']}), NOT measured in this run"
         except Exception:
             pass
-        roofline.update({'traffic': traffic, 'traffic_note': traffic_note, 'peak_source': pk['src'] + (' (sustained bf16)' if roofline['bound'] == 'tensor' else ''),
+        roofline.update({'traffic': traffic, 'traffic_note': traffic_note, 'traffic_source': traffic_source,
+                         'peak_source': pk['src'] + (' (sustained bf16)' if roofline['bound'] == 'tensor' else ''),
                          'avg_launch_us': tv['ms'] / tv['launches'] * 1e3, 'launches_per_step': tv['launches'] // args.profile_steps,
                          'share_of_step': tv['ms'] / tot_ms,
                          'how': f'{args.profile_steps} extra step(s) after the timed region with per-launch CUDA events (msx_profile_*)'})
-    loss_metric = loss_metric_leg(msx, _lib, dev, pk) if world == 1 and not args.ncu else None
+    loss_metric = loss_metric_leg(msx, _lib, dev, pk) if extras else None
+    workload_name = wl.name
+    model_roofline = {'train_gflop_per_img': wl.gflop_img, 'conv_act_gb_per_img_bf16': wl.gb_img, **wl.fractions(value / world, pk)}
+
+    # the other single-GPU BASELINE configs, briefly (bounded: 3 warm-up + 5 graph replays each), for the driver's record
+    other = None
+    if extras and args.model == 'ducknet17' and not args.kd and bf16 and replay is not None:
+        del replay, wl
+        torch.cuda.empty_cache()
+        other = {}
+        for name, ob, okd in (('unet32', 16, None), ('ducknet34', 32, None), ('unet32', 16, 'resnet101')):
+            key = name + (f'+kd_{okd}' if okd else '')
+            try:
+                w2 = Workload(msx, name, ob, S, True, dev, 1, 0, okd)
+                r2, err2, _ = capture(w2, 3)
+                if r2 is None:
+                    other[key] = {'error': err2 or 'graph capture disabled'}
+                else:
+                    ms2 = timed(r2, 5)
+                    v2 = ob * 5 / (ms2 / 1e3)
+                    other[key] = {'value': v2, 'unit': 'img/s', 'ms_per_step': ms2 / 5, 'batch': ob, 'size': S, 'dtype': 'bf16', **w2.fractions(v2, pk)}
+                    if okd:
+                        other[key].pop('tensor_frac'), other[key].pop('hbm_frac')      # student-only flop/byte model does not cover the teacher
+                del r2, w2
+            except Exception as e:                               # noqa: BLE001
+                other[key] = {'error': f'{type(e).__name__}: {e}'[:200]}
+            torch.cuda.empty_cache()
+    gpu_eager = gpu_eager_leg(workload_name, B, S, dev) if extras and not args.kd else None
     cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
-        cpu_baseline, _ = cpu_reference_leg(args.model, 2, 1, batch=2, hw=S)
+        cpu_baseline, _ = cpu_reference_leg(workload_name, 2, 1, batch=2, hw=S)
+    graph_on = launches_per_step is not None and graph_err is None and not args.no_graph
     line = {
         'metric': 'train_imgs_per_sec', 'value': value, 'unit': 'img/s', 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
         'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
         'dtype': 'bf16' if bf16 else 'f32', 'data': 'synthetic',
-        'config': {'workload': f'{args.model} training step (fwd+CE+' + (f'frozen smp.Unet({args.kd}) teacher fwd+KD(kl,T=4)+' if args.kd else '') + f'bwd+Adam+EMA copy), {S}x{S}, batch {B}/GPU, num_class 2, per-GPU BN',
+        'config': {'workload': f'{workload_name} training step (fwd+CE+' + (f'frozen smp.Unet({args.kd}) teacher fwd+KD(kl,T=4)+' if args.kd else '') + f'bwd+Adam+EMA copy), {S}x{S}, batch {B}/GPU, num_class 2, per-GPU BN',
                    'global_batch': B * world, 'parallelism': f'dp{world}', 'l2': 'per-step working set >> 126 MB L2 (no flush needed)',
                    'seed': 'weights manual_seed(1); data PCG64(1+rank)',
-                   'launch': 'one CUDA graph replay per step' if graph is not None else 'eager Python launches' + (f' (graph capture failed: {graph_err})' if graph_err else '')},
+                   'launch': 'one CUDA graph replay per step (msx.capture_step)' if graph_on else 'eager Python launches' + (f' (graph capture failed: {graph_err})' if graph_err else '')},
         'clocks': clocks,
-        'e2e': {'value': imgs / (ms_e2e / 1e3), 'unit': 'img/s', 'h2d_bytes_per_step': xh.numel() * 4 + th.numel() * 8, 'd2h_bytes_per_step': 4},
+        'e2e': {'value': imgs / (ms_e2e / 1e3), 'unit': 'img/s', 'h2d_bytes_per_step': B * 3 * S * S * 4 + B * S * S * 8, 'd2h_bytes_per_step': 4},
         'gpu_launches': int(launches),
+        'eager_value': eager_value,
         'roofline': roofline,
         'cpu_baseline': cpu_baseline,
-        'model_roofline': {'train_gflop_per_img': gflop_img, 'conv_act_gb_per_img_bf16': gb_img,
-                           'tensor_frac': value / world * gflop_img / 1e3 / pk['tf'],
-                           'hbm_frac': value / world * gb_img * (1 if bf16 else 2) / pk['hbm_gbs']},
+        'gpu_eager_baseline': gpu_eager,
+        'model_roofline': model_roofline,
+        'other_configs': other,
         'kernels': kernels,
         'loss_metric_gbs': loss_metric,
     }

@@ -45,6 +45,9 @@ enum { MSX_F32 = 0, MSX_BF16 = 1 };
 enum { MSX_ENGINE_AUTO = 0, MSX_ENGINE_SIMT = 1, MSX_ENGINE_TCGEN05 = 2 };
 enum { MSX_PACK_FPROP = 0, MSX_PACK_DGRAD = 1 };
 enum { MSX_REDUCE_MEAN = 0, MSX_REDUCE_SUM = 1, MSX_REDUCE_NONE = 2 };
+/* `relu` argument of the BatchNorm BACKWARD entry points is a bit set: bit 0 = a ReLU followed the BN; bit 1 = the
+ * forward ran in eval mode (running statistics are constants: dx = gamma * invstd * g, no batch-statistics terms). */
+enum { MSX_BN_RELU = 1, MSX_BN_EVAL = 2 };
 
 const char* msx_last_error(void);
 int msx_version(void);
@@ -132,8 +135,9 @@ int msx_conv_bn_act_fwd(const msx_conv_desc* d, const void* x, const float* w_ma
                         float* save_mean, float* save_invstd,
                         void* ws, size_t ws_bytes, void* stream);
 
-/* Backward of the above (training mode): from dz produces dx (nullable), dw, dbias (nullable),
- * dgamma, dbeta.  dy_scratch: same shape/stride as y_raw.  The ReLU mask is recomputed from y_raw. */
+/* Backward of the above: from dz produces dx (nullable), dw, dbias (nullable), dgamma, dbeta.
+ * dy_scratch: same shape/stride as y_raw.  The ReLU mask is recomputed from y_raw.  `relu` is a MSX_BN_* bit set
+ * (MSX_BN_EVAL when the forward used running statistics - frozen-BN fine-tuning, input saliency). */
 int msx_conv_bn_act_bwd(const msx_conv_desc* d, const void* x, const float* w_master,
                         const void* y_raw, const void* dz, int32_t lddz,
                         const float* gamma, const float* beta,
@@ -156,7 +160,7 @@ int msx_sum_bn_act_fwd(int dtype, int n_in, const void* const* host_xs, const in
                        float eps, float momentum, int training, int relu,
                        void* z, int32_t ldz, float* save_mean, float* save_invstd,
                        void* ws, size_t ws_bytes, void* stream);
-/* ds = d(loss)/d(s) given dz; also dgamma, dbeta. */
+/* ds = d(loss)/d(s) given dz; also dgamma, dbeta.  `relu`: MSX_BN_* bit set. */
 int msx_bn_act_bwd(int dtype, const void* s, int32_t lds, const void* dz, int32_t lddz,
                    int64_t pixels, int32_t channels,
                    const float* gamma, const float* beta, const float* save_mean, const float* save_invstd,
@@ -173,8 +177,10 @@ int msx_sum_n(int dtype, int n_in, const void* const* host_xs, const int32_t* ho
  *   - channels must be <= MSX_BN_STATIC_MAX_CHANNELS, otherwise MSX_ERR_UNSUPPORTED is returned;
  *   - each GPU that loads libmsx.so holds about 2.4 MB for it until the process exits;
  *   - the device the buffers live on must be the current device;
- *   - the first call on each device looks the scratch address up (no allocation); make that first call
- *     before starting any stream capture;
+ *   - the first call on each device looks the scratch address up.  That call allocates nothing itself, but under
+ *     CUDA's default lazy module loading it may be the moment the driver loads this library's device image and
+ *     reserves the array's 2.4 MB - so make that first call at start-up, before any stream capture;
+ *   - the address is cached per device for the life of the process: calls after cudaDeviceReset are unsupported;
  *   - every call uses the same scratch: two calls that can run at the same time on one GPU (different
  *     streams, or different host threads on different streams) race on it - keep them on one stream or
  *     order them yourself.  Nothing has to be cleared between calls.
@@ -267,13 +273,23 @@ int msx_confmat_update(const float* logits, const int64_t* labels, int32_t n, in
 /* Multi-tensor optimizer / EMA steps over one flat fp32 parameter arena
  * (utils/optimizer.py:8-16 -> torch.optim.Adam/AdamW/SGD; utils/model_ema.py:29-40).
  * grad_scale multiplies the gradient first (1/world_size after the DDP all-reduce).
- * step_dev: device int64 step counter, incremented by the Adam kernel. */
+ * step_dev: device int64 step counter, incremented by the Adam kernel.
+ * hyper_dev (nullable): device float[4] = {lr, beta1 | momentum, beta2, weight_decay} that OVERRIDES the scalar
+ * arguments.  The reference steps OneCycleLR every iteration (utils/scheduler.py:12-19, core/seg_trainer.py:85),
+ * which also cycles momentum / beta1; scalars baked into a captured CUDA graph could not follow it, a device
+ * array refreshed by one small copy per step can. */
 int msx_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t count,
                   float lr, float beta1, float beta2, float eps, float weight_decay, int decoupled_wd,
-                  float grad_scale, int64_t* step_dev, void* stream);
+                  float grad_scale, int64_t* step_dev, const float* hyper_dev, void* stream);
 int msx_sgd_step(float* param, const float* grad, float* momentum_buf, int64_t count,
-                 float lr, float momentum, float weight_decay, float grad_scale, int first_step, void* stream);
-int msx_ema_update(float* ema, const float* model, int64_t count, float decay, void* stream);
+                 float lr, float momentum, float weight_decay, float grad_scale, int first_step,
+                 const float* hyper_dev, void* stream);
+/* ModelEmaV2.update (utils/model_ema.py:29-40): e = decay * e + (1 - decay) * m as two rounded products and one
+ * rounded sum in fp32 (what the reference's three torch kernels compute; no fused multiply-add), or a plain copy when
+ * decay == 0.  The _i64 form is the same rule applied to the int64 num_batches_tracked counters, which the reference
+ * also runs through the float expression and truncates back to int64 with copy_ (utils/model_ema.py:31-35). */
+int msx_ema_update(float* ema, const float* model, int64_t count, double decay, void* stream);
+int msx_ema_update_i64(int64_t* ema, const int64_t* model, int64_t count, double decay, void* stream);
 
 #ifdef __cplusplus
 }

@@ -8,7 +8,8 @@ from ._lib import MsxError, lib  # noqa: F401  (fails loudly when libmsx.so is a
 from .ducknet import DuckNet
 from .loss import CrossEntropyLoss, DiceBCELoss, OhemCELoss, get_loss_fn, kd_loss_fn
 from .metrics import Dice, JaccardIndex, get_seg_metrics
-from .optim import FusedOptimizer, ModelEma, get_ema_model, get_optimizer
+from .graph import CapturedStep, capture_step
+from .optim import FusedOptimizer, ModelEma, get_ema_model, get_optimizer, get_scheduler
 from .parallel import (DistributedDataParallelB200, de_parallel, destroy_ddp_process, is_parallel, parallel_model,
                        sampler_set_epoch, set_device)
 from .teacher import SmpUnet
@@ -49,5 +50,5 @@ def get_teacher_model(config, device):
 
 __all__ = ['UNet', 'DuckNet', 'SmpUnet', 'get_model', 'get_teacher_model', 'get_loss_fn', 'kd_loss_fn', 'get_seg_metrics', 'parallel_model',
            'de_parallel', 'is_parallel', 'set_device', 'destroy_ddp_process', 'sampler_set_epoch', 'get_optimizer',
-           'get_ema_model', 'FusedOptimizer', 'ModelEma', 'CrossEntropyLoss', 'OhemCELoss', 'DiceBCELoss',
+           'get_ema_model', 'get_scheduler', 'capture_step', 'CapturedStep', 'FusedOptimizer', 'ModelEma', 'CrossEntropyLoss', 'OhemCELoss', 'DiceBCELoss',
            'JaccardIndex', 'Dice', 'DistributedDataParallelB200', 'MsxError']

@@ -15,6 +15,7 @@ F32, BF16 = 0, 1
 PACK_FPROP, PACK_DGRAD = 0, 1
 ENGINE_AUTO, ENGINE_SIMT, ENGINE_TCGEN05 = 0, 1, 2
 REDUCE = {'mean': 0, 'sum': 1, 'none': 2}
+BN_RELU, BN_EVAL = 1, 2
 
 
 class ConvDesc(C.Structure):
@@ -86,9 +87,10 @@ def _load():
         'msx_dice_bce_loss_fwd_bwd': (C.c_int, [p, p, C.c_int, i64, f32, p, p, p, sz, p]),
         'msx_scale_by_device_scalar': (C.c_int, [p, i64, p, p]),
         'msx_confmat_update': (C.c_int, [p, p, i32, i32, i64, i64, p, p, p]),
-        'msx_adam_step': (C.c_int, [p, p, p, p, i64, f32, f32, f32, f32, f32, C.c_int, f32, p, p]),
-        'msx_sgd_step': (C.c_int, [p, p, p, i64, f32, f32, f32, f32, C.c_int, p]),
-        'msx_ema_update': (C.c_int, [p, p, i64, f32, p]),
+        'msx_adam_step': (C.c_int, [p, p, p, p, i64, f32, f32, f32, f32, f32, C.c_int, f32, p, p, p]),
+        'msx_sgd_step': (C.c_int, [p, p, p, i64, f32, f32, f32, f32, C.c_int, p, p]),
+        'msx_ema_update': (C.c_int, [p, p, i64, C.c_double, p]),
+        'msx_ema_update_i64': (C.c_int, [p, p, i64, C.c_double, p]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)          # AttributeError here == header/library mismatch

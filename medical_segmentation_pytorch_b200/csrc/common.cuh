@@ -173,7 +173,7 @@ int bn_apply_launch(int dtype, const void* x, int ldx, void* z, int ldz, int64_t
                     const float* mean, const float* invstd, const float* gamma, const float* beta, int relu,
                     cudaStream_t st);
 int bn_bwd_launch(int dtype, const void* x, int ldx, const void* dz, int lddz, int64_t pixels, int channels,
-                  const float* gamma, const float* beta, const float* mean, const float* invstd, int relu,
+                  const float* gamma, const float* beta, const float* mean, const float* invstd, int flags /* MSX_BN_* */,
                   void* dx, int lddx, float* dgamma, float* dbeta, void* ws, size_t ws_bytes, cudaStream_t st);
 int channel_sum_launch(int dtype, const void* x, int ld, int64_t pixels, int channels, float* out,
                        void* ws, size_t ws_bytes, cudaStream_t st);

@@ -20,6 +20,11 @@
 //   Scheduling    persistent: grid = min(#tiles, 148), static round-robin over (pixel tile, n tile).
 #include <cuda.h>
 #include <stdlib.h>
+#include <string.h>
+
+#include <mutex>
+#include <set>
+#include <utility>
 
 #include "common.cuh"
 
@@ -359,8 +364,16 @@ struct HaloParams {
     uint32_t a_bytes, a_stage, b_tap_bytes;
     int issuers;                   // 1 or 2 MMA-issuing warps
     int tw, boxes_x, total_boxes;  // tw == 2 (pair mode): one TMA box covers two tiles side by side; issuer / epilogue group j takes tile j
+#ifdef MSX_ABLATION
     int dbg;                       // MSX_DBG_HALO ablations (results are wrong): 1 no stores, 2 no MMAs, 4 no TMA loads, 8 no tcgen05.ld
+#endif
 };
+// Ablation switches exist only in -DMSX_ABLATION builds (tools/microbench.py measurements); the shipped kernel has none.
+#ifdef MSX_ABLATION
+#define MSX_DBG(p, bit) ((p).dbg & (bit))
+#else
+#define MSX_DBG(p, bit) 0
+#endif
 
 // Start address shifted by whole 128 B pixel rows, base_offset field left 0: measured on B200, the
 // 128B swizzle is applied to the absolute shared-memory address bits, so a window that starts at any
@@ -416,7 +429,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 const int ty = rem / units_x;
                 const int y0 = ty * 16, x0 = (rem - ty * units_x) * unit_w;
                 mbar_wait(bar_empty + 8 * stage, phase ^ 1);
-                if (p.dbg & 4) mbar_arrive(bar_full + 8 * stage);
+                if (MSX_DBG(p, 4)) mbar_arrive(bar_full + 8 * stage);
                 else {
                     mbar_expect_tx(bar_full + 8 * stage, p.a_bytes);
                     tma_load_4d(sA + stage * p.a_stage, &tmA, bar_full + 8 * stage, 0, x0 + p.ox_min, y0 + p.oy_min, img);
@@ -457,7 +470,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 tc_fence_after();
                 const uint32_t tmem_d = tmem_base + as * BN;
                 const uint32_t a_lo = a_lo0 + stage * a_stage16;
-                if (!(p.dbg & 2)) {
+                if (!MSX_DBG(p, 2)) {
 #pragma unroll
                 for (int tap = 0; tap < TAPS; ++tap) {
 #pragma unroll
@@ -467,7 +480,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     }
                 }
                 }
-                if (p.dbg & 16) { mbar_arrive(bar_empty + 8 * stage); mbar_arrive(bar_tfull + 8 * as); }
+                if (MSX_DBG(p, 16)) { mbar_arrive(bar_empty + 8 * stage); mbar_arrive(bar_tfull + 8 * as); }
                 else {
                     umma_commit(bar_empty + 8 * stage);
                     umma_commit(bar_tfull + 8 * as);
@@ -491,7 +504,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const int img = t / tiles_per_img, rem = t - img * tiles_per_img;
             const int ty = rem / units_x;
             const int y = ty * 16 + dy, x = (rem - ty * units_x) * unit_w + (pair ? grp * 8 : 0) + dx;
-            const bool valid = y < p.H && x < p.W && !(p.dbg & 1);
+            const bool valid = y < p.H && x < p.W && !MSX_DBG(p, 1);
             bf16* out = dst + ((int64_t)(img * p.H + y) * p.W + x) * p.ldd;
             const int as = it % p.nacc;
             const uint32_t taddr = tlane + as * p.BN;
@@ -500,7 +513,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             int c0 = 0;
             for (; c0 + 32 <= ncols || (c0 < ncols && ncols - c0 > 16); c0 += 32) {
                 uint32_t v[32];
-                if (!(p.dbg & 8)) {
+                if (!MSX_DBG(p, 8)) {
                     tmem_ld32(taddr + c0, v);
                     tmem_ld_wait();
                 }
@@ -542,6 +555,20 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 }
 
 // ---- host side ----------------------------------------------------------------------------------
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-device (per-context) setting: opt in once per (device, kernel).
+// Called from the caller's thread and from the autograd worker thread, hence the lock.
+int ensure_big_smem(const void* kernel) {
+    static std::mutex mu;
+    static std::set<std::pair<int, const void*>> done;
+    int dev = 0;
+    MSX_CHECK_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(mu);
+    if (done.count({dev, kernel})) return MSX_OK;
+    MSX_CHECK_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    done.insert({dev, kernel});
+    return MSX_OK;
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -557,14 +584,37 @@ EncodeTiledFn encode_fn() {
     return fn;
 }
 
+// Encoded tensor maps are pure functions of (pointer, geometry): the eager (non-graph) path re-encounters the same few
+// hundred of them every step (the caching allocator hands the same blocks back), so they are kept in a small
+// direct-mapped per-thread cache instead of calling the driver's encoder twice per convolution.
+struct MapKey {
+    const void* ptr;
+    cuuint64_t dims[4], strides[3];
+    cuuint32_t box[4];
+    int rank, sw;
+};
+struct MapSlot { MapKey key; CUtensorMap map; bool used; };
+constexpr int kMapSlots = 2048;
+
 int make_map(CUtensorMap* m, int rank, const void* ptr, const cuuint64_t* dims, const cuuint64_t* strides_bytes,
              const cuuint32_t* box, CUtensorMapSwizzle sw) {
     EncodeTiledFn fn = encode_fn();
     if (!fn) return set_error(MSX_ERR_CUDA, "cuTensorMapEncodeTiled entry point unavailable");
+    static thread_local MapSlot* cache = static_cast<MapSlot*>(calloc(kMapSlots, sizeof(MapSlot)));
+    MapKey key;
+    memset(&key, 0, sizeof(key));
+    key.ptr = ptr; key.rank = rank; key.sw = (int)sw;
+    for (int i = 0; i < rank; ++i) { key.dims[i] = dims[i]; key.box[i] = box[i]; }
+    for (int i = 0; i + 1 < rank; ++i) key.strides[i] = strides_bytes[i];
+    uint64_t h = 1469598103934665603ull;
+    for (size_t i = 0; i < sizeof(key) / 8; ++i) { h ^= reinterpret_cast<const uint64_t*>(&key)[i]; h *= 1099511628211ull; }
+    MapSlot* slot = cache ? &cache[(h ^ (h >> 29)) % kMapSlots] : nullptr;
+    if (slot && slot->used && memcmp(&slot->key, &key, sizeof(key)) == 0) { *m = slot->map; return MSX_OK; }
     cuuint32_t es[5] = {1, 1, 1, 1, 1};
     CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(ptr), dims, strides_bytes, box, es,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return set_error(MSX_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+    if (slot) { slot->key = key; slot->map = *m; slot->used = true; }
     return MSX_OK;
 }
 
@@ -1018,11 +1068,7 @@ int conv_wgrad_tc(const msx_conv_desc* d, const void* x, const void* dy, float* 
         MSX_TRY(make_map(&tmS, 4, small, dims, strides, box, p.chunkA == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B));
     }
     MSX_TRY(make_src_maps(tmG, big, p.Bp, p.N, Hb, Wb, ldb, d->stride, p.chunkB, p.halo ? p.Wh : p.tw, p.halo ? p.Hh : p.th, mask));
-    static bool attr_set = false;
-    if (!attr_set) {
-        MSX_CHECK_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        attr_set = true;
-    }
+    MSX_TRY(ensure_big_smem(reinterpret_cast<const void*>(wgrad_tc_kernel)));
     const size_t smem = 1024 + (size_t)p.SA * p.a_stage + (size_t)p.stagesB * p.b_stage + 64 + 16 * kMaxStages + 64;
     const int grid = p.a_tiles * p.b_tiles * p.tap_groups * p.splits;
     const int taps = p.kh * p.kw;
@@ -1065,7 +1111,9 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     const uint32_t bres = ((uint32_t)taps * p.b_tap_bytes + 1023u) & ~1023u;
     p.nacc = 512 / p.BN < kMaxAcc ? 512 / p.BN : kMaxAcc;
     if (p.nacc % 2) --p.nacc;                                     // two epilogue groups alternate tiles
-    { const char* e = getenv("MSX_DBG_HALO"); p.dbg = e ? atoi(e) : 0; }
+#ifdef MSX_ABLATION
+    { static const int dbg = [] { const char* e = getenv("MSX_DBG_HALO"); return e ? atoi(e) : 0; }(); p.dbg = dbg; }
+#endif
     static const int iss = [] { const char* e = getenv("MSX_HALO_ISSUERS"); return e && atoi(e) == 1 ? 1 : 2; }();
     static const int want_pair = [] { const char* e = getenv("MSX_HALO_PAIR"); return e ? atoi(e) : 0; }();
     p.issuers = p.nacc >= 2 ? iss : 1;
@@ -1086,8 +1134,14 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
         p.tw = 1;                                                 // the wide box does not leave room for two stages
     }
     if (p.stages < 2) return MSX_OK;
-    { const char* e = getenv("MSX_DBG_STAGES"); if (e && atoi(e) >= 2 && atoi(e) < p.stages) p.stages = atoi(e); }
-    { const char* e = getenv("MSX_DBG_NACC"); if (e && atoi(e) >= 2 && atoi(e) < p.nacc) p.nacc = atoi(e) & ~1; }
+#ifdef MSX_ABLATION
+    {
+        static const int st = [] { const char* e = getenv("MSX_DBG_STAGES"); return e ? atoi(e) : 0; }();
+        static const int na = [] { const char* e = getenv("MSX_DBG_NACC"); return e ? atoi(e) : 0; }();
+        if (st >= 2 && st < p.stages) p.stages = st;
+        if (na >= 2 && na < p.nacc) p.nacc = na & ~1;
+    }
+#endif
     // Two issuers need an even stage (and accumulator) count: then every stage / accumulator belongs to ONE issuer and
     // its mbarrier phases advance only with that thread's own progress.  With an odd count a stage alternates between
     // the issuers, one of them can run two phases ahead of the other and a parity wait passes on the wrong phase
@@ -1122,15 +1176,7 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     MSX_HALO_CASE(1, 1) MSX_HALO_CASE(1, 2) MSX_HALO_CASE(1, 3) MSX_HALO_CASE(1, 4)
 #undef MSX_HALO_CASE
     if (!kern) return MSX_OK;                                     // other tap counts: streaming kernel
-    {
-        static HaloKernel seen[16] = {nullptr};                    // opt in to > 48 KB dynamic smem once per instantiation
-        int i = 0;
-        while (i < 16 && seen[i] && seen[i] != kern) ++i;
-        if (i < 16 && !seen[i]) {
-            MSX_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-            seen[i] = kern;
-        }
-    }
+    MSX_TRY(ensure_big_smem(reinterpret_cast<const void*>(kern)));     // > 48 KB dynamic smem: once per device and instantiation
     {
         ProfScope ps__(K_CONV_TC, st, M * (K + Nc) * 2.0, 2.0 * M * Nc * K * taps);
         kern<<<grid, kHaloThreads2, smem, st>>>(tmA, tmB, static_cast<bf16*>(dst), ep, p);
@@ -1237,11 +1283,7 @@ int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const
         cuuint32_t box[3] = {(cuuint32_t)p.chunk, (cuuint32_t)p.BN, 1};
         MSX_TRY(make_map(&tmB, 3, packed, dims, strides, box, sw));
     }
-    static bool attr_set = false;
-    if (!attr_set) {
-        MSX_CHECK_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-        attr_set = true;
-    }
+    MSX_TRY(ensure_big_smem(reinterpret_cast<const void*>(conv_tc_kernel)));
     const int nphase = (!f_form && d->stride == 2) ? 4 : 1;      // b-form stride 2: one launch per destination phase
     for (int ph = 0; ph < nphase; ++ph) {
         const int pa = ph >> 1, pb = ph & 1;

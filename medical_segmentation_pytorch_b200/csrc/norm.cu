@@ -308,7 +308,7 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const T* __restrict_
 
 __global__ void bn_bwd_finalize_kernel(const double* __restrict__ partials, int nblk, int cp, int channels, int64_t count,
                                        float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                       float* __restrict__ c1, float* __restrict__ c2) {
+                                       float* __restrict__ c1, float* __restrict__ c2, int eval_mode) {
     const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (c >= cp) return;
@@ -318,8 +318,9 @@ __global__ void bn_bwd_finalize_kernel(const double* __restrict__ partials, int 
     if (lane != 0) return;
     if (dbeta) dbeta[c] = (float)s;
     if (dgamma) dgamma[c] = (float)q;
-    c1[c] = (float)(s / (double)count);
-    c2[c] = (float)(q / (double)count);
+    // eval mode: mean / invstd are constants (running statistics), so dx = gamma * invstd * g without the batch terms
+    c1[c] = eval_mode ? 0.f : (float)(s / (double)count);
+    c2[c] = eval_mode ? 0.f : (float)(q / (double)count);
 }
 
 template <typename T>
@@ -668,8 +669,9 @@ int bn_apply_launch(int dtype, const void* x, int ldx, void* z, int ldz, int64_t
 }
 
 int bn_bwd_launch(int dtype, const void* x, int ldx, const void* dz, int lddz, int64_t pixels, int channels,
-                  const float* gamma, const float* beta, const float* mean, const float* invstd, int relu,
+                  const float* gamma, const float* beta, const float* mean, const float* invstd, int flags,
                   void* dx, int lddx, float* dgamma, float* dbeta, void* ws, size_t ws_bytes, cudaStream_t st) {
+    const int relu = flags & MSX_BN_RELU, eval_mode = (flags & MSX_BN_EVAL) ? 1 : 0;
     MSX_TRY(check_ld(ldx, channels, "bn_bwd x"));
     MSX_TRY(check_ld(lddz, channels, "bn_bwd dz"));
     MSX_TRY(check_ld(lddx, channels, "bn_bwd dx"));
@@ -683,7 +685,7 @@ int bn_bwd_launch(int dtype, const void* x, int ldx, const void* dz, int lddz, i
         const int g = reduce_grid(pixels, c.lanes);
         { ProfScope ps__(K_BN_BWD_REDUCE, st, 2.0 * (double)pixels * channels * (double)sizeof(T), 0); bn_bwd_reduce_kernel<T><<<dim3(g, c.nchunk), 256, 0, st>>>(static_cast<const T*>(x), ldx, static_cast<const T*>(dz), lddz,
                                                                  pixels, c.cp, c.vch, channels, mean, invstd, gamma, beta, relu, partials); }
-        { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_bwd_finalize_kernel<<<(cp * 32 + 127) / 128, 128, 0, st>>>(partials, g, cp, channels, pixels, dgamma, dbeta, c1, c2); }
+        { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_bwd_finalize_kernel<<<(cp * 32 + 127) / 128, 128, 0, st>>>(partials, g, cp, channels, pixels, dgamma, dbeta, c1, c2, eval_mode); }
         { ProfScope ps__(K_BN_BWD_APPLY, st, 3.0 * (double)pixels * channels * (double)sizeof(T), 0); bn_bwd_apply_kernel<T><<<dim3(stream_grid(pixels, c.lanes), c.nchunk), 256, 0, st>>>(
             static_cast<const T*>(x), ldx, static_cast<const T*>(dz), lddz, static_cast<T*>(dx), lddx, pixels, c.cp, c.vch, channels,
             mean, invstd, gamma, beta, c1, c2, relu); }

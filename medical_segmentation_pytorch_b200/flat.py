@@ -18,6 +18,10 @@ class FlatParams:
         params = [p for p in model.parameters() if p.requires_grad]
         if not params:
             raise ValueError('model has no trainable parameters')
+        if any(getattr(p, '_msx_grad', None) is not None for p in params):
+            # a second arena would re-point p.data / p.grad while DDP buckets and the optimizer still hold the first
+            raise RuntimeError('these parameters already live in a flat arena (model._msx_flat); pass the model itself, '
+                               'not a wrapper, or reuse model._msx_flat')
         dev, dt = params[0].device, params[0].dtype
         assert all(p.dtype == dt and p.device == dev for p in params)
         self.params = params

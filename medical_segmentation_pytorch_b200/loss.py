@@ -51,6 +51,10 @@ class _ScaledGradReq(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         grad, = ctx.saved_tensors
+        if getattr(ctx, 'scaled', False):
+            # the saved gradient was scaled in place by the first backward; a second pass would scale it twice
+            raise RuntimeError('backward through a fused loss a second time (retain_graph): call the loss again instead')
+        ctx.scaled = True
         g = g.to(torch.float32).contiguous()
         L.check(lib.msx_scale_by_device_scalar(L.ptr(grad), grad.numel(), L.ptr(g), L.stream()))
         return grad, None

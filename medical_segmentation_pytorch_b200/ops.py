@@ -195,7 +195,8 @@ class ConvBNActFn(torch.autograd.Function):
             C.byref(d), L.ptr(x), None if pre else L.ptr(weight), L.ptr(_f32(bias)), L.ptr(_f32(gamma)), L.ptr(_f32(beta)),
             L.ptr(rm), L.ptr(rv), L.ptr(nbt), eps, momentum, int(training), int(relu),
             L.ptr(pk), L.ptr(y), L.ptr(z), ld_of(z), L.ptr(mean), L.ptr(invstd), L.ptr(ws), ws.numel(), L.stream()))
-        ctx.g, ctx.relu, ctx.d = g, relu, d
+        ctx.g, ctx.d = g, d
+        ctx.relu = int(relu) | (0 if training else L.BN_EVAL)      # MSX_BN_* bit set for the backward
         ctx.bias = bias                      # leaf parameter (or None); only its identity is needed
         ctx.save_for_backward(x, weight, gamma, beta, y, mean, invstd)
         return z
@@ -410,7 +411,8 @@ class SumBNActFn(torch.autograd.Function):
             L.dtype_code(dt), len(xs), ptrs, lds, int(up2x), n, h, w, c, L.ptr(s), cp if s is not None else 0,
             L.ptr(_f32(gamma)), L.ptr(_f32(beta)), L.ptr(rm), L.ptr(rv), L.ptr(nbt), eps, momentum, int(training), int(relu),
             L.ptr(z), ld_of(z), L.ptr(mean), L.ptr(invstd), L.ptr(ws), ws.numel(), L.stream()))
-        ctx.c, ctx.relu, ctx.up2x, ctx.nx = c, relu, up2x, len(xs)
+        ctx.c, ctx.up2x, ctx.nx = c, up2x, len(xs)
+        ctx.relu = int(relu) | (0 if training else L.BN_EVAL)
         ctx.x0_shape = xs[0].shape
         ctx.save_for_backward(s if need_sum else xs[0], gamma, beta, mean, invstd)
         return z

@@ -2,7 +2,8 @@
 
 Run in the build container only (the reference is not present on the GPU box):
 
-    python oracle/gen_golden.py
+    python oracle/gen_golden.py            # UNet-8 / DuckNet-3 / losses / parameter counts
+    python oracle/gen_golden.py --wide     # DuckNet-17 and -34 (the benchmark's channel widths)
 
 The reference's ``models`` package imports ``segmentation_models_pytorch`` at module top
 (models/__init__.py:2), which is not installed; a stub is placed in ``sys.modules`` so that
@@ -58,7 +59,7 @@ class Cfg:
     pass
 
 
-def model_case(ref_cls, name, base, n, hw, seed, loss_mod, out):
+def model_case(ref_cls, name, base, n, hw, seed, loss_mod, out, light=False):
     rng = np.random.Generator(np.random.PCG64(seed))
     img, mask = synth_batch(rng, n, hw, hw, 2, ignore_frac=0.03)
     layout = ref_models.model_layout(name, num_class=2, n_channel=3, base_channel=base)
@@ -78,9 +79,11 @@ def model_case(ref_cls, name, base, n, hw, seed, loss_mod, out):
         x = torch.from_numpy(img).to(dt)
         logits = model(x)
         loss = loss_fn(logits, torch.from_numpy(mask))
-        loss.backward()
         res[f'logits_{tag}'] = logits.detach().numpy()
         res[f'loss_{tag}'] = loss.detach().numpy()
+        if light:                      # forward only (the 160 M-parameter base-34 model)
+            continue
+        loss.backward()
         gn = []
         for k, p in model.named_parameters():
             gn.append(p.grad.norm().item())
@@ -113,6 +116,80 @@ def model_case(ref_cls, name, base, n, hw, seed, loss_mod, out):
     res['param_names'] = np.asarray([k for k, _ in model.named_parameters()])
     np.savez_compressed(out, **res)
     print('wrote', out, {k: getattr(v, 'shape', None) for k, v in res.items() if k.startswith('logits')})
+
+
+def _rel(a, b):
+    return float((a.detach().double() - b.detach().double()).norm() / max(float(b.detach().double().norm()), 1e-300))
+
+
+def stage_case(ref_cls, base, n, hw, seed, out, backward=True):
+    """Teacher-forced block-level yardstick for bf16: every DuckNet block of the REAL reference
+    is run alone from the fp64-truth inputs of that block (rounded to bf16), once in fp64 (truth) and once under the
+    reference's AMP switch with dtype=bfloat16 (core/seg_trainer.py:61; backward outside autocast, :82).  The
+    recorded errors of the reference against its own fp64 twin are what the CUDA path is held to in
+    tests/test_gpu_models.py - whole-network bf16 logits cannot serve (the reference disagrees with itself by
+    ~0.7 rel-L2 there: stacked train-mode BN amplifies every rounding ~50x)."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    img, _ = synth_batch(rng, n, hw, hw, 2, ignore_frac=0.03)
+    layout = ref_models.model_layout('ducknet', num_class=2, n_channel=3, base_channel=base)
+    sd = ref_models.synth_state_dict(layout, seed + 100)
+    m64 = ref_cls(num_class=2, n_channel=3, base_channel=base)
+    m64.load_state_dict(sd)
+    m64 = m64.double().train()
+    m32 = ref_cls(num_class=2, n_channel=3, base_channel=base)
+    m32.load_state_dict(sd)
+    m32.train()
+    # block inputs of the fp64 forward, via the oracle restatement (pinned to the reference by the whole-model fixture)
+    plan, _ = ref_models.FnNet('ducknet', ref_models.make_trainable(sd, torch.float64), training=True).ducknet_stages(
+        torch.from_numpy(img).double())
+
+    def module_of(model, prefix):
+        mod = model
+        for part in prefix.replace('.duck', '').split('.'):
+            mod = mod[int(part)] if part.isdigit() else getattr(mod, part)
+        return mod
+
+    def call(mod, kind, ins):
+        if kind == 'down1':
+            return mod(ins[0])
+        if kind == 'down':
+            return mod(ins[0] + ins[1], ins[1])
+        if kind == 'res':
+            return (mod(ins[0]),)
+        return (mod(ins[0], ins[1]),)
+
+    names, fwd, din, dp_med, dp_max = [], [], [], [], []
+    for idx, (prefix, kind, ins) in enumerate(plan):
+        ins_r = [t.float().bfloat16().float() for t in ins]
+        mod64, mod32 = module_of(m64, prefix), module_of(m32, prefix)
+        i64 = [t.double().requires_grad_(kind != 'down1') for t in ins_r]
+        o64 = call(mod64, kind, i64)
+        douts = [ref_models.stage_dout(idx, k, o.shape) for k, o in enumerate(o64)]
+        i32 = [t.clone().requires_grad_(kind != 'down1') for t in ins_r]
+        with torch.autocast('cpu', dtype=torch.bfloat16):
+            o32 = call(mod32, kind, i32)
+        names.append(prefix)
+        fwd.append(max(_rel(a, b) for a, b in zip(o32, o64)))
+        if not backward:
+            continue
+        m64.zero_grad()
+        m32.zero_grad()
+        sum((o * d.double()).sum() for o, d in zip(o64, douts)).backward()
+        sum((o.float() * d).sum() for o, d in zip(o32, douts)).backward()
+        din.append(max([_rel(a.grad, b.grad) for a, b in zip(i32, i64) if b.grad is not None] or [0.0]))
+        g64 = [p.grad for p in mod64.parameters()]
+        g32 = [p.grad for p in mod32.parameters()]
+        gmax = max(float(g.norm()) for g in g64)
+        errs = np.array([_rel(a, b) for a, b in zip(g32, g64) if float(b.norm()) > 1e-9 * gmax])
+        dp_med.append(float(np.median(errs)))
+        dp_max.append(float(errs.max()))
+        print(f'{prefix:18s} fwd {fwd[-1]:.3e} din {din[-1]:.3e} dparam med {dp_med[-1]:.3e} max {dp_max[-1]:.3e}', flush=True)
+    res = {'stage_names': np.asarray(names), 'ref_bf16_fwd': np.asarray(fwd), 'base_channel': np.int64(base),
+           'weight_seed': np.int64(seed + 100), 'data_seed': np.int64(seed), 'n': np.int64(n), 'hw': np.int64(hw)}
+    if backward:
+        res.update({'ref_bf16_din': np.asarray(din), 'ref_bf16_dparam_median': np.asarray(dp_med), 'ref_bf16_dparam_max': np.asarray(dp_max)})
+    np.savez_compressed(out, **res)
+    print('wrote', out, 'fwd errors', np.round(fwd, 4))
 
 
 def loss_case(loss_mod, out):
@@ -166,6 +243,14 @@ def main():
     UNet, DuckNet, loss_mod = load_reference()
     g = os.path.join(ROOT, 'tests', 'golden')
     os.makedirs(g, exist_ok=True)
+    if '--wide' in sys.argv:
+        # the benchmark's own channel widths (17 * 2^k and 34 * 2^k): whole model + per-block bf16 yardstick
+        torch.set_num_threads(os.cpu_count() or 1)
+        model_case(DuckNet, 'ducknet', 17, 2, 128, 13, loss_mod, os.path.join(g, 'ducknet_b17_128.npz'))
+        stage_case(DuckNet, 17, 2, 128, 13, os.path.join(g, 'ducknet_b17_128_stages.npz'))
+        model_case(DuckNet, 'ducknet', 34, 2, 96, 14, loss_mod, os.path.join(g, 'ducknet_b34_96.npz'), light=True)
+        stage_case(DuckNet, 34, 2, 96, 14, os.path.join(g, 'ducknet_b34_96_stages.npz'), backward=False)
+        return
     model_case(UNet, 'unet', 8, 2, 32, 11, loss_mod, os.path.join(g, 'unet_b8_32.npz'))
     model_case(DuckNet, 'ducknet', 3, 2, 64, 12, loss_mod, os.path.join(g, 'ducknet_b3_64.npz'))
     loss_case(loss_mod, os.path.join(g, 'losses.npz'))

@@ -246,8 +246,49 @@ class FnNet:
             x = self.duck(x, f'up_stage{i}.duck')
         return F.conv2d(x, self.p['seg_head.weight'])
 
+    # -- DuckNet cut at block boundaries (teacher-forcing protocol of the -m gpu model tests) -------
+    def stage_fn(self, kind, p):
+        """The function one DuckNet block computes from its input tensors (models/ducknet.py:38-49):
+        'down1' (img) / 'down' (x_prev1, x) -> (x1, skip, x2); 'res' (x) -> y; 'up' (x, skip) -> y."""
+        if kind == 'down1':
+            return lambda img: self._duck_down(img, None, p)
+        if kind == 'down':
+            return lambda a, b: self._duck_down(a + b, b, p)
+        if kind == 'res':
+            return lambda x: (self.resblock(x, p),)
+        if kind == 'up':
+            return lambda x, skip: (self.duck(F.interpolate(x, skip.shape[2:], mode='nearest') + skip, p),)
+        raise ValueError(kind)
+
+    def ducknet_stages(self, x):
+        """Run the DuckNet forward and return ([(prefix, kind, inputs)], logits): the inputs every block saw,
+        detached, so that each block can be re-run alone from the same tensors."""
+        rec = []
+
+        def run(kind, p, *ins):
+            rec.append((p, kind, tuple(t.detach().clone() for t in ins)))
+            return self.stage_fn(kind, p)(*ins)
+        x1, s1, x = run('down1', 'down_stage1', x)
+        skips = [s1]
+        for i in (2, 3, 4, 5):
+            x1, s, x = run('down', f'down_stage{i}', x1, x)
+            skips.append(s)
+        x = x1 + x
+        for j in range(4):
+            x, = run('res', f'mid_stage.{j}', x)
+        for i, skip in zip((5, 4, 3, 2, 1), reversed(skips)):
+            x, = run('up', f'up_stage{i}.duck', x, skip)
+        return rec, F.conv2d(x, self.p['seg_head.weight'])
+
     def __call__(self, x):
         return self.unet(x) if self.name == 'unet' else self.ducknet(x)
+
+
+def stage_dout(stage_index, k, shape):
+    """Upstream gradient of output ``k`` of DuckNet block ``stage_index`` in the teacher-forcing tests:
+    N(0, 1) from numpy PCG64 (torch-version independent), rounded to bf16 so every precision sees the same values."""
+    rng = np.random.Generator(np.random.PCG64(1000 + 10 * stage_index + k))
+    return torch.from_numpy(rng.standard_normal(tuple(shape)).astype(np.float32)).bfloat16().float()
 
 
 def make_trainable(sd, dtype=None):

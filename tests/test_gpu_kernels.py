@@ -81,6 +81,11 @@ TC_CASES = [
     (17, 17, 7, 1, 1, 64, 32, 2),       # halo path, no x-halo (8-pixel-wide halo rows)
     (17, 17, 3, 3, 3, 48, 48, 2),       # halo path, dilation 3
     (64, 64, 3, 3, 1, 48, 40, 1),       # halo path, full 64-channel chunk
+    (17, 17, 1, 1, 1, 32, 48, 2),       # 1x1 at <= 64 channels: conv_tc_halo_kernel<1,K> (resident weights, no halo), K = 2
+    (34, 34, 1, 1, 1, 24, 24, 2),       # K = 3
+    (64, 64, 1, 1, 1, 24, 40, 2),       # K = 4
+    (3, 17, 1, 1, 1, 32, 32, 2),        # K = 1 (DUCK(3 -> 17) shortcuts)
+    (34, 17, 1, 1, 1, 32, 32, 2),       # up-path shortcut 2b -> b
 ]
 
 
@@ -121,6 +126,8 @@ S2_CASES = [
     (64, 32, 3, 1, 20, 20, 2, True),         # ConvTranspose2d(3, s2, p1, op1): 20 -> 40
     (512, 256, 3, 1, 11, 11, 1, True),
     (17, 24, 3, 1, 12, 20, 2, True),
+    (17, 34, 3, 1, 352, 352, 2, False),      # DownsampleBlock.conv1 of stage 1 at the benchmark's real 352 -> 176 size
+    (3, 34, 2, 0, 352, 352, 2, False),       # DownsampleBlock.conv2 of stage 1 (2x2 s2 stem) at 352 -> 176
 ]
 
 
@@ -242,21 +249,174 @@ def test_maxpool_3s2(dtype):
     assert rel(from_act(a.t.grad, 24), xd.grad) < (1e-6 if dtype == torch.float32 else 1e-2)
 
 
+@pytest.mark.parametrize('case', [(17, 17, 3, 3, 1), (3, 17, 3, 3, 1), (17, 17, 1, 7, 1), (17, 17, 3, 3, 2)])
+def test_wgrad_tcgen05_full_size(case):
+    """Weight gradient at the benchmark's own size, 16 x 352 x 352 (tap-stacked halo mode, 148 pixel splits, 105 tiles
+    accumulated in TMEM per CTA), against the float64 weight gradient of F.conv2d on the CPU."""
+    ops = _ops()
+    from medical_segmentation_pytorch_b200 import _lib
+    cin, cout, kh, kw, dil = case
+    n, H = 16, 352
+    torch.manual_seed(sum(case))
+    torch.set_num_threads(max(1, (__import__('os').cpu_count() or 2)))
+    x = torch.randn(n, cin, H, H).bfloat16().float()
+    dy = torch.randn(n, cout, H, H).bfloat16().float()
+    pad = ((kh - 1) // 2 * dil, (kw - 1) // 2 * dil)
+    dw_ref = torch.nn.grad.conv2d_weight(x.double(), (cout, cin, kh, kw), dy.double(), stride=1, padding=pad, dilation=dil)
+    g = ops.ConvGeom(cin, cout, kh, kw, 1, dil, pad[0], pad[1], engine=2)
+    a = to_act(x, torch.bfloat16)                       # no input gradient: only the wgrad kernels run in backward
+    wp = torch.nn.Parameter((torch.randn(cout, cin, kh, kw) / (cin * kh * kw) ** 0.5).to(DEV))
+    y = ops.Conv2dFn.apply(a.t, wp, g)
+    y.backward(to_act(dy, torch.bfloat16).t)
+    torch.cuda.synchronize()
+    assert _lib.lib.msx_last_conv_engine() == 2
+    e = rel(wp.grad, dw_ref)
+    print(f'full-size wgrad {case}: rel-L2 {e:.2e}')
+    assert e < 1e-4                                     # bf16-exact operands, fp32 accumulation over 2 M pixels
+
+
 @pytest.mark.parametrize('nc', [1, 2, 5])
-def test_head(nc):
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_head(nc, dtype):
     ops = _ops()
     torch.manual_seed(nc)
     c, n, h, w = 17, 2, 8, 12
     x, wt = torch.randn(n, c, h, w), torch.randn(nc, c, 1, 1)
+    if dtype == torch.bfloat16:
+        x = x.bfloat16().float()
     xd, wd = x.double().requires_grad_(True), wt.double().requires_grad_(True)
     ref = F.conv2d(xd, wd)
     dl = torch.randn(ref.shape)
     ref.backward(dl.double())
-    a = to_act(x, torch.float32, True)
+    a = to_act(x, dtype, True)
     wp = torch.nn.Parameter(wt.to(DEV))
     out = ops.HeadFn.apply(a.t, wp, c)
+    assert out.dtype == torch.float32                    # logits leave the head as NCHW fp32 in either mode
     out.backward(dl.to(DEV))
-    assert rel(out, ref) < 1e-6 and rel(from_act(a.t.grad, c), xd.grad) < 1e-6 and rel(wp.grad, wd.grad) < 1e-6
+    tol = 1e-6 if dtype == torch.float32 else 4e-3      # bf16: only dx is rounded to bf16 on store
+    assert rel(out, ref) < 1e-6 and rel(wp.grad, wd.grad) < 1e-6
+    assert rel(from_act(a.t.grad, c), xd.grad) < tol
+
+
+def _arena_model():
+    import medical_segmentation_pytorch_b200 as msx
+    torch.manual_seed(2)
+    m = msx.UNet(2, 3, 8).to(DEV)
+    ref = [p.detach().clone().requires_grad_(True) for p in m.parameters()]
+    return msx, m, ref
+
+
+@pytest.mark.parametrize('kind', ['sgd', 'adam', 'adamw'])
+def test_fused_optimizer_matches_torch_optim(kind):
+    """msx_sgd_step / msx_adam_step over the flat arena vs torch.optim.{SGD, Adam, AdamW} with the reference's
+    hyper-parameters (utils/optimizer.py:8-16: SGD momentum 0.9, weight decay 1e-4 on every parameter; Adam / AdamW
+    torch defaults), four steps with fresh gradients, a changing learning rate and the 1/world gradient scale."""
+    msx, m, ref = _arena_model()
+    opt = msx.FusedOptimizer(m, kind, lr=0.05, momentum=0.9, weight_decay=1e-4 if kind == 'sgd' else 0.0)
+    tkw = dict(lr=0.05)
+    if kind == 'sgd':
+        tkw.update(momentum=0.9, weight_decay=1e-4)
+    topt = {'sgd': torch.optim.SGD, 'adam': torch.optim.Adam, 'adamw': torch.optim.AdamW}[kind](ref, **tkw)
+    params = list(m.parameters())
+    for step in range(4):
+        lr = 0.05 * (1 + step) / 2
+        opt.param_groups[0]['lr'] = lr
+        topt.param_groups[0]['lr'] = lr
+        for p, r in zip(params, ref):
+            gr = torch.randn_like(r)
+            p.grad.copy_(gr * 2.0)                        # arena gradient holds the SUM over 2 ranks ...
+            r.grad = gr.clone()
+        opt.step(grad_scale=0.5)                          # ... and the step applies 1/world
+        topt.step()
+        worst = max(rel(p, r) for p, r in zip(params, ref))
+        assert worst < 2e-6, (kind, step, worst)
+
+
+@pytest.mark.parametrize('use_ema', [False, True])
+def test_model_ema_matches_reference_rule(use_ema):
+    """ModelEmaV2.update (utils/model_ema.py:29-40) over the arenas: with use_ema the reference applies
+    decay * e + (1 - decay) * m to EVERY state_dict tensor - the int64 num_batches_tracked counters included, whose
+    float result is truncated back to int64 by copy_ - with decay = clamp(itr / total_itrs, 0, 1); otherwise a plain
+    copy.  Bit-exact against the per-tensor torch expressions, over three updates with a training step in between."""
+    msx, m, _ = _arena_model()
+    from medical_segmentation_pytorch_b200.synth import synth_batch
+    ema = msx.ModelEma(m, use_ema=use_ema, total_itrs=10)
+    want = {k: v.detach().clone() for k, v in m.state_dict().items()}          # the deepcopy at construction
+    x, t = synth_batch(2, 32, 32, seed=4)
+    x, t = x.to(DEV), t.to(DEV)
+    opt = msx.FusedOptimizer(m, 'sgd', lr=0.05)
+    lf = msx.get_loss_fn(Cfg(), DEV)
+    m.train()
+    for itr in (3, 4, 7):
+        for _ in range(itr):                                                # several forwards: num_batches_tracked moves by more than 1
+            lf(m(x), t).backward()
+        opt.step()
+        ema.update(m, itr)
+        decay = min(max(itr / 10, 0), 1)
+        for k, mv in m.state_dict().items():
+            want[k] = (decay * want[k] + (1. - decay) * mv).to(want[k].dtype) if use_ema else mv.detach().clone()
+        got = ema.ema.state_dict()
+        assert list(got.keys()) == list(want.keys())
+        for k in want:
+            assert got[k].dtype == want[k].dtype and torch.equal(got[k], want[k]), (k, itr)
+    assert not ema.ema.training and all(not p.requires_grad for p in ema.ema.parameters())
+
+
+@pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
+def test_eval_mode_bn_backward_uses_running_statistics(dtype):
+    """A forward in eval mode with autograd on (frozen-BN fine-tuning, saliency maps): BatchNorm is a fixed affine map, so
+    dx = gamma * invstd * g without the batch-statistics terms; checked for ConvBNAct and for a stand-alone sum -> BN ->
+    ReLU against torch's eval-mode BatchNorm in float64."""
+    import medical_segmentation_pytorch_b200 as msx
+    torch.manual_seed(9)
+    cin, cout, n, H = 8, 17, 2, 12
+    m = msx.modules.ConvBNAct(cin, cout, 3).to(DEV)
+    with torch.no_grad():
+        m[1].running_mean.uniform_(-0.5, 0.5)
+        m[1].running_var.uniform_(0.5, 1.5)
+        m[1].weight.uniform_(0.5, 1.5)
+        m[1].bias.uniform_(-0.3, 0.3)
+        if dtype == torch.bfloat16:
+            m[0].weight.copy_(m[0].weight.bfloat16().float())
+    m.eval()
+    ref = torch.nn.Sequential(torch.nn.Conv2d(cin, cout, 3, 1, 1, bias=False), torch.nn.BatchNorm2d(cout), torch.nn.ReLU()).double()
+    ref.load_state_dict({k: v.double().cpu() if v.is_floating_point() else v.cpu() for k, v in m.state_dict().items()})
+    ref.eval()
+    x = torch.randn(n, cin, H, H)
+    if dtype == torch.bfloat16:
+        x = x.bfloat16().float()
+    xd = x.double().requires_grad_(True)
+    zr = ref(xd)
+    dz = torch.randn(zr.shape)
+    zr.backward(dz.double())
+    a = to_act(x, dtype, requires_grad=True)
+    z = m(a)
+    z.t.backward(to_act(dz, dtype).t)
+    tol = 2e-5 if dtype == torch.float32 else 3e-2
+    assert rel(from_act(z.t.detach(), cout), zr) < tol
+    assert rel(from_act(a.t.grad, cin), xd.grad) < tol
+    assert rel(m[0].weight.grad, ref[0].weight.grad) < tol
+    assert rel(m[1].weight.grad, ref[1].weight.grad) < tol and rel(m[1].bias.grad, ref[1].bias.grad) < tol
+    # stand-alone BN after an add (ResidualBlock.bn in eval mode)
+    bn = torch.nn.BatchNorm2d(cout).to(DEV)
+    with torch.no_grad():
+        bn.running_mean.uniform_(-0.5, 0.5)
+        bn.running_var.uniform_(0.5, 1.5)
+    bn.eval()
+    u, v = torch.randn(n, cout, H, H), torch.randn(n, cout, H, H)
+    if dtype == torch.bfloat16:
+        u, v = u.bfloat16().float(), v.bfloat16().float()
+    ud, vd = u.double().requires_grad_(True), v.double().requires_grad_(True)
+    bref = torch.nn.BatchNorm2d(cout).double()
+    bref.load_state_dict({k: t.double().cpu() if t.is_floating_point() else t.cpu() for k, t in bn.state_dict().items()})
+    bref.eval()
+    zr = torch.relu(bref(ud + vd))
+    zr.backward(dz.double())
+    ua, va = to_act(u, dtype, True), to_act(v, dtype, True)
+    z = msx.modules.sum_bn_act([ua, va], bn, 1)
+    z.t.backward(to_act(dz, dtype).t)
+    assert rel(from_act(ua.t.grad, cout), ud.grad) < tol and rel(from_act(va.t.grad, cout), vd.grad) < tol
+    assert rel(bn.weight.grad, bref.weight.grad) < tol
 
 
 # ---- losses ------------------------------------------------------------------------------------

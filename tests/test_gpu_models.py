@@ -3,10 +3,15 @@
 
 Protocol: an error of the new path against fp64 truth must not exceed
 max(3 x the reference-fp32 error against the same truth, floor).  Loss within 1e-4 relative
-(north_star fp32 tolerance).  bf16 (autocast) tolerance, stated: loss within 5e-2 relative; logits
-rel-L2 against fp64 truth at most 1.5 x what the reference itself shows under
-torch.autocast(dtype=bfloat16) on the same inputs (golden 'logits_bf16'; 0.06 on the UNet case, 0.77 on
-the tiny DuckNet whose 2x2-pixel BatchNorms are ill-conditioned in any precision)."""
+(north_star fp32 tolerance).  bf16 (autocast) tolerance, stated.  UNet: loss within 5e-2 relative; logits rel-L2 against fp64 truth at most
+1.5 x what the reference itself shows under torch.autocast(dtype=bfloat16) on the same inputs (golden
+'logits_bf16': 0.06).  DUCK-Net: whole-network bf16 logits are NOT a usable yardstick - the unmodified reference
+under bf16 autocast differs from its own fp64 twin by ~0.7 rel-L2 at every size and width tried (stacked
+train-mode BN amplifies each rounding ~50x: the same network disagrees with itself by 4e-4 in fp32) - so the
+bf16 gate is block-wise teacher forcing at the benchmark's own channel widths (17 * 2^k, 34 * 2^k): every
+DuckNet block is run alone from the fp64-truth inputs of that block (rounded to bf16) and compared with the
+fp64 oracle; the bound is a multiple of the error the REAL reference shows in the same protocol
+(tests/golden/ducknet_b*_stages.npz, written by oracle/gen_golden.py --wide), every bound <= 0.2."""
 import os
 
 import numpy as np
@@ -25,7 +30,7 @@ def _build(name, base):
     return cls(num_class=2, n_channel=3, base_channel=base).to(DEV), ref_models
 
 
-@pytest.mark.parametrize('name,fname', [('unet', 'unet_b8_32.npz'), ('ducknet', 'ducknet_b3_64.npz')])
+@pytest.mark.parametrize('name,fname', [('unet', 'unet_b8_32.npz'), ('ducknet', 'ducknet_b3_64.npz'), ('ducknet', 'ducknet_b17_128.npz')])
 def test_model_fp32_vs_reference_golden(golden_dir, name, fname):
     import medical_segmentation_pytorch_b200 as msx
     g = np.load(os.path.join(golden_dir, fname))
@@ -75,26 +80,127 @@ def test_model_fp32_vs_reference_golden(golden_dir, name, fname):
     assert list(out.keys()) == list(sd.keys()) and all(tuple(out[k].shape) == tuple(sd[k].shape) for k in sd)
 
 
-@pytest.mark.parametrize('name,fname', [('unet', 'unet_b8_32.npz'), ('ducknet', 'ducknet_b3_64.npz')])
-def test_model_bf16_autocast(golden_dir, name, fname):
+def test_unet_bf16_autocast(golden_dir):
     import medical_segmentation_pytorch_b200 as msx
-    g = np.load(os.path.join(golden_dir, fname))
+    from medical_segmentation_pytorch_b200 import _lib
+    g = np.load(os.path.join(golden_dir, 'unet_b8_32.npz'))
     base = int(g['base_channel'])
-    model, ref_models = _build(name, base)
-    model.load_state_dict(ref_models.synth_state_dict(ref_models.model_layout(name, num_class=2, n_channel=3, base_channel=base), int(g['weight_seed'])))
+    model, ref_models = _build('unet', base)
+    model.load_state_dict(ref_models.synth_state_dict(ref_models.model_layout('unet', num_class=2, n_channel=3, base_channel=base), int(g['weight_seed'])))
     model.train()
     x, t = torch.from_numpy(g['images']).to(DEV), torch.from_numpy(g['masks']).to(DEV)
     with torch.autocast('cuda', dtype=torch.bfloat16):          # the reference's AMP switch (core/seg_trainer.py:61)
         logits = model(x)
         loss = msx.get_loss_fn(Cfg(), DEV)(logits, t)
     loss.backward()
-    assert logits.dtype == torch.float32
+    assert logits.dtype == torch.float32 and _lib.lib.msx_last_conv_engine() == 2
     e = rel(logits, g['logits_f64'])
-    e_ref = rel(g['logits_bf16'], g['logits_f64'])           # the reference itself under bf16 autocast (CPU)
-    print(f'{name} bf16: logits rel-L2 {e:.3e} (reference bf16 autocast {e_ref:.3e}), loss {float(loss):.5f} vs {float(g["loss_f64"]):.5f}')
-    assert e <= max(1.5 * e_ref, 0.05)
+    e_ref = rel(g['logits_bf16'], g['logits_f64'])           # the reference itself under bf16 autocast (CPU): 0.06
+    print(f'unet bf16: logits rel-L2 {e:.3e} (reference bf16 autocast {e_ref:.3e}), loss {float(loss):.5f} vs {float(g["loss_f64"]):.5f}')
+    assert e_ref < 0.1 and e <= 1.5 * e_ref
     assert abs(float(loss) - float(g['loss_f64'])) <= 5e-2 * abs(float(g['loss_f64']))
     assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in model.parameters())
+
+
+@pytest.mark.parametrize('fname', ['ducknet_b3_64.npz', 'ducknet_b17_128.npz'])
+def test_ducknet_bf16_autocast_whole_model(golden_dir, fname):
+    """Whole DUCK-Net step under bf16 autocast on the tcgen05 engine: loss within 1e-2 of the fp64 reference (the
+    reference's own bf16 run is within 1e-3), all gradients finite.  The logits error is printed, not bounded
+    (module docstring: the reference's own figure is ~0.7); block-wise parity is the next test."""
+    import medical_segmentation_pytorch_b200 as msx
+    from medical_segmentation_pytorch_b200 import _lib
+    g = np.load(os.path.join(golden_dir, fname))
+    base = int(g['base_channel'])
+    model, ref_models = _build('ducknet', base)
+    model.load_state_dict(ref_models.synth_state_dict(ref_models.model_layout('ducknet', num_class=2, n_channel=3, base_channel=base), int(g['weight_seed'])))
+    model.train()
+    x, t = torch.from_numpy(g['images']).to(DEV), torch.from_numpy(g['masks']).to(DEV)
+    with torch.autocast('cuda', dtype=torch.bfloat16):
+        logits = model(x)
+        loss = msx.get_loss_fn(Cfg(), DEV)(logits, t)
+    loss.backward()
+    torch.cuda.synchronize()
+    assert logits.dtype == torch.float32 and _lib.lib.msx_last_conv_engine() == 2
+    e, e_ref = rel(logits, g['logits_f64']), rel(g['logits_bf16'], g['logits_f64'])
+    print(f'ducknet-{base} bf16: logits rel-L2 {e:.3e} (reference bf16 autocast {e_ref:.3e}), loss {float(loss):.6f} vs {float(g["loss_f64"]):.6f} '
+          f'(reference bf16 {float(g["loss_bf16"]):.6f})')
+    assert abs(float(loss) - float(g['loss_f64'])) <= 1e-2 * abs(float(g['loss_f64']))
+    assert all(p.grad is not None and torch.isfinite(p.grad).all() for p in model.parameters())
+
+
+def _module_of(model, prefix):
+    mod = model
+    for part in prefix.replace('.duck', '').split('.'):
+        mod = mod[int(part)] if part.isdigit() else getattr(mod, part)
+    return mod
+
+
+def _run_block(model, kind, prefix, acts):
+    from medical_segmentation_pytorch_b200.modules import fanout
+    mod = _module_of(model, prefix)
+    if kind == 'down1':
+        return mod([acts[0]], acts[0])
+    if kind == 'down':                                   # DuckNet._forward: x feeds the add and the next conv2
+        xa, xb = fanout(acts[1], 2)
+        return mod([acts[0], xa], xb)
+    if kind == 'res':
+        return (mod(acts[0]),)
+    return (mod(acts[0], acts[1]),)
+
+
+@pytest.mark.parametrize('fname,backward', [('ducknet_b17_128', True), ('ducknet_b34_96', False)])
+def test_ducknet_bf16_blocks_teacher_forced(golden_dir, fname, backward):
+    """Every block of DuckNet-17 / -34 (5 DownsampleBlocks, 4 mid ResidualBlocks, 5 UpsampleBlocks: all 273 convs at
+    17 * 2^k / 34 * 2^k channels) in bf16 on the tcgen05 engine, alone, from the fp64 oracle's inputs of that block
+    rounded to bf16; outputs, input gradients and every parameter gradient of the block against the fp64 oracle.
+    Bounds: forward <= 2 x the real reference's own bf16 error in the same protocol (<= 0.033); input gradients and
+    the per-tensor median of parameter gradients <= 1.0 x the reference's (<= 0.18 / 0.14); worst single parameter
+    tensor <= 0.2 + nothing (absolute; the reference reaches 0.23-0.42 there)."""
+    import medical_segmentation_pytorch_b200 as msx
+    from medical_segmentation_pytorch_b200 import _lib
+    from gpu_util import from_act, to_act
+    g = np.load(os.path.join(golden_dir, fname + '.npz'))
+    st = np.load(os.path.join(golden_dir, fname + '_stages.npz'))
+    base = int(g['base_channel'])
+    model, ref_models = _build('ducknet', base)
+    sd = ref_models.synth_state_dict(ref_models.model_layout('ducknet', num_class=2, n_channel=3, base_channel=base), int(g['weight_seed']))
+    model.load_state_dict(sd)
+    model.train()
+    params = dict(model.named_parameters())
+    torch.set_num_threads(max(1, (os.cpu_count() or 2)))
+    p64 = ref_models.make_trainable(sd, torch.float64)
+    net = ref_models.FnNet('ducknet', p64, training=True)
+    with torch.no_grad():
+        plan, _ = net.ducknet_stages(torch.from_numpy(g['images']).double())
+    assert [pfx for pfx, _, _ in plan] == [str(s) for s in st['stage_names']]
+    for idx, (prefix, kind, ins) in enumerate(plan):
+        ins_r = [t.float().bfloat16().float() for t in ins]
+        i64 = [t.double().requires_grad_(backward and kind != 'down1') for t in ins_r]
+        o64 = net.stage_fn(kind, prefix)(*i64)
+        acts = [to_act(t, torch.bfloat16, requires_grad=backward and kind != 'down1') for t in ins_r]
+        outs = _run_block(model, kind, prefix, acts)
+        assert _lib.lib.msx_last_conv_engine() == 2
+        e_fwd = max(rel(from_act(o.t.detach(), o.c), r) for o, r in zip(outs, o64))
+        ref_fwd = float(st['ref_bf16_fwd'][idx])
+        msg = f'{fname} {prefix}: fwd {e_fwd:.3e} (reference bf16 {ref_fwd:.3e})'
+        assert e_fwd <= 2.0 * ref_fwd, msg
+        if backward:
+            for v in list(p64.values()) + list(params.values()):
+                v.grad = None
+            douts = [ref_models.stage_dout(idx, k, o.shape) for k, o in enumerate(o64)]
+            sum((o * d.double()).sum() for o, d in zip(o64, douts)).backward()
+            torch.autograd.backward([o.t for o in outs], [to_act(d, torch.bfloat16).t for d in douts])
+            torch.cuda.synchronize()
+            e_din = max([rel(from_act(a.t.grad, a.c), r.grad) for a, r in zip(acts, i64) if r.grad is not None] or [0.0])
+            keys = [k for k in params if k.startswith(prefix.replace('.duck', '') + '.')]
+            gmax = max(float(p64[k].grad.norm()) for k in keys)
+            errs = np.array([rel(params[k].grad, p64[k].grad) for k in keys if float(p64[k].grad.norm()) > 1e-9 * gmax])
+            r_din, r_med, r_max = float(st['ref_bf16_din'][idx]), float(st['ref_bf16_dparam_median'][idx]), float(st['ref_bf16_dparam_max'][idx])
+            msg += f' din {e_din:.3e} ({r_din:.3e}) dparam median {np.median(errs):.3e} ({r_med:.3e}) max {errs.max():.3e} ({r_max:.3e})'
+            assert e_din <= max(1.0 * r_din, 0.05), msg
+            assert np.median(errs) <= 1.0 * r_med, msg
+            assert errs.max() <= 0.2, msg
+        print(msg)
 
 
 def test_train_step_flat_arena_matches_autograd_path():

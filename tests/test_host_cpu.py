@@ -140,3 +140,51 @@ def test_teacher_state_dict_matches_the_oracle_layout():
         assert list(sa.keys()) == list(sb.keys())
         assert all(sa[k].shape == sb[k].shape and sa[k].dtype == sb[k].dtype for k in sb)
         a.load_state_dict(sb)
+
+
+def test_optimizer_and_ema_built_from_the_ddp_wrapper_share_the_wrapped_arena():
+    """The usual PyTorch order (wrap first, then build the optimizer): FusedOptimizer / ModelEma / get_optimizer must
+    find the arena of the WRAPPED module instead of flattening the parameters a second time (which would leave DDP's
+    buckets reducing a dead gradient arena)."""
+    import medical_segmentation_pytorch_b200 as msx
+    from medical_segmentation_pytorch_b200.flat import FlatParams
+    m = msx.UNet(2, 3, 8)
+    ddp = msx.DistributedDataParallelB200(m)                # world 1 without a process group: host logic only
+    opt = msx.FusedOptimizer(ddp, 'sgd', lr=0.1)
+    assert opt.flat is ddp.flat and m._msx_flat is ddp.flat
+    ema = msx.ModelEma(ddp)
+    assert ema.src_p is ddp.flat
+
+    class C:
+        optimizer_type, base_lr, gpu_num, momentum, weight_decay = 'adamw', 0.01, 2, 0.9, 1e-4
+    opt2 = msx.get_optimizer(C, ddp)
+    assert opt2.flat is ddp.flat and abs(C.lr - 0.002) < 1e-12 and opt2.param_groups[0]['weight_decay'] == 0.01
+    with pytest.raises(RuntimeError, match='already live in a flat arena'):
+        FlatParams(m)
+    for p, q in zip(m.parameters(), opt.param_groups[0]['params']):
+        assert p is q
+
+
+def test_reference_lr_policies_drive_the_fused_optimizer():
+    """utils/scheduler.py:12-19: OneCycleLR stepped every iteration, which also cycles momentum (SGD) / beta1 (Adam);
+    the fused optimizer is a torch.optim.Optimizer, so torch's scheduler runs on it unchanged and step() sees the values."""
+    import medical_segmentation_pytorch_b200 as msx
+
+    class C:
+        DDP, train_num, train_bs, gpu_num, total_epoch, warmup_epochs, lr_policy = False, 80, 8, 1, 4, 1, 'cos_warmup'
+        optimizer_type, base_lr, momentum, weight_decay = 'sgd', 0.01, 0.9, 1e-4
+    m = msx.UNet(2, 3, 8)
+    opt = msx.get_optimizer(C, m)
+    sched = msx.get_scheduler(C, opt)
+    ref_opt = torch.optim.SGD([torch.nn.Parameter(torch.zeros(1))], lr=C.lr, momentum=0.9, weight_decay=1e-4)
+    ref_sched = torch.optim.lr_scheduler.OneCycleLR(ref_opt, max_lr=C.lr, total_steps=C.total_itrs, pct_start=0.25)
+    assert C.total_itrs == 40
+    for _ in range(5):
+        assert opt._hyper()[:2] == (ref_opt.param_groups[0]['lr'], ref_opt.param_groups[0]['momentum'])
+        sched.step()
+        ref_opt.step()
+        ref_sched.step()
+    assert opt.hyper_changed()
+    C.lr_policy = 'nope'
+    with pytest.raises(NotImplementedError):
+        msx.get_scheduler(C, opt)

@@ -44,6 +44,42 @@ def test_model_matches_reference_fp64(golden_dir, name, fname, fused_bn):
         assert rel(net(x).numpy(), g['eval_logits_f64']) < 1e-10
 
 
+def test_ducknet17_matches_reference_fp64(golden_dir):
+    """The oracle at the benchmark's own channel widths (17 * 2^k): whole-model vectors from the real reference."""
+    torch.set_num_threads(max(1, (os.cpu_count() or 2)))
+    g = np.load(os.path.join(golden_dir, 'ducknet_b17_128.npz'))
+    sd = ref_models.synth_state_dict(ref_models.model_layout('ducknet', num_class=2, n_channel=3, base_channel=17), int(g['weight_seed']))
+    p = ref_models.make_trainable(sd, torch.float64)
+    net = ref_models.FnNet('ducknet', p, training=True)
+    x = torch.from_numpy(g['images']).double()
+    plan, logits = net.ducknet_stages(x)                      # the block-cut forward IS the forward
+    loss = ref_loss.ce_loss(logits, torch.from_numpy(g['masks']))
+    loss.backward()
+    assert rel(logits.detach().numpy(), g['logits_f64']) < 1e-10
+    assert abs(loss.item() - float(g['loss_f64'])) < 1e-12
+    names = [str(s) for s in g['param_names']]
+    gn = np.array([p[k].grad.norm().item() for k in names])
+    big = g['grad_norms_f64'] > 1e-9 * g['grad_norms_f64'].max()
+    assert np.max(np.abs(gn[big] / g['grad_norms_f64'][big] - 1)) < 1e-6
+    st = np.load(os.path.join(golden_dir, 'ducknet_b17_128_stages.npz'))
+    assert [str(s) for s in st['stage_names']] == [pfx for pfx, _, _ in plan]
+    # re-running one block alone from its recorded inputs reproduces what the whole forward fed the next block
+    (p0, k0, ins0), (p1, k1, ins1) = plan[0], plan[1]
+    with torch.no_grad():
+        net2 = ref_models.FnNet('ducknet', ref_models.make_trainable(sd, torch.float64), training=True)
+        x1, _, xc = net2.stage_fn(k0, p0)(*ins0)
+    assert rel(x1.numpy(), ins1[0].numpy()) < 1e-12 and rel(xc.numpy(), ins1[1].numpy()) < 1e-12
+
+
+def test_ducknet34_forward_matches_reference_fp64(golden_dir):
+    torch.set_num_threads(max(1, (os.cpu_count() or 2)))
+    g = np.load(os.path.join(golden_dir, 'ducknet_b34_96.npz'))
+    sd = ref_models.synth_state_dict(ref_models.model_layout('ducknet', num_class=2, n_channel=3, base_channel=34), int(g['weight_seed']))
+    with torch.no_grad():
+        logits = ref_models.FnNet('ducknet', ref_models.make_trainable(sd, torch.float64), training=True)(torch.from_numpy(g['images']).double())
+    assert rel(logits.numpy(), g['logits_f64']) < 1e-10
+
+
 def test_param_counts_match_readme(golden_dir):
     g = np.load(os.path.join(golden_dir, 'param_counts.npz'))
     cases = {'unet32': ('unet', 32), 'ducknet17': ('ducknet', 17), 'ducknet34': ('ducknet', 34)}

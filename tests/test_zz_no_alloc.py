@@ -73,9 +73,10 @@ def test_static_scratch_entry_point_matches_workspace_entry_point(dtype):
     cases = [_case(1, 2, 24, 40, 17, dtype), _case(2, 3, 32, 48, 136, dtype)]
     expected = [_run(lib, L, k, static=False) for k in cases]
     torch.cuda.synchronize()
-    before = torch.cuda.memory_allocated()
     got = []
-    _run(lib, L, cases[0], static=True)                 # first call on this device looks up the scratch symbol
+    # first call on this device: looks up the scratch symbol (with lazy module loading this may be when the driver
+    # reserves the array), so it is made before the calls whose allocations are counted
+    _run(lib, L, cases[0], static=True)
     for k in cases:
         got.append(_run(lib, L, k, static=True, check_no_alloc=True))
     for exp, out in zip(expected, got):
@@ -85,7 +86,6 @@ def test_static_scratch_entry_point_matches_workspace_entry_point(dtype):
     again = _run(lib, L, cases[0], static=True)
     for a, b in zip(expected[0], again):
         assert torch.equal(a, b)
-    assert before >= 0
 
 
 def test_static_scratch_entry_point_rejects_oversize():
