@@ -158,7 +158,7 @@ def stage_case(ref_cls, base, n, hw, seed, out, backward=True):
             return (mod(ins[0]),)
         return (mod(ins[0], ins[1]),)
 
-    names, fwd, din, dp_med, dp_max = [], [], [], [], []
+    names, fwd, din, dp_med, dp_max, dp_glob = [], [], [], [], [], []
     for idx, (prefix, kind, ins) in enumerate(plan):
         ins_r = [t.float().bfloat16().float() for t in ins]
         mod64, mod32 = module_of(m64, prefix), module_of(m32, prefix)
@@ -183,11 +183,13 @@ def stage_case(ref_cls, base, n, hw, seed, out, backward=True):
         errs = np.array([_rel(a, b) for a, b in zip(g32, g64) if float(b.norm()) > 1e-9 * gmax])
         dp_med.append(float(np.median(errs)))
         dp_max.append(float(errs.max()))
-        print(f'{prefix:18s} fwd {fwd[-1]:.3e} din {din[-1]:.3e} dparam med {dp_med[-1]:.3e} max {dp_max[-1]:.3e}', flush=True)
+        dp_glob.append(_rel(torch.cat([g.flatten() for g in g32]), torch.cat([g.flatten() for g in g64])))
+        print(f'{prefix:18s} fwd {fwd[-1]:.3e} din {din[-1]:.3e} dparam global {dp_glob[-1]:.3e} med {dp_med[-1]:.3e} max {dp_max[-1]:.3e}', flush=True)
     res = {'stage_names': np.asarray(names), 'ref_bf16_fwd': np.asarray(fwd), 'base_channel': np.int64(base),
            'weight_seed': np.int64(seed + 100), 'data_seed': np.int64(seed), 'n': np.int64(n), 'hw': np.int64(hw)}
     if backward:
-        res.update({'ref_bf16_din': np.asarray(din), 'ref_bf16_dparam_median': np.asarray(dp_med), 'ref_bf16_dparam_max': np.asarray(dp_max)})
+        res.update({'ref_bf16_din': np.asarray(din), 'ref_bf16_dparam_median': np.asarray(dp_med), 'ref_bf16_dparam_max': np.asarray(dp_max),
+                    'ref_bf16_dparam_global': np.asarray(dp_glob)})
     np.savez_compressed(out, **res)
     print('wrote', out, 'fwd errors', np.round(fwd, 4))
 
@@ -246,8 +248,11 @@ def main():
     if '--wide' in sys.argv:
         # the benchmark's own channel widths (17 * 2^k and 34 * 2^k): whole model + per-block bf16 yardstick
         torch.set_num_threads(os.cpu_count() or 1)
-        model_case(DuckNet, 'ducknet', 17, 2, 128, 13, loss_mod, os.path.join(g, 'ducknet_b17_128.npz'))
+        if '--stages-only' not in sys.argv:
+            model_case(DuckNet, 'ducknet', 17, 2, 128, 13, loss_mod, os.path.join(g, 'ducknet_b17_128.npz'))
         stage_case(DuckNet, 17, 2, 128, 13, os.path.join(g, 'ducknet_b17_128_stages.npz'))
+        if '--stages-only' in sys.argv:
+            return
         model_case(DuckNet, 'ducknet', 34, 2, 96, 14, loss_mod, os.path.join(g, 'ducknet_b34_96.npz'), light=True)
         stage_case(DuckNet, 34, 2, 96, 14, os.path.join(g, 'ducknet_b34_96_stages.npz'), backward=False)
         return
