@@ -19,6 +19,27 @@ int set_error(int code, const char* fmt, ...) {
 }
 void note_conv_engine(int engine) { g_engine = engine; }
 
+// ---- reduction tickets (common.cuh) ----
+static __device__ unsigned int g_tickets[kTicketSlots];        // zero at module load; every slot re-arms itself
+unsigned int* next_ticket() {
+    static std::atomic<unsigned> ctr{0};
+    static std::mutex mu;
+    static unsigned int* base[64] = {nullptr};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    unsigned int* b = base[dev];
+    if (!b) {
+        std::lock_guard<std::mutex> lk(mu);
+        if (!base[dev]) {
+            void* p = nullptr;
+            if (cudaGetSymbolAddress(&p, g_tickets) != cudaSuccess) return nullptr;
+            base[dev] = static_cast<unsigned int*>(p);
+        }
+        b = base[dev];
+    }
+    return b + ctr.fetch_add(1, std::memory_order_relaxed) % kTicketSlots;
+}
+
 // ---- profiler ----
 struct ProfRec { cudaEvent_t a, b; int cls; double bytes, flops; };
 static std::mutex g_mu;

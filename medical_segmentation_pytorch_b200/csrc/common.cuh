@@ -145,24 +145,143 @@ inline cudaStream_t as_stream(void* s) { return reinterpret_cast<cudaStream_t>(s
         else return msx::set_error(MSX_ERR_INVALID, "unknown dtype %d", (int)(dtype)); \
     } while (0)
 
+
+// ---- "the last CTA to arrive finalizes" ------------------------------------------------------------------------
+// Channel reductions (BatchNorm statistics, BN-backward sums) are two-stage: every CTA writes one row of per-channel
+// partials, then somebody folds the rows.  That second stage used to be its own launch (584 of them per DUCK-Net
+// step, 9 us of pure latency each); now every CTA takes a ticket after its row is visible and the CTA that draws the
+// last one does the fold.  Tickets live in a zero-initialised __device__ array of the library (api.cu), one slot per
+// launch handed out round-robin by the host (a slot re-arms itself, so graph replays reuse theirs); two launches could
+// only share a slot while both are in flight if kTicketSlots other reductions were launched in between.
+// No allocation, no memset node, deterministic result (the fold order is fixed).
+constexpr int kTicketSlots = 8192;
+unsigned int* next_ticket();     // api.cu: device address of the next slot on the current device (nullptr on a CUDA error)
+
+// True in every thread of the last of `total` CTAs to call it (all threads of the CTA must call).  `flag`: one int of
+// shared memory.  The caller's global writes made before the call are visible to the last CTA after it.
+__device__ inline bool ticket_is_last(unsigned int* ticket, unsigned int total, int* flag) {
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned int t = atomicAdd(ticket, 1u);
+        const int last = t == total - 1;
+        if (last) *ticket = 0;                  // re-arm for the next launch that is handed this slot
+        *flag = last;
+    }
+    __syncthreads();
+    const bool last = *flag != 0;
+    if (last) __threadfence();
+    return last;
+}
+
+// Fold per-CTA partial rows [nblk][2][cp] (doubles) of channel c: one warp, fixed order.  L2 loads (__ldcg): the rows
+// were written by other CTAs of the same launch.
+__device__ inline void fold_partials(const double* partials, int nblk, int cp, int c, double& s, double& q) {
+    const int lane = threadIdx.x & 31;
+    s = 0.0; q = 0.0;
+    int b = lane;
+    for (; b + 96 < nblk; b += 128) {                           // 8 independent loads in flight
+        double s4[4], q4[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            s4[u] = __ldcg(partials + ((int64_t)(b + 32 * u) * 2 + 0) * cp + c);
+            q4[u] = __ldcg(partials + ((int64_t)(b + 32 * u) * 2 + 1) * cp + c);
+        }
+        s += (s4[0] + s4[1]) + (s4[2] + s4[3]);
+        q += (q4[0] + q4[1]) + (q4[2] + q4[3]);
+    }
+    for (; b < nblk; b += 32) {
+        s += __ldcg(partials + ((int64_t)b * 2 + 0) * cp + c);
+        q += __ldcg(partials + ((int64_t)b * 2 + 1) * cp + c);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        s += __shfl_xor_sync(0xffffffffu, s, o);
+        q += __shfl_xor_sync(0xffffffffu, q, o);
+    }
+}
+
+// What the forward statistics become (nn.BatchNorm2d, training): mean / invstd for this step, running statistics with
+// the unbiased variance, num_batches_tracked.  With `sums` set nothing is finalized: the per-channel [sum, sum of
+// squares] (doubles, [2][cp]) are left there for a cross-rank reduction (SyncBatchNorm) and msx_bn_finalize_sums.
+struct BnFinalize {
+    double* partials;            // [rows][2][cp]
+    unsigned int* ticket;        // nullptr: no in-kernel finalize
+    double* sums;                // nullable
+    float *mean, *invstd, *running_mean, *running_var;
+    long long* nbt;
+    long long count;             // pixels per channel
+    int channels, cp;
+    float eps, momentum;
+};
+
+__device__ inline void bn_finalize_one(const BnFinalize& f, int c, double s, double q) {
+    const double m = s / (double)f.count;
+    double var = q / (double)f.count - m * m;
+    if (var < 0.0) var = 0.0;
+    f.mean[c] = (float)m;
+    f.invstd[c] = (float)(1.0 / sqrt(var + (double)f.eps));
+    if (f.running_mean) {
+        const double unb = f.count > 1 ? var * ((double)f.count / (double)(f.count - 1)) : var;
+        f.running_mean[c] = (float)((1.0 - f.momentum) * (double)f.running_mean[c] + (double)f.momentum * m);
+        f.running_var[c] = (float)((1.0 - f.momentum) * (double)f.running_var[c] + (double)f.momentum * unb);
+    }
+}
+
+// Executed by every thread of the last CTA: warp w handles channels w, w + nwarps, ...
+__device__ inline void bn_finalize_all(const BnFinalize& f, int nblk) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    if (threadIdx.x == 0 && f.nbt && !f.sums) *f.nbt += 1;
+    for (int c = warp; c < f.cp; c += nwarps) {
+        if (c >= f.channels) {
+            if (lane == 0) {
+                if (f.sums) { f.sums[c] = 0.0; f.sums[f.cp + c] = 0.0; }
+                else { f.mean[c] = 0.f; f.invstd[c] = 0.f; }
+            }
+            continue;
+        }
+        double s, q;
+        fold_partials(f.partials, nblk, f.cp, c, s, q);
+        if (lane != 0) continue;
+        if (f.sums) { f.sums[c] = s; f.sums[f.cp + c] = q; }
+        else bn_finalize_one(f, c, s, q);
+    }
+}
+
 // What a gather-form conv kernel does to an accumulator column c before storing it:
 //   v += bias[c] (ConvTranspose2d bias);  v = v * scale[c] + shift[c] (eval-mode BatchNorm folded to an affine);  ReLU.
 // All pointers nullable; columns >= the logical channel count store zeros.
+//   With `stats` the kernel also produces the training-mode BatchNorm statistics of what it stores (sum and sum of
+//   squares per channel of the bf16-rounded outputs) and its last CTA finalizes them: no separate pass over y.
 struct ConvEpilogue {
     const float* bias;
     const float* scale;
     const float* shift;
     int relu;
+    int stats;                   // 0 / 1: bnf is valid
+    BnFinalize bnf;
 };
+inline ConvEpilogue conv_epilogue(const float* bias, const float* scale = nullptr, const float* shift = nullptr, int relu = 0) {
+    ConvEpilogue e;
+    e.bias = bias; e.scale = scale; e.shift = shift; e.relu = relu; e.stats = 0;
+    e.bnf = BnFinalize{};
+    return e;
+}
 
 // ---- internal cross-file entry points -------------------------------------------------------
 // channel-reduction partial sums: [nblk][2][cp] doubles
 size_t bn_partials_bytes(int channels);
-int bn_stats_launch(int dtype, const void* x, int ld, int64_t pixels, int channels, double* partials,
+int bn_finalize_args(BnFinalize* f, double* partials, int channels, int64_t count, float eps, float momentum, float* mean,
+                     float* invstd, float* running_mean, float* running_var, int64_t* nbt, double* sums);
+int bn_stats_launch(int dtype, const void* x, int ld, int64_t pixels, int channels, double* partials, const BnFinalize* fin,
                     int* nblk_out, cudaStream_t st);
-int bn_finalize_launch(const double* partials, int nblk, int channels, int64_t count, float eps, float momentum,
-                       float* mean, float* invstd, float* running_mean, float* running_var,
-                       int64_t* num_batches_tracked, cudaStream_t st);
+int bn_finalize_sums_launch(const double* sums, const BnFinalize& f, cudaStream_t st);
+int bn_bwd_reduce_launch(int dtype, const void* x, int ldx, const void* dz, int lddz, int64_t pixels, int channels,
+                         const float* gamma, const float* beta, const float* mean, const float* invstd, int flags,
+                         float* dgamma, float* dbeta, double* partials, float* c1, float* c2, double* sums, cudaStream_t st);
+int bn_bwd_apply_launch(int dtype, const void* x, int ldx, const void* dz, int lddz, int64_t pixels, int channels,
+                        const float* gamma, const float* beta, const float* mean, const float* invstd, int flags,
+                        const float* c1, const float* c2, void* dx, int lddx, cudaStream_t st);
 int bn_eval_stats_launch(int channels, const float* running_mean, const float* running_var, float eps,
                          float* mean, float* invstd, cudaStream_t st);
 // eval-mode BN as y*scale + shift (scale = gamma*invstd, shift = beta - mean*scale [+ bias*scale]); arrays of round_up(channels, 8)

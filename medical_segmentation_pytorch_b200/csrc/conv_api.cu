@@ -42,7 +42,7 @@ static int conv_gather(const msx_conv_desc* d, bool fwd_pass, const void* src, c
 }
 static int conv_gather(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
                        void* dst, cudaStream_t st) {
-    return conv_gather(d, fwd_pass, src, packed, ConvEpilogue{bias, nullptr, nullptr, 0}, dst, st);
+    return conv_gather(d, fwd_pass, src, packed, conv_epilogue(bias), dst, st);
 }
 
 static size_t ws_conv_bytes(const msx_conv_desc* d) {
@@ -137,14 +137,14 @@ int msx_conv_bn_act_fwd(const msx_conv_desc* d, const void* x, const float* w_ma
         MSX_TRY(bn_eval_affine_launch(d->cout, running_mean, running_var, eps, gamma, beta, bias, save_mean, save_invstd, scale, shift, st));
         msx_conv_desc dz = *d;
         dz.ldy = ldz;
-        return conv_gather(&dz, true, x, w_packed, ConvEpilogue{nullptr, scale, shift, relu}, z, st);
+        return conv_gather(&dz, true, x, w_packed, conv_epilogue(nullptr, scale, shift, relu), z, st);
     }
     MSX_TRY(conv_gather(d, true, x, w_packed, bias, y_raw, st));
     if (training) {
-        int nblk = 0;
-        MSX_TRY(bn_stats_launch(d->dtype, y_raw, d->ldy, pixels, d->cout, static_cast<double*>(ws), &nblk, st));
-        MSX_TRY(bn_finalize_launch(static_cast<double*>(ws), nblk, d->cout, pixels, eps, momentum, save_mean, save_invstd,
-                                   running_mean, running_var, num_batches_tracked, st));
+        BnFinalize fin;
+        MSX_TRY(bn_finalize_args(&fin, static_cast<double*>(ws), d->cout, pixels, eps, momentum, save_mean, save_invstd, running_mean,
+                                 running_var, num_batches_tracked, nullptr));
+        MSX_TRY(bn_stats_launch(d->dtype, y_raw, d->ldy, pixels, d->cout, static_cast<double*>(ws), &fin, nullptr, st));
     } else {
         MSX_TRY(bn_eval_stats_launch(d->cout, running_mean, running_var, eps, save_mean, save_invstd, st));
     }

@@ -77,9 +77,10 @@ inline int stream_grid(int64_t pixels, int lanes) {
 // ---- statistics ---------------------------------------------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(256) bn_stats_kernel(const T* __restrict__ x, int ld, int64_t pixels, int cp, int vch,
-                                                       double* __restrict__ partials) {
+                                                       double* partials, const BnFinalize fin) {
     constexpr int VEC = Vec<T>::N;
     __shared__ double sh[2 * VEC * 256];
+    __shared__ int last_flag;
     const ChanThread t = chan_thread<VEC>(cp, vch);
     double acc[2 * VEC];
 #pragma unroll
@@ -119,52 +120,16 @@ __global__ void __launch_bounds__(256) bn_stats_kernel(const T* __restrict__ x, 
             partials[((int64_t)blockIdx.x * 2 + 1) * cp + t.c0 + j] = acc[VEC + j];
         }
     }
+    if (fin.ticket && ticket_is_last(fin.ticket, gridDim.x * gridDim.y, &last_flag)) bn_finalize_all(fin, gridDim.x);
 }
 
-// One warp per channel: lanes stride over the (<= 592) per-CTA partials, then shuffle-reduce.
-__device__ inline void reduce_partials(const double* __restrict__ partials, int nblk, int cp, int c, double& s, double& q) {
-    const int lane = threadIdx.x & 31;
-    s = 0.0; q = 0.0;
-    int b = lane;
-    for (; b + 96 < nblk; b += 128) {                           // 8 independent loads in flight
-        double s4[4], q4[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            s4[u] = partials[((int64_t)(b + 32 * u) * 2 + 0) * cp + c];
-            q4[u] = partials[((int64_t)(b + 32 * u) * 2 + 1) * cp + c];
-        }
-        s += (s4[0] + s4[1]) + (s4[2] + s4[3]);
-        q += (q4[0] + q4[1]) + (q4[2] + q4[3]);
-    }
-    for (; b < nblk; b += 32) {
-        s += partials[((int64_t)b * 2 + 0) * cp + c];
-        q += partials[((int64_t)b * 2 + 1) * cp + c];
-    }
-    s = warp_sum(s);
-    q = warp_sum(q);
-}
-
-__global__ void bn_finalize_kernel(const double* __restrict__ partials, int nblk, int cp, int channels, int64_t count,
-                                   float eps, float momentum, float* __restrict__ mean, float* __restrict__ invstd,
-                                   float* running_mean, float* running_var, int64_t* nbt) {
-    const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int lane = threadIdx.x & 31;
-    if (c == 0 && lane == 0 && nbt) *nbt += 1;
-    if (c >= cp) return;
-    if (c >= channels) { if (lane == 0) { mean[c] = 0.f; invstd[c] = 0.f; } return; }
-    double s, q;
-    reduce_partials(partials, nblk, cp, c, s, q);
-    if (lane != 0) return;
-    const double m = s / (double)count;
-    double var = q / (double)count - m * m;
-    if (var < 0.0) var = 0.0;
-    mean[c] = (float)m;
-    invstd[c] = (float)(1.0 / sqrt(var + (double)eps));
-    if (running_mean) {
-        const double unb = count > 1 ? var * ((double)count / (double)(count - 1)) : var;
-        running_mean[c] = (float)((1.0 - momentum) * (double)running_mean[c] + (double)momentum * m);
-        running_var[c] = (float)((1.0 - momentum) * (double)running_var[c] + (double)momentum * unb);
-    }
+// SyncBatchNorm: per-channel [sum, sum of squares] (doubles, already reduced over ranks) -> mean / invstd / running stats
+__global__ void bn_finalize_sums_kernel(const double* __restrict__ sums, const BnFinalize f) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c == 0 && f.nbt) *f.nbt += 1;
+    if (c >= f.cp) return;
+    if (c >= f.channels) { f.mean[c] = 0.f; f.invstd[c] = 0.f; return; }
+    bn_finalize_one(f, c, sums[c], sums[f.cp + c]);
 }
 
 __global__ void bn_eval_stats_kernel(int cp, int channels, const float* rm, const float* rv, float eps,
@@ -237,15 +202,56 @@ __global__ void __launch_bounds__(256) bn_apply_kernel(const T* __restrict__ x, 
 }
 
 // ---- backward -----------------------------------------------------------------------------
+// What the backward sums become: dbeta = sum g, dgamma = sum g*xhat, and the two per-channel coefficients of
+// dx = gamma*invstd*(g - c1 - xhat*c2): c1 = sum g / count, c2 = sum g*xhat / count (both 0 in eval mode, where mean and
+// invstd are constants).  With `sums` (SyncBatchNorm) the two sums also go to [2][cp] doubles for the cross-rank
+// reduction that msx_bn_bwd_coeffs_from_sums turns into c1 / c2.
+struct BnBwdFinalize {
+    unsigned int* ticket;
+    double* sums;
+    float *dgamma, *dbeta, *c1, *c2;
+    long long count;
+    int channels, cp, eval_mode;
+};
+
+__device__ inline void bn_bwd_finalize_all(const BnBwdFinalize& f, const double* partials, int nblk) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    for (int c = warp; c < f.cp; c += nwarps) {
+        if (c >= f.channels) {
+            if (lane == 0) {
+                if (f.sums) { f.sums[c] = 0.0; f.sums[f.cp + c] = 0.0; }
+                f.c1[c] = 0.f; f.c2[c] = 0.f;
+            }
+            continue;
+        }
+        double s, q;
+        fold_partials(partials, nblk, f.cp, c, s, q);
+        if (lane != 0) continue;
+        if (f.dbeta) f.dbeta[c] = (float)s;
+        if (f.dgamma) f.dgamma[c] = (float)q;
+        if (f.sums) { f.sums[c] = s; f.sums[f.cp + c] = q; }
+        f.c1[c] = f.eval_mode ? 0.f : (float)(s / (double)f.count);
+        f.c2[c] = f.eval_mode ? 0.f : (float)(q / (double)f.count);
+    }
+}
+
+__global__ void bn_bwd_coeffs_kernel(const double* __restrict__ sums, int cp, int channels, double count, float* c1, float* c2) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= cp) return;
+    c1[c] = c < channels ? (float)(sums[c] / count) : 0.f;
+    c2[c] = c < channels ? (float)(sums[cp + c] / count) : 0.f;
+}
+
 // g = dz * [relu mask];  partial sums of g and g*xhat.
 template <typename T>
 __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const T* __restrict__ x, int ldx, const T* __restrict__ dz, int lddz,
                                                             int64_t pixels, int cp, int vch, int channels,
                                                             const float* __restrict__ mean, const float* __restrict__ invstd,
                                                             const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                            int relu, double* __restrict__ partials) {
+                                                            int relu, double* partials, const BnBwdFinalize fin) {
     constexpr int VEC = Vec<T>::N;
     __shared__ double shm[2 * VEC * 256];
+    __shared__ int last_flag;
     const ChanThread t = chan_thread<VEC>(cp, vch);
     float mu[VEC], is[VEC], ga[VEC], be[VEC];
     double acc[2 * VEC];
@@ -304,23 +310,7 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const T* __restrict_
             partials[((int64_t)blockIdx.x * 2 + 1) * cp + t.c0 + j] = acc[VEC + j];
         }
     }
-}
-
-__global__ void bn_bwd_finalize_kernel(const double* __restrict__ partials, int nblk, int cp, int channels, int64_t count,
-                                       float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                       float* __restrict__ c1, float* __restrict__ c2, int eval_mode) {
-    const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int lane = threadIdx.x & 31;
-    if (c >= cp) return;
-    if (c >= channels) { if (lane == 0) { c1[c] = 0.f; c2[c] = 0.f; } return; }
-    double s, q;
-    reduce_partials(partials, nblk, cp, c, s, q);
-    if (lane != 0) return;
-    if (dbeta) dbeta[c] = (float)s;
-    if (dgamma) dgamma[c] = (float)q;
-    // eval mode: mean / invstd are constants (running statistics), so dx = gamma * invstd * g without the batch terms
-    c1[c] = eval_mode ? 0.f : (float)(s / (double)count);
-    c2[c] = eval_mode ? 0.f : (float)(q / (double)count);
+    if (fin.ticket && ticket_is_last(fin.ticket, gridDim.x * gridDim.y, &last_flag)) bn_bwd_finalize_all(fin, partials, gridDim.x);
 }
 
 template <typename T>
@@ -383,11 +373,12 @@ struct SumArgs {
 };
 template <typename T, bool STATS>
 __global__ void __launch_bounds__(256) sum_stats_kernel(SumArgs a, int up2x, int H, int W, T* __restrict__ s, int lds,
-                                                        int64_t pixels, int cp, int vch, double* __restrict__ partials,
+                                                        int64_t pixels, int cp, int vch, double* partials,
                                                         const float* __restrict__ scale = nullptr, const float* __restrict__ shift = nullptr,
-                                                        int relu = 0) {
+                                                        int relu = 0, const BnFinalize fin = BnFinalize{}) {
     constexpr int VEC = Vec<T>::N;
     __shared__ double sh[STATS ? 2 * VEC * 256 : 1];
+    __shared__ int last_flag;
     const ChanThread t = chan_thread<VEC>(cp, vch);
     // inference: eval-mode BN affine (+ReLU) applied to the sum before it is stored (STATS == false only)
     float asc[VEC], ash[VEC];
@@ -466,6 +457,7 @@ __global__ void __launch_bounds__(256) sum_stats_kernel(SumArgs a, int up2x, int
             partials[((int64_t)blockIdx.x * 2 + 1) * cp + t.c0 + j] = acc[VEC + j];
         }
     }
+    if (partials && fin.ticket && ticket_is_last(fin.ticket, gridDim.x * gridDim.y, &last_flag)) bn_finalize_all(fin, gridDim.x);
 }
 
 template <typename T>
@@ -597,7 +589,7 @@ __global__ void channel_sum_finalize_kernel(const double* __restrict__ partials,
     const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (c >= channels) return;
     double s, q;
-    reduce_partials(partials, nblk, cp, c, s, q);
+    fold_partials(partials, nblk, cp, c, s, q);
     if ((threadIdx.x & 31) == 0) out[c] = (float)s;
 }
 
@@ -615,25 +607,37 @@ size_t bn_partials_bytes(int channels) {
     return (size_t)kMaxPartialBlocks * 2 * cp * sizeof(double) + 2 * (size_t)cp * sizeof(float) + 256;
 }
 
-int bn_stats_launch(int dtype, const void* x, int ld, int64_t pixels, int channels, double* partials, int* nblk_out,
-                    cudaStream_t st) {
+int bn_finalize_args(BnFinalize* f, double* partials, int channels, int64_t count, float eps, float momentum, float* mean,
+                     float* invstd, float* running_mean, float* running_var, int64_t* nbt, double* sums) {
+    f->partials = partials;
+    f->ticket = next_ticket();
+    if (!f->ticket) return set_error(MSX_ERR_CUDA, "reduction ticket array unavailable (cudaGetSymbolAddress failed)");
+    f->sums = sums;
+    f->mean = mean; f->invstd = invstd; f->running_mean = running_mean; f->running_var = running_var;
+    f->nbt = reinterpret_cast<long long*>(nbt);
+    f->count = count;
+    f->channels = channels; f->cp = round_up(channels, 8);
+    f->eps = eps; f->momentum = momentum;
+    return MSX_OK;
+}
+
+// fin == nullptr: per-CTA partial rows only (nblk_out rows); otherwise the launch's last CTA folds and finalizes them
+int bn_stats_launch(int dtype, const void* x, int ld, int64_t pixels, int channels, double* partials, const BnFinalize* fin,
+                    int* nblk_out, cudaStream_t st) {
     MSX_TRY(check_ld(ld, channels, "bn_stats"));
+    BnFinalize f = fin ? *fin : BnFinalize{};
     MSX_DISPATCH_DTYPE(dtype, T, {
         const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
         const int g = reduce_grid(pixels, c.lanes);
-        { ProfScope ps__(K_BN_STATS, st, (double)pixels * channels * (double)sizeof(T), 0); bn_stats_kernel<T><<<dim3(g, c.nchunk), 256, 0, st>>>(static_cast<const T*>(x), ld, pixels, c.cp, c.vch, partials); }
-        *nblk_out = g;
+        { ProfScope ps__(K_BN_STATS, st, (double)pixels * channels * (double)sizeof(T), 0); bn_stats_kernel<T><<<dim3(g, c.nchunk), 256, 0, st>>>(static_cast<const T*>(x), ld, pixels, c.cp, c.vch, partials, f); }
+        if (nblk_out) *nblk_out = g;
     });
     MSX_LAUNCH_CHECK();
     return MSX_OK;
 }
 
-int bn_finalize_launch(const double* partials, int nblk, int channels, int64_t count, float eps, float momentum,
-                       float* mean, float* invstd, float* running_mean, float* running_var, int64_t* nbt,
-                       cudaStream_t st) {
-    const int cp = round_up(channels, 8);
-    { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_finalize_kernel<<<(cp * 32 + 127) / 128, 128, 0, st>>>(partials, nblk, cp, channels, count, eps, momentum, mean, invstd,
-                                                         running_mean, running_var, nbt); }
+int bn_finalize_sums_launch(const double* sums, const BnFinalize& f, cudaStream_t st) {
+    { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_finalize_sums_kernel<<<(f.cp + 127) / 128, 128, 0, st>>>(sums, f); }
     MSX_LAUNCH_CHECK();
     return MSX_OK;
 }
@@ -668,24 +672,36 @@ int bn_apply_launch(int dtype, const void* x, int ldx, void* z, int ldz, int64_t
     return MSX_OK;
 }
 
-int bn_bwd_launch(int dtype, const void* x, int ldx, const void* dz, int lddz, int64_t pixels, int channels,
-                  const float* gamma, const float* beta, const float* mean, const float* invstd, int flags,
-                  void* dx, int lddx, float* dgamma, float* dbeta, void* ws, size_t ws_bytes, cudaStream_t st) {
-    const int relu = flags & MSX_BN_RELU, eval_mode = (flags & MSX_BN_EVAL) ? 1 : 0;
+// The two halves of the BatchNorm(+ReLU) backward.  reduce: dgamma / dbeta and the coefficients c1, c2 (fp32[cp] each, in
+// the caller's scratch) by the launch's last CTA; sums (nullable, [2][cp] doubles): the raw sums for SyncBatchNorm.
+int bn_bwd_reduce_launch(int dtype, const void* x, int ldx, const void* dz, int lddz, int64_t pixels, int channels,
+                         const float* gamma, const float* beta, const float* mean, const float* invstd, int flags,
+                         float* dgamma, float* dbeta, double* partials, float* c1, float* c2, double* sums, cudaStream_t st) {
+    const int relu = flags & MSX_BN_RELU;
     MSX_TRY(check_ld(ldx, channels, "bn_bwd x"));
     MSX_TRY(check_ld(lddz, channels, "bn_bwd dz"));
-    MSX_TRY(check_ld(lddx, channels, "bn_bwd dx"));
-    if (ws_bytes < bn_partials_bytes(channels)) return set_error(MSX_ERR_WORKSPACE, "bn_bwd: workspace %zu < %zu", ws_bytes, bn_partials_bytes(channels));
-    const int cp = round_up(channels, 8);
-    double* partials = static_cast<double*>(ws);
-    float* c1 = reinterpret_cast<float*>(partials + (size_t)kMaxPartialBlocks * 2 * cp);
-    float* c2 = c1 + cp;
+    BnBwdFinalize f;
+    f.ticket = next_ticket();
+    if (!f.ticket) return set_error(MSX_ERR_CUDA, "reduction ticket array unavailable (cudaGetSymbolAddress failed)");
+    f.sums = sums; f.dgamma = dgamma; f.dbeta = dbeta; f.c1 = c1; f.c2 = c2;
+    f.count = pixels; f.channels = channels; f.cp = round_up(channels, 8); f.eval_mode = (flags & MSX_BN_EVAL) ? 1 : 0;
     MSX_DISPATCH_DTYPE(dtype, T, {
         const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
         const int g = reduce_grid(pixels, c.lanes);
         { ProfScope ps__(K_BN_BWD_REDUCE, st, 2.0 * (double)pixels * channels * (double)sizeof(T), 0); bn_bwd_reduce_kernel<T><<<dim3(g, c.nchunk), 256, 0, st>>>(static_cast<const T*>(x), ldx, static_cast<const T*>(dz), lddz,
-                                                                 pixels, c.cp, c.vch, channels, mean, invstd, gamma, beta, relu, partials); }
-        { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_bwd_finalize_kernel<<<(cp * 32 + 127) / 128, 128, 0, st>>>(partials, g, cp, channels, pixels, dgamma, dbeta, c1, c2, eval_mode); }
+                                                                 pixels, c.cp, c.vch, channels, mean, invstd, gamma, beta, relu, partials, f); }
+    });
+    MSX_LAUNCH_CHECK();
+    return MSX_OK;
+}
+
+int bn_bwd_apply_launch(int dtype, const void* x, int ldx, const void* dz, int lddz, int64_t pixels, int channels,
+                        const float* gamma, const float* beta, const float* mean, const float* invstd, int flags,
+                        const float* c1, const float* c2, void* dx, int lddx, cudaStream_t st) {
+    const int relu = flags & MSX_BN_RELU;
+    MSX_TRY(check_ld(lddx, channels, "bn_bwd dx"));
+    MSX_DISPATCH_DTYPE(dtype, T, {
+        const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
         { ProfScope ps__(K_BN_BWD_APPLY, st, 3.0 * (double)pixels * channels * (double)sizeof(T), 0); bn_bwd_apply_kernel<T><<<dim3(stream_grid(pixels, c.lanes), c.nchunk), 256, 0, st>>>(
             static_cast<const T*>(x), ldx, static_cast<const T*>(dz), lddz, static_cast<T*>(dx), lddx, pixels, c.cp, c.vch, channels,
             mean, invstd, gamma, beta, c1, c2, relu); }
@@ -694,11 +710,23 @@ int bn_bwd_launch(int dtype, const void* x, int ldx, const void* dz, int lddz, i
     return MSX_OK;
 }
 
+int bn_bwd_launch(int dtype, const void* x, int ldx, const void* dz, int lddz, int64_t pixels, int channels,
+                  const float* gamma, const float* beta, const float* mean, const float* invstd, int flags,
+                  void* dx, int lddx, float* dgamma, float* dbeta, void* ws, size_t ws_bytes, cudaStream_t st) {
+    if (ws_bytes < bn_partials_bytes(channels)) return set_error(MSX_ERR_WORKSPACE, "bn_bwd: workspace %zu < %zu", ws_bytes, bn_partials_bytes(channels));
+    const int cp = round_up(channels, 8);
+    double* partials = static_cast<double*>(ws);
+    float* c1 = reinterpret_cast<float*>(partials + (size_t)kMaxPartialBlocks * 2 * cp);
+    float* c2 = c1 + cp;
+    MSX_TRY(bn_bwd_reduce_launch(dtype, x, ldx, dz, lddz, pixels, channels, gamma, beta, mean, invstd, flags, dgamma, dbeta, partials, c1, c2, nullptr, st));
+    return bn_bwd_apply_launch(dtype, x, ldx, dz, lddz, pixels, channels, gamma, beta, mean, invstd, flags, c1, c2, dx, lddx, st);
+}
+
 int channel_sum_launch(int dtype, const void* x, int ld, int64_t pixels, int channels, float* out, void* ws,
                        size_t ws_bytes, cudaStream_t st) {
     if (ws_bytes < bn_partials_bytes(channels)) return set_error(MSX_ERR_WORKSPACE, "channel_sum: workspace too small");
     int nblk = 0;
-    MSX_TRY(bn_stats_launch(dtype, x, ld, pixels, channels, static_cast<double*>(ws), &nblk, st));
+    MSX_TRY(bn_stats_launch(dtype, x, ld, pixels, channels, static_cast<double*>(ws), nullptr, &nblk, st));
     { ProfScope ps__(K_MISC, st, 0, 0); channel_sum_finalize_kernel<<<(channels * 32 + 127) / 128, 128, 0, st>>>(static_cast<double*>(ws), nblk, round_up(channels, 8), channels, out); }
     MSX_LAUNCH_CHECK();
     return MSX_OK;
@@ -729,6 +757,10 @@ int msx_sum_bn_act_fwd(int dtype, int n_in, const void* const* host_xs, const in
     int ldsrc = host_ldxs[0];
     int nblk = 0;
     const bool need_sum = n_in > 1 || up2x_first;
+    BnFinalize fin{};                 // training: the statistics kernel's last CTA finalizes (mean, invstd, running stats)
+    if (training)
+        MSX_TRY(bn_finalize_args(&fin, partials, channels, pixels, eps, momentum, save_mean, save_invstd, running_mean, running_var,
+                                 num_batches_tracked, nullptr));
     if (need_sum && !training && s == nullptr) {
         // inference: one kernel sums the inputs, applies the eval-mode BN affine and the ReLU and writes z
         MSX_REQUIRE(running_mean && running_var, "sum_bn_act: eval mode needs running statistics");
@@ -765,18 +797,15 @@ int msx_sum_bn_act_fwd(int dtype, int n_in, const void* const* host_xs, const in
             const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
             nblk = reduce_grid(pixels, c.lanes);
             { ProfScope ps__(K_SUM, st, (double)pixels * channels * (double)sizeof(T) * (n_in + 1.0), 0); sum_stats_kernel<T, true><<<dim3(nblk, c.nchunk), 256, 0, st>>>(a, up2x_first, h, w, static_cast<T*>(s), lds, pixels, c.cp, c.vch,
-                                                                     training ? partials : nullptr); }
+                                                                     training ? partials : nullptr, nullptr, nullptr, 0, fin); }
         });
         MSX_LAUNCH_CHECK();
         src = s;
         ldsrc = lds;
     } else if (training) {
-        MSX_TRY(bn_stats_launch(dtype, src, ldsrc, pixels, channels, partials, &nblk, st));
+        MSX_TRY(bn_stats_launch(dtype, src, ldsrc, pixels, channels, partials, &fin, &nblk, st));
     }
-    if (training)
-        MSX_TRY(bn_finalize_launch(partials, nblk, channels, pixels, eps, momentum, save_mean, save_invstd, running_mean,
-                                   running_var, num_batches_tracked, st));
-    else
+    if (!training)
         MSX_TRY(bn_eval_stats_launch(channels, running_mean, running_var, eps, save_mean, save_invstd, st));
     return bn_apply_launch(dtype, src, ldsrc, z, ldz, pixels, channels, save_mean, save_invstd, gamma, beta, relu, st);
 }
