@@ -1,4 +1,6 @@
 // extern "C" convolution entry points: engine selection + the ConvBNAct composites.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace msx {
@@ -18,7 +20,7 @@ int conv_wgrad_simt(const msx_conv_desc* d, const void* x, const void* dy, float
 bool conv_tc_supported(const msx_conv_desc* d, bool fwd_pass);
 bool conv_tc_gather_supported(const msx_conv_desc* d, bool fwd_pass);
 int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const ConvEpilogue& ep,
-                   void* dst, cudaStream_t st);
+                   void* dst, cudaStream_t st, bool* stats_fused);
 
 size_t conv_wgrad_tc_ws_bytes(const msx_conv_desc* d);
 int conv_wgrad_tc(const msx_conv_desc* d, const void* x, const void* dy, float* dw, void* ws, size_t ws_bytes, cudaStream_t st);
@@ -33,9 +35,10 @@ static int conv_wgrad(const msx_conv_desc* d, const void* x, const void* dy, flo
 }
 
 static int conv_gather(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const ConvEpilogue& ep,
-                       void* dst, cudaStream_t st) {
+                       void* dst, cudaStream_t st, bool* stats_fused = nullptr) {
+    if (stats_fused) *stats_fused = false;
     const bool want_tc = d->engine == MSX_ENGINE_TCGEN05 || (d->engine == MSX_ENGINE_AUTO && d->dtype == MSX_BF16);
-    if (want_tc && conv_tc_gather_supported(d, fwd_pass)) return conv_gather_tc(d, fwd_pass, src, packed, ep, dst, st);
+    if (want_tc && conv_tc_gather_supported(d, fwd_pass)) return conv_gather_tc(d, fwd_pass, src, packed, ep, dst, st, stats_fused);
     if (d->engine == MSX_ENGINE_TCGEN05)
         return set_error(MSX_ERR_UNSUPPORTED, "conv: tcgen05 engine requested for a shape/dtype it does not support");
     return conv_gather_simt(d, fwd_pass, src, packed, ep, dst, st);
@@ -43,6 +46,12 @@ static int conv_gather(const msx_conv_desc* d, bool fwd_pass, const void* src, c
 static int conv_gather(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
                        void* dst, cudaStream_t st) {
     return conv_gather(d, fwd_pass, src, packed, conv_epilogue(bias), dst, st);
+}
+
+// MSX_FUSED_STATS=0: statistics by the stand-alone pass everywhere (measurement / bisecting switch, read once)
+static bool fused_stats_enabled() {
+    static const bool on = [] { const char* e = getenv("MSX_FUSED_STATS"); return !(e && atoi(e) == 0); }();
+    return on;
 }
 
 static size_t ws_conv_bytes(const msx_conv_desc* d) {
@@ -139,13 +148,18 @@ int msx_conv_bn_act_fwd(const msx_conv_desc* d, const void* x, const float* w_ma
         dz.ldy = ldz;
         return conv_gather(&dz, true, x, w_packed, conv_epilogue(nullptr, scale, shift, relu), z, st);
     }
-    MSX_TRY(conv_gather(d, true, x, w_packed, bias, y_raw, st));
     if (training) {
-        BnFinalize fin;
-        MSX_TRY(bn_finalize_args(&fin, static_cast<double*>(ws), d->cout, pixels, eps, momentum, save_mean, save_invstd, running_mean,
+        // batch statistics come out of the convolution's own epilogue (tcgen05 kernels: per-channel sums of what is stored,
+        // finalized by the launch's last CTA); engines / geometries without that run one statistics pass over y_raw
+        ConvEpilogue ep = conv_epilogue(bias);
+        MSX_TRY(bn_finalize_args(&ep.bnf, static_cast<double*>(ws), d->cout, pixels, eps, momentum, save_mean, save_invstd, running_mean,
                                  running_var, num_batches_tracked, nullptr));
-        MSX_TRY(bn_stats_launch(d->dtype, y_raw, d->ldy, pixels, d->cout, static_cast<double*>(ws), &fin, nullptr, st));
+        ep.stats = fused_stats_enabled() ? 1 : 0;
+        bool fused = false;
+        MSX_TRY(conv_gather(d, true, x, w_packed, ep, y_raw, st, &fused));
+        if (!fused) MSX_TRY(bn_stats_launch(d->dtype, y_raw, d->ldy, pixels, d->cout, static_cast<double*>(ws), &ep.bnf, nullptr, st));
     } else {
+        MSX_TRY(conv_gather(d, true, x, w_packed, bias, y_raw, st));
         MSX_TRY(bn_eval_stats_launch(d->cout, running_mean, running_var, eps, save_mean, save_invstd, st));
     }
     return bn_apply_launch(d->dtype, y_raw, d->ldy, z, ldz, pixels, d->cout, save_mean, save_invstd, gamma, beta, relu, st);

@@ -86,6 +86,91 @@ __device__ __forceinline__ void epilogue_cols(uint32_t (&v)[NV], int col0, int N
     }
 }
 
+__device__ __forceinline__ uint32_t pack_bf16(uint32_t a, uint32_t b) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(a), __uint_as_float(b));
+    return *reinterpret_cast<uint32_t*>(&h);
+}
+
+// Column sums over the 32 lanes of a warp, one accumulator row per lane: on return lane l holds the sum over all lanes of
+// v[l] (NV == 32) or of v[l & 15] (NV == 16).  Transpose-reduce: each step halves the columns a lane is responsible for,
+// 31 shuffles in total instead of 5 per column.  v is destroyed.
+template <int N>
+__device__ __forceinline__ void colsum_step(float* v, int lane) {
+    const bool up = (lane & N) != 0;
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        const float keep = up ? v[i + N] : v[i];
+        const float send = up ? v[i] : v[i + N];
+        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, N);
+    }
+}
+template <int NV>
+__device__ __forceinline__ float warp_colsum(float (&v)[NV], int lane) {
+    if (NV == 32) colsum_step<16>(v, lane);
+    else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] += __shfl_xor_sync(0xffffffffu, v[i], 16);
+    }
+    colsum_step<8>(v, lane);
+    colsum_step<4>(v, lane);
+    colsum_step<2>(v, lane);
+    colsum_step<1>(v, lane);
+    return v[0];
+}
+
+// One chunk of NV accumulator columns of one pixel row (this thread's): bias / affine / ReLU, bf16 pack, 16 B stores, and -
+// with ep.stats - the training-mode BatchNorm statistics of exactly what was stored (the bf16-rounded values, so that the
+// apply and backward passes, which re-read y, see the same numbers): per-column sums over the warp's 32 pixels in fp32,
+// then a running double per (warp, column) in shared memory (stat_s / stat_q point at this chunk's column 0).
+template <int NV>
+__device__ __forceinline__ void epilogue_chunk(uint32_t (&v)[NV], int col0, int cols_left, bool valid, bf16* out, int Nc,
+                                               const ConvEpilogue& ep, double* stat_s, double* stat_q, int lane) {
+    epilogue_cols<NV>(v, col0, Nc, ep);
+    uint32_t pk[NV / 2];
+#pragma unroll
+    for (int j = 0; j < NV / 2; ++j) pk[j] = pack_bf16(v[2 * j], v[2 * j + 1]);
+    if (valid) {
+#pragma unroll
+        for (int q = 0; q < NV / 8; ++q)
+            if (8 * q < cols_left)
+                *reinterpret_cast<uint4*>(out + 8 * q) = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+    }
+    if (ep.stats) {
+        float a[NV];
+#pragma unroll
+        for (int j = 0; j < NV / 2; ++j) {
+            a[2 * j] = valid ? __uint_as_float(pk[j] << 16) : 0.f;
+            a[2 * j + 1] = valid ? __uint_as_float(pk[j] & 0xffff0000u) : 0.f;
+        }
+        const float s = warp_colsum<NV>(a, lane);
+#pragma unroll
+        for (int j = 0; j < NV / 2; ++j) {
+            const float lo = valid ? __uint_as_float(pk[j] << 16) : 0.f, hi = valid ? __uint_as_float(pk[j] & 0xffff0000u) : 0.f;
+            a[2 * j] = lo * lo;
+            a[2 * j + 1] = hi * hi;
+        }
+        const float q = warp_colsum<NV>(a, lane);
+        if (NV == 32 || lane < 16) {
+            stat_s[lane] += (double)s;
+            stat_q[lane] += (double)q;
+        }
+    }
+}
+
+// After every role of the CTA is done: fold the 8 epilogue warps' running sums into this CTA's row of partials; the last
+// CTA of the launch to get here folds the rows and finalizes (mean, invstd, running statistics).  All threads call.
+__device__ __forceinline__ void stats_tail(const ConvEpilogue& ep, double* sstat, int nca, int* flag) {
+    const BnFinalize& f = ep.bnf;
+    for (int c = threadIdx.x; c < f.cp; c += blockDim.x) {
+        double s = 0.0, q = 0.0;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) { s += sstat[(w * 2 + 0) * nca + c]; q += sstat[(w * 2 + 1) * nca + c]; }
+        f.partials[((int64_t)blockIdx.x * 2 + 0) * f.cp + c] = s;
+        f.partials[((int64_t)blockIdx.x * 2 + 1) * f.cp + c] = q;
+    }
+    if (ticket_is_last(f.ticket, gridDim.x, flag)) bn_finalize_all(f, gridDim.x);
+}
+
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
 }
@@ -176,10 +261,6 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
           "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
         : "r"(taddr));
 }
-__device__ __forceinline__ uint32_t pack_bf16(uint32_t a, uint32_t b) {
-    __nv_bfloat162 h = __floats2bfloat162_rn(__uint_as_float(a), __uint_as_float(b));
-    return *reinterpret_cast<uint32_t*>(&h);
-}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // K-major operand descriptor for a tile of rows x (64|32) bf16, rows `row_bytes` apart, 8-row swizzle
@@ -200,6 +281,12 @@ conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CU
     const uint32_t bar_tfull = bars + 16 * kMaxStages, bar_tempty = bar_tfull + 16;
     const uint32_t tmem_slot = bar_tempty + 16;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // fused BatchNorm statistics: [8 epilogue warps][sum, sum of squares][nca columns] running doubles, then one flag
+    const int nca = (p.ncp + 31) & ~31;
+    double* sstat = reinterpret_cast<double*>(smem_raw + (tmem_slot + 16 - smem_u32(smem_raw)));
+    int* sflag = reinterpret_cast<int*>(sstat + 16 * nca);
+    if (ep.stats)
+        for (int i = threadIdx.x; i < 16 * nca; i += blockDim.x) sstat[i] = 0.0;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < p.stages; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, 1); }
@@ -299,34 +386,20 @@ conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CU
             bf16* out = dst + ((int64_t)(img * p.Hd + y * p.dmul + p.da) * p.Wd + x * p.dmul + p.db) * p.ldd + n0;
             mbar_wait(bar_tfull + 8 * grp, (it >> 1) & 1);
             tc_fence_after();
+            double* ws_s = sstat + ((warp - 2) * 2 + 0) * nca + n0;       // stats need n_tiles == 1 (n0 == 0): the launcher guarantees it
+            double* ws_q = sstat + ((warp - 2) * 2 + 1) * nca + n0;
             int c0 = 0;
             for (; c0 < ncols && ncols - c0 > 16; c0 += 32) {
                 uint32_t v[32];
                 tmem_ld32(taddr + c0, v);
                 tmem_ld_wait();
-                if (valid) {
-                    epilogue_cols<32>(v, n0 + c0, p.Nc, ep);
-#pragma unroll
-                    for (int q = 0; q < 4; ++q)
-                        if (c0 + 8 * q < ncols)
-                            *reinterpret_cast<uint4*>(out + c0 + 8 * q) =
-                                make_uint4(pack_bf16(v[8 * q], v[8 * q + 1]), pack_bf16(v[8 * q + 2], v[8 * q + 3]),
-                                           pack_bf16(v[8 * q + 4], v[8 * q + 5]), pack_bf16(v[8 * q + 6], v[8 * q + 7]));
-                }
+                epilogue_chunk<32>(v, n0 + c0, ncols - c0, valid, out + c0, p.Nc, ep, ws_s + c0, ws_q + c0, lane);
             }
             for (; c0 < ncols; c0 += 16) {
                 uint32_t v[16];
                 tmem_ld16(taddr + c0, v);
                 tmem_ld_wait();
-                if (valid) {
-                    epilogue_cols<16>(v, n0 + c0, p.Nc, ep);
-#pragma unroll
-                    for (int q = 0; q < 2; ++q)
-                        if (c0 + 8 * q < ncols)
-                            *reinterpret_cast<uint4*>(out + c0 + 8 * q) =
-                                make_uint4(pack_bf16(v[8 * q], v[8 * q + 1]), pack_bf16(v[8 * q + 2], v[8 * q + 3]),
-                                           pack_bf16(v[8 * q + 4], v[8 * q + 5]), pack_bf16(v[8 * q + 6], v[8 * q + 7]));
-                }
+                epilogue_chunk<16>(v, n0 + c0, ncols - c0, valid, out + c0, p.Nc, ep, ws_s + c0, ws_q + c0, lane);
             }
             tc_fence_before();
             __syncwarp();
@@ -339,6 +412,7 @@ conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CU
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)p.tmem_cols));
     }
+    if (ep.stats) stats_tail(ep, sstat, nca, sflag);
 }
 
 // =================================================================================================
@@ -396,6 +470,12 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const uint32_t bar_tfull = bars + 16 * kMaxStages, bar_tempty = bar_tfull + 8 * kMaxAcc, bar_w = bar_tempty + 8 * kMaxAcc;
     const uint32_t tmem_slot = bar_w + 8;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // fused BatchNorm statistics (see conv_tc_kernel)
+    const int nca = (p.ncp + 31) & ~31;
+    double* sstat = reinterpret_cast<double*>(smem_raw + (tmem_slot + 24 - smem_u32(smem_raw)));
+    int* sflag = reinterpret_cast<int*>(sstat + 16 * nca);
+    if (ep.stats)
+        for (int i = threadIdx.x; i < 16 * nca; i += blockDim.x) sstat[i] = 0.0;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < p.stages; ++s) { mbar_init(bar_full + 8 * s, 1); mbar_init(bar_empty + 8 * s, p.tw == 2 ? 2 : 1); }   // pair mode: both issuers release a box
@@ -510,6 +590,8 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const uint32_t taddr = tlane + as * p.BN;
             mbar_wait(bar_tfull + 8 * as, (it / p.nacc) & 1);
             tc_fence_after();
+            double* ws_s = sstat + ((warp - 2) * 2 + 0) * nca;
+            double* ws_q = sstat + ((warp - 2) * 2 + 1) * nca;
             int c0 = 0;
             for (; c0 + 32 <= ncols || (c0 < ncols && ncols - c0 > 16); c0 += 32) {
                 uint32_t v[32];
@@ -517,29 +599,13 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     tmem_ld32(taddr + c0, v);
                     tmem_ld_wait();
                 }
-                if (valid) {
-                    epilogue_cols<32>(v, c0, p.Nc, ep);
-#pragma unroll
-                    for (int q = 0; q < 4; ++q)
-                        if (c0 + 8 * q < ncols)
-                            *reinterpret_cast<uint4*>(out + c0 + 8 * q) =
-                                make_uint4(pack_bf16(v[8 * q], v[8 * q + 1]), pack_bf16(v[8 * q + 2], v[8 * q + 3]),
-                                           pack_bf16(v[8 * q + 4], v[8 * q + 5]), pack_bf16(v[8 * q + 6], v[8 * q + 7]));
-                }
+                epilogue_chunk<32>(v, c0, ncols - c0, valid, out + c0, p.Nc, ep, ws_s + c0, ws_q + c0, lane);
             }
             for (; c0 < ncols; c0 += 16) {
                 uint32_t v[16];
                 tmem_ld16(taddr + c0, v);
                 tmem_ld_wait();
-                if (valid) {
-                    epilogue_cols<16>(v, c0, p.Nc, ep);
-#pragma unroll
-                    for (int q = 0; q < 2; ++q)
-                        if (c0 + 8 * q < ncols)
-                            *reinterpret_cast<uint4*>(out + c0 + 8 * q) =
-                                make_uint4(pack_bf16(v[8 * q], v[8 * q + 1]), pack_bf16(v[8 * q + 2], v[8 * q + 3]),
-                                           pack_bf16(v[8 * q + 4], v[8 * q + 5]), pack_bf16(v[8 * q + 6], v[8 * q + 7]));
-                }
+                epilogue_chunk<16>(v, c0, ncols - c0, valid, out + c0, p.Nc, ep, ws_s + c0, ws_q + c0, lane);
             }
             tc_fence_before();
             __syncwarp();
@@ -552,6 +618,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)p.tmem_cols));
     }
+    if (ep.stats) stats_tail(ep, sstat, nca, sflag);
 }
 
 // ---- host side ----------------------------------------------------------------------------------
@@ -1081,6 +1148,8 @@ int conv_wgrad_tc(const msx_conv_desc* d, const void* x, const void* dy, float* 
     return wgrad_reduce_launch(static_cast<const float*>(ws), p.splits, taps, A, B, p.Apad, p.Bpad, dw, st);
 }
 
+static inline uint32_t stat_smem_bytes(int ncp) { return 16u * (uint32_t)((ncp + 31) & ~31) * 8u + 16u; }
+
 static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const ConvEpilogue& ep,
                                void* dst, cudaStream_t st, bool* used) {
     *used = false;
@@ -1108,7 +1177,8 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     p.BN = Np; p.ksteps = (Kp + 15) / 16;
     p.Nc = Nc; p.ncp = round_up(Nc, 8); p.ldd = fwd_pass ? d->ldy : d->ldx;
     p.b_tap_bytes = (uint32_t)p.BN * 128;
-    const uint32_t bres = ((uint32_t)taps * p.b_tap_bytes + 1023u) & ~1023u;
+    const uint32_t stat_bytes = ep.stats ? stat_smem_bytes(p.ncp) : 0;
+    const uint32_t bres = (((uint32_t)taps * p.b_tap_bytes + 1023u) & ~1023u) + stat_bytes;      // resident bytes: weights + statistics
     p.nacc = 512 / p.BN < kMaxAcc ? 512 / p.BN : kMaxAcc;
     if (p.nacc % 2) --p.nacc;                                     // two epilogue groups alternate tiles
 #ifdef MSX_ABLATION
@@ -1244,13 +1314,21 @@ static unsigned build_taps(const msx_conv_desc* d, bool f_form, int pa, int pb, 
     return mask;
 }
 
-int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const ConvEpilogue& ep,
-                   void* dst, cudaStream_t st) {
+// stats_fused (nullable): set when ep.stats was honoured (the kernel produced and finalized the BatchNorm statistics);
+// geometries that cannot (several launches per convolution, more than one tile of output channels) leave it false and
+// the caller runs the stand-alone statistics pass.
+int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const ConvEpilogue& ep_in,
+                   void* dst, cudaStream_t st, bool* stats_fused) {
     const bool f_form = d->transposed ? !fwd_pass : fwd_pass;
+    if (stats_fused) *stats_fused = false;
+    ConvEpilogue ep = ep_in;
     if (d->stride == 1 && !d->transposed) {
         bool used = false;
         MSX_TRY(conv_gather_tc_halo(d, fwd_pass, src, packed, ep, dst, st, &used));
-        if (used) return MSX_OK;
+        if (used) {
+            if (stats_fused) *stats_fused = ep.stats != 0;
+            return MSX_OK;
+        }
     }
     TcParams p;
     const int K = fwd_pass ? d->cin : d->cout, Nc = fwd_pass ? d->cout : d->cin;
@@ -1269,12 +1347,15 @@ int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const
     p.b_bytes = (uint32_t)p.BN * row_bytes;
     p.a_stage = 128 * row_bytes;                                 // full 128-row operand tile
     p.b_stage = (p.b_bytes + 1023u) & ~1023u;
-    int stages = (int)(kSmemBudget / (p.a_stage + p.b_stage));
+    const int nphase = (!f_form && d->stride == 2) ? 4 : 1;      // b-form stride 2: one launch per destination phase
+    if (p.n_tiles != 1 || nphase != 1) ep.stats = 0;
+    const uint32_t stat_bytes = ep.stats ? stat_smem_bytes(p.ncp) : 0;
+    int stages = (int)((kSmemBudget - stat_bytes) / (p.a_stage + p.b_stage));
     p.stages = stages > kMaxStages ? kMaxStages : (stages < 2 ? 2 : stages);
     int cols = 32;
     while (cols < 2 * p.BN) cols <<= 1;
     p.tmem_cols = cols;
-    const size_t smem = 1024 + (size_t)p.stages * (p.a_stage + p.b_stage) + 16 * kMaxStages + 64;
+    const size_t smem = 1024 + (size_t)p.stages * (p.a_stage + p.b_stage) + 16 * kMaxStages + 64 + stat_bytes;
     const CUtensorMapSwizzle sw = p.chunk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
     CUtensorMap tmB;
     {
@@ -1284,7 +1365,6 @@ int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const
         MSX_TRY(make_map(&tmB, 3, packed, dims, strides, box, sw));
     }
     MSX_TRY(ensure_big_smem(reinterpret_cast<const void*>(conv_tc_kernel)));
-    const int nphase = (!f_form && d->stride == 2) ? 4 : 1;      // b-form stride 2: one launch per destination phase
     for (int ph = 0; ph < nphase; ++ph) {
         const int pa = ph >> 1, pb = ph & 1;
         const unsigned mask = build_taps(d, f_form, pa, pb, p.taps);
@@ -1307,6 +1387,7 @@ int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const
         MSX_LAUNCH_CHECK();
     }
     note_conv_engine(MSX_ENGINE_TCGEN05);
+    if (stats_fused) *stats_fused = ep.stats != 0;
     return MSX_OK;
 }
 

@@ -198,6 +198,64 @@ def test_conv_transpose_bn_relu(dtype):
         assert int(m.up_conv[1].num_batches_tracked) == 1
 
 
+BN_FUSED_CASES = [
+    # cin, cout, k, stride, dil, H, W, n
+    (17, 17, 3, 1, 1, 40, 56, 2),       # halo kernel, one 32-column chunk (24 stored columns)
+    (3, 17, 3, 1, 1, 33, 47, 3),        # ragged tiles: rows past the image must not enter the statistics
+    (34, 34, 3, 1, 2, 24, 24, 2),       # halo kernel, 40 columns: one 32-chunk + one 16-chunk
+    (64, 64, 1, 1, 1, 24, 40, 2),       # 1x1 halo kernel, two 32-column chunks
+    (17, 17, (1, 7), 1, 1, 20, 40, 2),
+    (136, 136, 3, 1, 1, 22, 22, 2),     # streaming kernel, 136 columns
+    (272, 136, 3, 1, 1, 11, 11, 2),
+    (17, 34, 3, 2, 1, 32, 48, 2),       # stride 2 (streaming kernel over phase views)
+    (3, 34, 2, 2, 1, 32, 32, 2),
+    (272, 544, 3, 1, 1, 11, 11, 2),     # > 256 output channels: two n tiles -> stand-alone statistics pass
+]
+
+
+@pytest.mark.parametrize('case', BN_FUSED_CASES)
+def test_conv_bn_relu_train_bf16_statistics_from_the_epilogue(case):
+    """ConvBNAct in training mode on the tcgen05 engine: the batch statistics come out of the convolution kernel's epilogue
+    (sums of the bf16-rounded outputs, finalized by the launch's last CTA).  Output, running statistics (momentum 0.1,
+    unbiased variance), num_batches_tracked and all gradients against float64 conv -> BatchNorm(train) -> ReLU, twice in
+    a row (the second call re-uses a re-armed ticket and stale partial rows)."""
+    import medical_segmentation_pytorch_b200 as msx
+    from medical_segmentation_pytorch_b200 import _lib
+    cin, cout, k, stride, dil, H, W, n = case
+    torch.manual_seed(cin * 1000 + cout + H)
+    m = msx.modules.ConvBNAct(cin, cout, k, stride, dil).to(DEV)
+    kk = k if isinstance(k, tuple) else (k, k)
+    pad = ((kk[0] - 1) // 2 * dil, (kk[1] - 1) // 2 * dil)
+    ref = torch.nn.Sequential(torch.nn.Conv2d(cin, cout, kk, stride, pad, dil, bias=False), torch.nn.BatchNorm2d(cout), torch.nn.ReLU()).double()
+    with torch.no_grad():
+        m[1].weight.uniform_(0.5, 1.5)
+        m[1].bias.uniform_(-0.3, 0.3)
+        m[0].weight.copy_(m[0].weight.bfloat16().float())
+    ref.load_state_dict({k_: v.double().cpu() if v.is_floating_point() else v.cpu() for k_, v in m.state_dict().items()})
+    for rep in range(2):
+        x = (torch.randn(n, cin, H, W) * (1 + rep) + 0.3 * rep).bfloat16().float()
+        xd = x.double().requires_grad_(True)
+        zr = ref(xd)
+        dz = torch.randn(zr.shape).bfloat16().float()
+        ref.zero_grad()
+        zr.backward(dz.double())
+        a = to_act(x, torch.bfloat16, requires_grad=True)
+        for p_ in m.parameters():
+            p_.grad = None
+        z = m(a)
+        assert _lib.lib.msx_last_conv_engine() == 2
+        z.t.backward(to_act(dz, torch.bfloat16).t)
+        torch.cuda.synchronize()
+        e_z = rel(from_act(z.t.detach(), cout), zr)
+        e_rm, e_rv = rel(m[1].running_mean, ref[1].running_mean), rel(m[1].running_var, ref[1].running_var)
+        e_dx, e_dw = rel(from_act(a.t.grad, cin), xd.grad), rel(m[0].weight.grad, ref[0].weight.grad)
+        e_dg, e_db = rel(m[1].weight.grad, ref[1].weight.grad), rel(m[1].bias.grad, ref[1].bias.grad)
+        print(f'fused-stats {case} rep {rep}: z {e_z:.2e} rm {e_rm:.2e} rv {e_rv:.2e} dx {e_dx:.2e} dw {e_dw:.2e} dgamma {e_dg:.2e} dbeta {e_db:.2e}')
+        assert e_z < 1.5e-2 and e_rm < 5e-3 and e_rv < 5e-3
+        assert e_dx < 6e-2 and e_dw < 6e-2 and e_dg < 3e-2 and e_db < 3e-2
+        assert int(m[1].num_batches_tracked) == rep + 1 and float(z.t[..., cout:].float().abs().sum()) == 0.0
+
+
 @pytest.mark.parametrize('c', [3, 17, 40, 272])
 @pytest.mark.parametrize('dtype', [torch.float32, torch.bfloat16])
 def test_sum_bn_relu_and_upsample(c, dtype):
