@@ -270,6 +270,14 @@ int msx_scale_by_device_scalar(float* data, int64_t count, const float* scale_de
 int msx_confmat_update(const float* logits, const int64_t* labels, int32_t n, int32_t c, int64_t hw,
                        int64_t ignore_index, int64_t* confmat, int32_t* bad_label_flag, void* stream);
 
+/* The evaluation sweep without logits in HBM (core/seg_trainer.py:114-119: preds = ema_model.ema(images) followed by
+ * metric.update(preds, masks); utils/metrics.py:4-12): seg_head 1x1 conv + argmax + confusion-matrix count in one pass
+ * over the NHWC features x [pixels, channels].  Counts are identical to msx_head_fwd followed by msx_confmat_update
+ * (same fp32 arithmetic in the same order, same tie / NaN rule).  labels int64 [pixels] (= the [n, h, w] mask). */
+int msx_head_confmat_update(int dtype, const void* x, int32_t ldx, int64_t pixels, int32_t channels, const float* w_master,
+                            int32_t num_class, const int64_t* labels, int64_t ignore_index, int64_t* confmat,
+                            int32_t* bad_label_flag, void* stream);
+
 /* Multi-tensor optimizer / EMA steps over one flat fp32 parameter arena
  * (utils/optimizer.py:8-16 -> torch.optim.Adam/AdamW/SGD; utils/model_ema.py:29-40).
  * grad_scale multiplies the gradient first (1/world_size after the DDP all-reduce).

@@ -87,6 +87,7 @@ def _load():
         'msx_dice_bce_loss_fwd_bwd': (C.c_int, [p, p, C.c_int, i64, f32, p, p, p, sz, p]),
         'msx_scale_by_device_scalar': (C.c_int, [p, i64, p, p]),
         'msx_confmat_update': (C.c_int, [p, p, i32, i32, i64, i64, p, p, p]),
+        'msx_head_confmat_update': (C.c_int, [C.c_int, p, i32, i64, i32, p, i32, p, i64, p, p, p]),
         'msx_adam_step': (C.c_int, [p, p, p, p, i64, f32, f32, f32, f32, f32, C.c_int, f32, p, p, p]),
         'msx_sgd_step': (C.c_int, [p, p, p, i64, f32, f32, f32, f32, C.c_int, p, p]),
         'msx_ema_update': (C.c_int, [p, p, i64, C.c_double, p]),

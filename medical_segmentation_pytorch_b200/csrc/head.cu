@@ -39,6 +39,67 @@ __global__ void __launch_bounds__(256) head_fwd_kernel(const T* __restrict__ x, 
     }
 }
 
+// Evaluation without logits in HBM (core/seg_trainer.py:114-119: preds = ema(images); metric.update(preds, masks)):
+// the 1x1 head, torch.argmax (first maximal index, NaN maximal) and the confusion-matrix count in one pass over the
+// features.  The logits are formed by exactly the fmaf chain of head_fwd_kernel, so every arg-max - ties included -
+// and therefore every count equals what msx_head_fwd + msx_confmat_update produce.
+template <typename T>
+__global__ void __launch_bounds__(256) head_confmat_kernel(const T* __restrict__ x, int ldx, int64_t pixels, int cp, int channels,
+                                                           const float* __restrict__ w, int nc, const int64_t* __restrict__ labels,
+                                                           int64_t ignore, unsigned long long* __restrict__ confmat, int* __restrict__ bad) {
+    extern __shared__ float ws[];                       // [nc][cp] weights, then counters
+    unsigned int* cnt = reinterpret_cast<unsigned int*>(ws + nc * cp);   // nc <= 4: [nc*nc][256] private; else [nc*nc] shared atomics
+    const bool priv = nc <= 4;
+    const int cells = nc * nc;
+    for (int i = threadIdx.x; i < nc * cp; i += blockDim.x) {
+        const int k = i / cp, c = i % cp;
+        ws[i] = c < channels ? w[k * channels + c] : 0.f;
+    }
+    if (priv) { for (int k = 0; k < cells; ++k) cnt[k * 256 + threadIdx.x] = 0; }
+    else { for (int k = threadIdx.x; k < cells; k += blockDim.x) cnt[k] = 0; }
+    __syncthreads();
+    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < pixels; p += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t t = labels[p];
+        float acc[kMaxClass];
+#pragma unroll
+        for (int k = 0; k < kMaxClass; ++k) acc[k] = 0.f;
+        const T* xp = x + p * ldx;
+        for (int c0 = 0; c0 < cp; c0 += 4) {
+            float v[4];
+            load4(xp + c0, v);
+#pragma unroll
+            for (int k = 0; k < kMaxClass; ++k)
+                if (k < nc) {
+                    const float* wk = ws + k * cp + c0;
+                    acc[k] = fmaf(v[0], wk[0], fmaf(v[1], wk[1], fmaf(v[2], wk[2], fmaf(v[3], wk[3], acc[k]))));
+                }
+        }
+        float best = acc[0];
+        int bi = 0;
+#pragma unroll
+        for (int k = 1; k < kMaxClass; ++k)
+            if (k < nc) {
+                const bool take = (acc[k] > best) || (acc[k] != acc[k] && best == best);
+                if (take) { best = acc[k]; bi = k; }
+            }
+        if (t == ignore) continue;
+        if (t < 0 || t >= nc) { *bad = 1; continue; }
+        const int cell = (int)t * nc + bi;
+        if (priv) cnt[cell * 256 + threadIdx.x] += 1; else atomicAdd(&cnt[cell], 1u);
+    }
+    __syncthreads();
+    if (priv) {
+        for (int k = 0; k < cells; ++k) {
+            unsigned int v = cnt[k * 256 + threadIdx.x];
+            v = warp_sum(v);
+            if ((threadIdx.x & 31) == 0 && v) atomicAdd(&confmat[k], (unsigned long long)v);
+        }
+    } else {
+        for (int k = threadIdx.x; k < cells; k += blockDim.x)
+            if (cnt[k]) atomicAdd(&confmat[k], (unsigned long long)cnt[k]);
+    }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(256) head_bwd_data_kernel(const float* __restrict__ dl, int64_t hw, int64_t pixels, int cp, int channels,
                                                             const float* __restrict__ w, int nc, T* __restrict__ dx, int lddx) {
@@ -163,6 +224,26 @@ int msx_head_fwd(int dtype, const void* x, int32_t ldx, int32_t n, int32_t h, in
     const int grid = (int)(cdiv64(pixels, 256) < kNumSMs * 8 ? cdiv64(pixels, 256) : kNumSMs * 8);
     MSX_DISPATCH_DTYPE(dtype, T, {
         { ProfScope ps__(K_HEAD, as_stream(stream), (double)pixels * (channels * (double)sizeof(T) + num_class * 4.0), 2.0 * (double)pixels * channels * num_class); head_fwd_kernel<T><<<grid, 256, smem, as_stream(stream)>>>(static_cast<const T*>(x), ldx, hw, pixels, cp, channels, w_master, num_class, logits); }
+    });
+    MSX_LAUNCH_CHECK();
+    return MSX_OK;
+}
+
+int msx_head_confmat_update(int dtype, const void* x, int32_t ldx, int64_t pixels, int32_t channels, const float* w_master,
+                            int32_t num_class, const int64_t* labels, int64_t ignore_index, int64_t* confmat,
+                            int32_t* bad_label_flag, void* stream) {
+    MSX_REQUIRE(x && w_master && labels && confmat && bad_label_flag, "head_confmat: null pointer");
+    MSX_REQUIRE(num_class >= 1 && num_class <= kMaxClass, "head: num_class %d not in [1,%d]", num_class, kMaxClass);
+    const int cp = round_up(channels, 8);
+    MSX_REQUIRE(ldx % 8 == 0 && ldx >= cp, "head_confmat: bad ldx %d", ldx);
+    const int cells = num_class * num_class;
+    const size_t smem = (size_t)num_class * cp * sizeof(float) + (num_class <= 4 ? (size_t)cells * 256 : (size_t)cells) * sizeof(unsigned int);
+    MSX_REQUIRE(smem <= 48 * 1024, "head_confmat: num_class*channels too large for shared memory");
+    const int grid = (int)(cdiv64(pixels, 256) < kNumSMs * 8 ? cdiv64(pixels, 256) : kNumSMs * 8);
+    auto* cm = reinterpret_cast<unsigned long long*>(confmat);
+    MSX_DISPATCH_DTYPE(dtype, T, {
+        { ProfScope ps__(K_CONFMAT, as_stream(stream), (double)pixels * (channels * (double)sizeof(T) + 8.0), 2.0 * (double)pixels * channels * num_class);
+          head_confmat_kernel<T><<<grid, 256, smem, as_stream(stream)>>>(static_cast<const T*>(x), ldx, pixels, cp, channels, w_master, num_class, labels, ignore_index, cm, bad_label_flag); }
     });
     MSX_LAUNCH_CHECK();
     return MSX_OK;
