@@ -7,7 +7,7 @@ PyTorch-eager or CPU fallback."""
 from ._lib import MsxError, lib  # noqa: F401  (fails loudly when libmsx.so is absent)
 from .ducknet import DuckNet
 from .loss import CrossEntropyLoss, DiceBCELoss, OhemCELoss, get_loss_fn, kd_loss_fn
-from .metrics import Dice, JaccardIndex, get_seg_metrics
+from .metrics import Dice, JaccardIndex, eval_sweep, get_seg_metrics
 from .graph import CapturedStep, capture_step
 from .optim import FusedOptimizer, ModelEma, get_ema_model, get_optimizer, get_scheduler
 from .parallel import (DistributedDataParallelB200, de_parallel, destroy_ddp_process, is_parallel, parallel_model,
@@ -48,7 +48,7 @@ def get_teacher_model(config, device):
     return model.to(device).eval()
 
 
-__all__ = ['UNet', 'DuckNet', 'SmpUnet', 'get_model', 'get_teacher_model', 'get_loss_fn', 'kd_loss_fn', 'get_seg_metrics', 'parallel_model',
+__all__ = ['UNet', 'DuckNet', 'SmpUnet', 'get_model', 'get_teacher_model', 'get_loss_fn', 'kd_loss_fn', 'get_seg_metrics', 'eval_sweep', 'parallel_model',
            'de_parallel', 'is_parallel', 'set_device', 'destroy_ddp_process', 'sampler_set_epoch', 'get_optimizer',
            'get_ema_model', 'get_scheduler', 'capture_step', 'CapturedStep', 'FusedOptimizer', 'ModelEma', 'CrossEntropyLoss', 'OhemCELoss', 'DiceBCELoss',
            'JaccardIndex', 'Dice', 'DistributedDataParallelB200', 'MsxError']

@@ -114,6 +114,8 @@ class UpsampleBlock(nn.Module):
 
 
 class DuckNet(nn.Module):
+    _features_only = False      # features(): stop before seg_head (fused head + argmax + confusion matrix in eval)
+
     def __init__(self, num_class=1, n_channel=3, base_channel=17, act_type='relu'):
         super().__init__()
         b = base_channel
@@ -140,6 +142,15 @@ class DuckNet(nn.Module):
         with packplan.active(self, dt, x.device, skip=(self.seg_head,)):     # all conv weights packed by one launch
             return self._forward(x, dt)
 
+    def features(self, x):
+        """The activation that feeds seg_head, as an NHWC ``Act`` (no logits are formed): input of
+        ``metric.update_from_features`` / ``metrics.eval_sweep``."""
+        self._features_only = True
+        try:
+            return self.forward(x)
+        finally:
+            self._features_only = False
+
     def _forward(self, x, dt):
         img = ops.to_nhwc(x, dt)
         x1, s1, xc = self.down_stage1([img], img)
@@ -153,4 +164,6 @@ class DuckNet(nn.Module):
             a = blk(a)
         for stage, s in zip((self.up_stage5, self.up_stage4, self.up_stage3, self.up_stage2, self.up_stage1), reversed(skips)):
             a = stage(a, s)
+        if self._features_only:
+            return a
         return ops.HeadFn.apply(a.t, self.seg_head.weight, a.c)

@@ -51,6 +51,27 @@ class _ConfMatMetric:
         L.check(lib.msx_confmat_update(L.ptr(preds), L.ptr(target), n, c, hw, self.ignore_index, L.ptr(self.confmat),
                                        L.ptr(self._bad), L.stream()))
 
+    @torch.no_grad()
+    def update_from_features(self, feat, head_weight, target):
+        """Same counts as ``update(model(images), target)`` without the logits ever reaching HBM:
+        ``feat`` is ``model.features(images)`` (NHWC ``Act``), ``head_weight`` is ``model.seg_head.weight``; the 1x1 head,
+        the argmax and the count run as one kernel (msx_head_confmat_update)."""
+        t = feat.t
+        if self.confmat is None:
+            self.to(t.device)
+        nc = head_weight.shape[0]
+        if nc != self.num_classes:
+            raise ValueError(f'expected {self.num_classes} class channels, got {nc}')
+        target = target.long().contiguous() if target.dtype != torch.int64 or not target.is_contiguous() else target
+        n, h, w, _ = t.shape
+        if target.numel() != n * h * w:
+            raise ValueError(f'target has {target.numel()} pixels, features have {n * h * w}')
+        wt = head_weight.detach()
+        if wt.dtype != torch.float32 or not wt.is_contiguous():
+            raise L.MsxError('seg_head weight must be contiguous fp32')
+        L.check(lib.msx_head_confmat_update(L.dtype_code(t.dtype), L.ptr(t), t.stride(2), n * h * w, feat.c, L.ptr(wt), nc,
+                                            L.ptr(target), self.ignore_index, L.ptr(self.confmat), L.ptr(self._bad), L.stream()))
+
     def _synced(self):
         cm = self.confmat
         if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
@@ -90,6 +111,21 @@ class Dice(_ConfMatMetric):
         if not bool(present.any()):
             return torch.zeros((), dtype=torch.float32, device=cm.device)
         return score[present].mean()
+
+
+@torch.no_grad()
+def eval_sweep(model, images, masks, metrics, batch_size=16):
+    """The validation loop of core/seg_trainer.py:100-125 for same-sized images: the reference feeds ``val_bs = 1`` image at
+    a time (configs/my_config.py:27) and hands the logits to each metric; here ``batch_size`` images go through the
+    eval-mode model together (per-image results do not depend on the batch in eval mode: BatchNorm uses running
+    statistics) and each metric counts straight from the features.  ``images`` [N,C,H,W], ``masks`` [N,H,W] on the
+    device; ``model`` in eval mode (the trainer passes ``ema_model.ema``).  Returns nothing: call ``metric.compute()``."""
+    if model.training:
+        raise ValueError('eval_sweep expects model.eval() (core/seg_trainer.py:114 validates the EMA copy in eval mode)')
+    for i in range(0, images.shape[0], batch_size):
+        feat = model.features(images[i:i + batch_size])
+        for m in metrics:
+            m.update_from_features(feat, model.seg_head.weight, masks[i:i + batch_size])
 
 
 def get_seg_metrics(config, metric_name):

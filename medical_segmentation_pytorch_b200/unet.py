@@ -43,6 +43,8 @@ class UpsampleBlock(nn.Module):
 
 
 class UNet(nn.Module):
+    _features_only = False      # features(): stop before seg_head (fused head + argmax + confusion matrix in eval)
+
     def __init__(self, num_class=1, n_channel=3, base_channel=64, act_type='relu'):
         super().__init__()
         if base_channel % 8:
@@ -67,6 +69,15 @@ class UNet(nn.Module):
         with packplan.active(self, dt, x.device, skip=(self.seg_head,)):     # all conv weights packed by one launch
             return self._forward(x, dt)
 
+    def features(self, x):
+        """The activation that feeds seg_head, as an NHWC ``Act`` (no logits are formed): input of
+        ``metric.update_from_features`` / ``metrics.eval_sweep``."""
+        self._features_only = True
+        try:
+            return self.forward(x)
+        finally:
+            self._features_only = False
+
     def _forward(self, x, dt):
         a = ops.to_nhwc(x, dt)
         n, _, h, w = x.shape
@@ -80,4 +91,6 @@ class UNet(nn.Module):
         a = self.mid_stage(a)
         for i, stage in zip((3, 2, 1, 0), (self.up_stage4, self.up_stage3, self.up_stage2, self.up_stage1)):
             a = stage(a, skips[i], bufs[i])
+        if self._features_only:
+            return a
         return ops.HeadFn.apply(a.t, self.seg_head.weight, a.c)

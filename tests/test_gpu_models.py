@@ -352,3 +352,50 @@ def test_ducknet_branch_streams_bit_identical(bf16):
         assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
         assert all(torch.equal(g, h) for g, h in zip(a[2], b[2]))
         assert all(torch.equal(g, h) for g, h in zip(a[3], b[3]))
+
+
+@pytest.mark.parametrize('arch,base,dtype', [('unet', 8, torch.float32), ('ducknet', 4, torch.float32), ('unet', 8, torch.bfloat16), ('ducknet', 17, torch.bfloat16)])
+def test_eval_sweep_fused_head_argmax_confmat_is_bit_exact(arch, base, dtype):
+    """core/seg_trainer.py:100-125 without logits in HBM: head 1x1 + argmax + confusion matrix in one kernel, images batched.
+    The counts must equal - exactly - those of the reference's own order of work (one image per update, logits
+    materialised, metric.update(logits, mask)) on the same eval-mode model, for both metrics, with ignore labels; and the
+    CPU oracle's confusion matrix of the logits path."""
+    import medical_segmentation_pytorch_b200 as msx
+    from medical_segmentation_pytorch_b200.synth import synth_batch
+    from oracle import ref_metrics
+    torch.manual_seed(11)
+    model = (msx.UNet if arch == 'unet' else msx.DuckNet)(2, 3, base).to(DEV)
+    with torch.no_grad():
+        for m in model.modules():                      # non-trivial running statistics, as after training
+            if isinstance(m, torch.nn.BatchNorm2d):
+                m.running_mean.uniform_(-0.2, 0.2)
+                m.running_var.uniform_(0.6, 1.4)
+    model.eval()
+    model.compute_dtype = dtype
+    x, t = synth_batch(5, 64, 96, seed=8, ignore_band=0.04)
+    x, t = x.to(DEV), t.to(DEV)
+    t_clean = torch.where(t == 255, torch.zeros_like(t), t)
+    cfg = Cfg()
+    ref_iou, ref_dice = msx.get_seg_metrics(cfg, 'iou').to(DEV), msx.get_seg_metrics(cfg, 'dice').to(DEV)
+    cm = np.zeros((2, 2), dtype=np.int64)
+    with torch.no_grad():
+        for i in range(x.shape[0]):                    # the reference's loop: val_bs = 1, logits -> metric.update
+            lg = model(x[i:i + 1])
+            ref_iou.update(lg, t[i:i + 1])
+            ref_dice.update(lg, t_clean[i:i + 1])
+            cm += ref_metrics.confusion_matrix(lg.cpu().numpy(), t[i:i + 1].cpu().numpy(), 2, 255)
+    assert np.array_equal(ref_iou.confmat.cpu().numpy(), cm)
+    for bs in (1, 2, 16):
+        iou, dice = msx.get_seg_metrics(cfg, 'iou').to(DEV), msx.get_seg_metrics(cfg, 'dice').to(DEV)
+        msx.eval_sweep(model, x, t, [iou], batch_size=bs)
+        msx.eval_sweep(model, x, t_clean, [dice], batch_size=bs)
+        assert torch.equal(iou.confmat, ref_iou.confmat), (bs, iou.confmat, ref_iou.confmat)
+        assert torch.equal(dice.confmat, ref_dice.confmat), bs
+        assert torch.equal(iou.compute(), ref_iou.compute()) and torch.equal(dice.compute(), ref_dice.compute())
+    assert int(ref_iou.confmat.sum()) == int((t != 255).sum())
+    bad = msx.get_seg_metrics(cfg, 'dice').to(DEV)      # Dice has no ignore_index: a 255 label is an error at compute()
+    msx.eval_sweep(model, x, t, [bad])
+    with pytest.raises(ValueError):
+        bad.compute()
+    with pytest.raises(ValueError):
+        msx.eval_sweep(model.train(), x, t, [iou])
