@@ -276,6 +276,8 @@ int bn_finalize_args(BnFinalize* f, double* partials, int channels, int64_t coun
 int bn_stats_launch(int dtype, const void* x, int ld, int64_t pixels, int channels, double* partials, const BnFinalize* fin,
                     int* nblk_out, cudaStream_t st);
 int bn_finalize_sums_launch(const double* sums, const BnFinalize& f, cudaStream_t st);
+int bn_finalize_launch(const BnFinalize& f, int nblk, cudaStream_t st);
+int ticket_max_cp();
 int bn_bwd_reduce_launch(int dtype, const void* x, int ldx, const void* dz, int lddz, int64_t pixels, int channels,
                          const float* gamma, const float* beta, const float* mean, const float* invstd, int flags,
                          float* dgamma, float* dbeta, double* partials, float* c1, float* c2, double* sums, cudaStream_t st);

@@ -157,8 +157,8 @@ __device__ __forceinline__ void epilogue_chunk(uint32_t (&v)[NV], int col0, int 
     }
 }
 
-// After every role of the CTA is done: fold the 8 epilogue warps' running sums into this CTA's row of partials; the last
-// CTA of the launch to get here folds the rows and finalizes (mean, invstd, running statistics).  All threads call.
+// After every role of the CTA is done: fold the 8 epilogue warps' running sums into this CTA's row of partials (a finalize
+// launch folds the <= 148 rows; with a ticket the last CTA of this launch does it instead).  All threads call.
 __device__ __forceinline__ void stats_tail(const ConvEpilogue& ep, double* sstat, int nca, int* flag) {
     const BnFinalize& f = ep.bnf;
     for (int c = threadIdx.x; c < f.cp; c += blockDim.x) {
@@ -168,7 +168,7 @@ __device__ __forceinline__ void stats_tail(const ConvEpilogue& ep, double* sstat
         f.partials[((int64_t)blockIdx.x * 2 + 0) * f.cp + c] = s;
         f.partials[((int64_t)blockIdx.x * 2 + 1) * f.cp + c] = q;
     }
-    if (ticket_is_last(f.ticket, gridDim.x, flag)) bn_finalize_all(f, gridDim.x);
+    if (f.ticket && ticket_is_last(f.ticket, gridDim.x, flag)) bn_finalize_all(f, gridDim.x);
 }
 
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
@@ -1252,6 +1252,7 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
         kern<<<grid, kHaloThreads2, smem, st>>>(tmA, tmB, static_cast<bf16*>(dst), ep, p);
     }
     MSX_LAUNCH_CHECK();
+    if (ep.stats && !ep.bnf.ticket) MSX_TRY(bn_finalize_launch(ep.bnf, grid, st));
     note_conv_engine(MSX_ENGINE_TCGEN05);
     *used = true;
     return MSX_OK;
@@ -1385,6 +1386,7 @@ int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const
             conv_tc_kernel<<<grid, kHaloThreads, smem, st>>>(maps, tmB, static_cast<bf16*>(dst), ep, p);
         }
         MSX_LAUNCH_CHECK();
+        if (ep.stats && !ep.bnf.ticket) MSX_TRY(bn_finalize_launch(ep.bnf, grid, st));
     }
     note_conv_engine(MSX_ENGINE_TCGEN05);
     if (stats_fused) *stats_fused = ep.stats != 0;

@@ -6,6 +6,8 @@
 // stay in registers and every warp access is a run of whole 16 B vectors along the contiguous
 // channel axis.  A CTA of 256 threads = `lanes` pixels x `vch` vectors; blockIdx.y selects a
 // chunk of <= 64 vectors when the tensor has more channels than that.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace msx {
@@ -123,6 +125,29 @@ __global__ void __launch_bounds__(256) bn_stats_kernel(const T* __restrict__ x, 
     if (fin.ticket && ticket_is_last(fin.ticket, gridDim.x * gridDim.y, &last_flag)) bn_finalize_all(fin, gridDim.x);
 }
 
+// Stand-alone fold + finalize: one warp per channel over many CTAs.  Measured (round 2): letting the reduction launch's last
+// CTA do this instead (tickets, common.cuh) removes a launch but serialises the fold of all channels in ONE CTA, which
+// costs more than the launch for every layer wider than ~40 channels (bn_bwd_reduce 6.8 -> 15.2 ms per DUCKNet-17 step),
+// so the in-kernel path is only taken up to ticket_max_cp() channels (default 0: never).
+__global__ void bn_finalize_kernel(int nblk, const BnFinalize f) {
+    const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (c == 0 && lane == 0 && f.nbt && !f.sums) *f.nbt += 1;
+    if (c >= f.cp) return;
+    if (c >= f.channels) {
+        if (lane == 0) {
+            if (f.sums) { f.sums[c] = 0.0; f.sums[f.cp + c] = 0.0; }
+            else { f.mean[c] = 0.f; f.invstd[c] = 0.f; }
+        }
+        return;
+    }
+    double s, q;
+    fold_partials(f.partials, nblk, f.cp, c, s, q);
+    if (lane != 0) return;
+    if (f.sums) { f.sums[c] = s; f.sums[f.cp + c] = q; }
+    else bn_finalize_one(f, c, s, q);
+}
+
 // SyncBatchNorm: per-channel [sum, sum of squares] (doubles, already reduced over ranks) -> mean / invstd / running stats
 __global__ void bn_finalize_sums_kernel(const double* __restrict__ sums, const BnFinalize f) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -233,6 +258,27 @@ __device__ inline void bn_bwd_finalize_all(const BnBwdFinalize& f, const double*
         f.c1[c] = f.eval_mode ? 0.f : (float)(s / (double)f.count);
         f.c2[c] = f.eval_mode ? 0.f : (float)(q / (double)f.count);
     }
+}
+
+__global__ void bn_bwd_finalize_kernel(const double* partials, int nblk, const BnBwdFinalize f) {
+    const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (c >= f.cp) return;
+    if (c >= f.channels) {
+        if (lane == 0) {
+            if (f.sums) { f.sums[c] = 0.0; f.sums[f.cp + c] = 0.0; }
+            f.c1[c] = 0.f; f.c2[c] = 0.f;
+        }
+        return;
+    }
+    double s, q;
+    fold_partials(partials, nblk, f.cp, c, s, q);
+    if (lane != 0) return;
+    if (f.dbeta) f.dbeta[c] = (float)s;
+    if (f.dgamma) f.dgamma[c] = (float)q;
+    if (f.sums) { f.sums[c] = s; f.sums[f.cp + c] = q; }
+    f.c1[c] = f.eval_mode ? 0.f : (float)(s / (double)f.count);
+    f.c2[c] = f.eval_mode ? 0.f : (float)(q / (double)f.count);
 }
 
 __global__ void bn_bwd_coeffs_kernel(const double* __restrict__ sums, int cp, int channels, double count, float* c1, float* c2) {
@@ -607,11 +653,26 @@ size_t bn_partials_bytes(int channels) {
     return (size_t)kMaxPartialBlocks * 2 * cp * sizeof(double) + 2 * (size_t)cp * sizeof(float) + 256;
 }
 
+int ticket_max_cp() {
+    static const int v = [] { const char* e = getenv("MSX_TICKET_MAX_CP"); return e ? atoi(e) : 0; }();
+    return v;
+}
+
+// fold nblk partial rows and finalize, as its own launch (what every reduction uses when its BnFinalize has no ticket)
+int bn_finalize_launch(const BnFinalize& f, int nblk, cudaStream_t st) {
+    { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_finalize_kernel<<<(f.cp * 32 + 127) / 128, 128, 0, st>>>(nblk, f); }
+    MSX_LAUNCH_CHECK();
+    return MSX_OK;
+}
+
 int bn_finalize_args(BnFinalize* f, double* partials, int channels, int64_t count, float eps, float momentum, float* mean,
                      float* invstd, float* running_mean, float* running_var, int64_t* nbt, double* sums) {
     f->partials = partials;
-    f->ticket = next_ticket();
-    if (!f->ticket) return set_error(MSX_ERR_CUDA, "reduction ticket array unavailable (cudaGetSymbolAddress failed)");
+    f->ticket = nullptr;
+    if (round_up(channels, 8) <= ticket_max_cp()) {
+        f->ticket = next_ticket();
+        if (!f->ticket) return set_error(MSX_ERR_CUDA, "reduction ticket array unavailable (cudaGetSymbolAddress failed)");
+    }
     f->sums = sums;
     f->mean = mean; f->invstd = invstd; f->running_mean = running_mean; f->running_var = running_var;
     f->nbt = reinterpret_cast<long long*>(nbt);
@@ -631,6 +692,7 @@ int bn_stats_launch(int dtype, const void* x, int ld, int64_t pixels, int channe
         const int g = reduce_grid(pixels, c.lanes);
         { ProfScope ps__(K_BN_STATS, st, (double)pixels * channels * (double)sizeof(T), 0); bn_stats_kernel<T><<<dim3(g, c.nchunk), 256, 0, st>>>(static_cast<const T*>(x), ld, pixels, c.cp, c.vch, partials, f); }
         if (nblk_out) *nblk_out = g;
+        if (fin && !fin->ticket) MSX_TRY(bn_finalize_launch(f, g, st));
     });
     MSX_LAUNCH_CHECK();
     return MSX_OK;
@@ -681,8 +743,11 @@ int bn_bwd_reduce_launch(int dtype, const void* x, int ldx, const void* dz, int 
     MSX_TRY(check_ld(ldx, channels, "bn_bwd x"));
     MSX_TRY(check_ld(lddz, channels, "bn_bwd dz"));
     BnBwdFinalize f;
-    f.ticket = next_ticket();
-    if (!f.ticket) return set_error(MSX_ERR_CUDA, "reduction ticket array unavailable (cudaGetSymbolAddress failed)");
+    f.ticket = nullptr;
+    if (round_up(channels, 8) <= ticket_max_cp()) {
+        f.ticket = next_ticket();
+        if (!f.ticket) return set_error(MSX_ERR_CUDA, "reduction ticket array unavailable (cudaGetSymbolAddress failed)");
+    }
     f.sums = sums; f.dgamma = dgamma; f.dbeta = dbeta; f.c1 = c1; f.c2 = c2;
     f.count = pixels; f.channels = channels; f.cp = round_up(channels, 8); f.eval_mode = (flags & MSX_BN_EVAL) ? 1 : 0;
     MSX_DISPATCH_DTYPE(dtype, T, {
@@ -690,6 +755,7 @@ int bn_bwd_reduce_launch(int dtype, const void* x, int ldx, const void* dz, int 
         const int g = reduce_grid(pixels, c.lanes);
         { ProfScope ps__(K_BN_BWD_REDUCE, st, 2.0 * (double)pixels * channels * (double)sizeof(T), 0); bn_bwd_reduce_kernel<T><<<dim3(g, c.nchunk), 256, 0, st>>>(static_cast<const T*>(x), ldx, static_cast<const T*>(dz), lddz,
                                                                  pixels, c.cp, c.vch, channels, mean, invstd, gamma, beta, relu, partials, f); }
+        if (!f.ticket) { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_bwd_finalize_kernel<<<(f.cp * 32 + 127) / 128, 128, 0, st>>>(partials, g, f); }
     });
     MSX_LAUNCH_CHECK();
     return MSX_OK;
@@ -800,6 +866,7 @@ int msx_sum_bn_act_fwd(int dtype, int n_in, const void* const* host_xs, const in
                                                                      training ? partials : nullptr, nullptr, nullptr, 0, fin); }
         });
         MSX_LAUNCH_CHECK();
+        if (training && !fin.ticket) MSX_TRY(bn_finalize_launch(fin, nblk, st));
         src = s;
         ldsrc = lds;
     } else if (training) {

@@ -56,7 +56,16 @@ def main():
 
         def wgrad():
             L.check(lib.msx_conv2d_bwd(C.byref(d), L.ptr(x), L.ptr(w), L.ptr(dy), L.ptr(pk), None, L.ptr(dw), None, L.ptr(ws), ws.numel(), st))
-        for name, fn in (('fprop', fprop), ('dgrad', dgrad), ('wgrad', wgrad)):
+        gam, bet = torch.rand(cout, device=dev) + 0.5, torch.rand(cout, device=dev)
+        rm, rv = torch.zeros(cout, device=dev), torch.ones(cout, device=dev)
+        nbt = torch.zeros((), dtype=torch.int64, device=dev)
+        cpo = ops.rup(cout)
+        mean, inv, z = torch.empty(cpo, device=dev), torch.empty(cpo, device=dev), torch.empty_like(dy)
+
+        def cbr():      # ConvBNAct training forward: conv (+ statistics) -> finalize -> apply  (MSX_FUSED_STATS=0: separate statistics pass)
+            L.check(lib.msx_conv_bn_act_fwd(C.byref(d), L.ptr(x), L.ptr(w), None, L.ptr(gam), L.ptr(bet), L.ptr(rm), L.ptr(rv), L.ptr(nbt),
+                                            1e-5, 0.1, 1, 1, L.ptr(pk), L.ptr(y), L.ptr(z), cpo, L.ptr(mean), L.ptr(inv), L.ptr(ws), ws.numel(), st))
+        for name, fn in (('fprop', fprop), ('dgrad', dgrad), ('wgrad', wgrad), ('cbr', cbr)):
             if name not in a.passes.split(','):
                 continue
             fn()
@@ -72,7 +81,8 @@ def main():
             main_k = {k: v for k, v in prof.items() if k.startswith('conv_')}
             ms = sum(v['ms'] for v in main_k.values()) / a.reps
             other = sum(v['ms'] for k, v in prof.items() if not k.startswith('conv_')) / a.reps
-            print(f'{cin:4d}->{cout:4d} {kh}x{kw} d{dil} @{hw:3d}^2     {name:6s} {ms * 1e3:9.1f} {by / ms / 1e6:8.0f} {fl / ms / 1e9:8.1f}   (+{other * 1e3:.1f} us pack/reduce)')
+            detail = ' '.join(f'{k}={v["ms"] / a.reps * 1e3:.1f}' for k, v in prof.items()) if name == 'cbr' else ''
+            print(f'{cin:4d}->{cout:4d} {kh}x{kw} d{dil} @{hw:3d}^2     {name:6s} {ms * 1e3:9.1f} {by / ms / 1e6:8.0f} {fl / ms / 1e9:8.1f}   (+{other * 1e3:.1f} us pack/reduce/bn) {detail}')
 
 
 if __name__ == '__main__':
