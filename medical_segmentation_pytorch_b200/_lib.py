@@ -9,7 +9,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'libmsx.so')
+LIB_PATH = os.environ.get('MSX_LIB') or os.path.join(_HERE, 'libmsx.so')     # MSX_LIB: a measurement build (build.py --variant)
 
 F32, BF16 = 0, 1
 PACK_FPROP, PACK_DGRAD = 0, 1

@@ -42,6 +42,32 @@ def _digest():
     return h.hexdigest()
 
 
+def build_variant(name, defines, verbose=False):
+    """Measurement builds: the same sources with extra -D switches into ``lib<name>.so`` next to libmsx.so
+    (select it at run time with MSX_LIB=<path>); never the default library."""
+    nvcc = _nvcc()
+    objdir = os.path.join(HERE, 'build', name)
+    os.makedirs(objdir, exist_ok=True)
+    procs = []
+    for s in _sources():
+        obj = os.path.join(objdir, s.replace('.cu', '.o'))
+        procs.append((s, obj, subprocess.Popen([nvcc] + NVCC_FLAGS + list(defines) + ['-c', os.path.join(CSRC, s), '-o', obj] + (['-Xptxas', '-v'] if verbose else []),
+                                               stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+    objs = []
+    for s, obj, p in procs:
+        out, _ = p.communicate()
+        if p.returncode != 0:
+            raise RuntimeError(f'nvcc failed on {s}:\n{out}')
+        if verbose and out:
+            print(out)
+        objs.append(obj)
+    lib = os.path.join(HERE, f'lib{name}.so')
+    r = subprocess.run([nvcc, '-shared', '-gencode', 'arch=compute_100a,code=sm_100a', '-o', lib] + objs, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if r.returncode != 0:
+        raise RuntimeError(f'link failed:\n{r.stdout}')
+    return lib
+
+
 def build(force=False, verbose=False):
     dig = _digest()
     if not force and os.path.exists(LIB) and os.path.exists(STAMP) and open(STAMP).read().strip() == dig:
@@ -74,4 +100,8 @@ def build(force=False, verbose=False):
 
 
 if __name__ == '__main__':
-    print(build(force='--force' in sys.argv, verbose='-v' in sys.argv))
+    if '--variant' in sys.argv:          # python build.py --variant msx_alt -DMSX_TC_SMEM_KB=150 ...
+        i = sys.argv.index('--variant')
+        print(build_variant(sys.argv[i + 1], [a for a in sys.argv[i + 2:] if a.startswith('-D')], verbose='-v' in sys.argv))
+    else:
+        print(build(force='--force' in sys.argv, verbose='-v' in sys.argv))

@@ -37,7 +37,10 @@ constexpr int kHaloThreads = 320;      // TMA warp + MMA warp + 2 x 4 epilogue w
 constexpr int kHaloThreads2 = 352;     // halo kernel: + a second MMA-issuing warp (warp 10)
 constexpr int kMaxStages = 8;
 constexpr int kMaxAcc = 8;
-constexpr uint32_t kSmemBudget = 200 * 1024;
+#ifndef MSX_TC_SMEM_KB
+#define MSX_TC_SMEM_KB 200
+#endif
+constexpr uint32_t kSmemBudget = MSX_TC_SMEM_KB * 1024;   // pipeline stages + resident weights of one CTA
 
 constexpr int kTapMax = 49;          // tap table capacity (7x7); wgrad / dgrad stay within kTapMaxTrain
 constexpr int kTapMaxTrain = 16;
@@ -93,29 +96,29 @@ __device__ __forceinline__ uint32_t pack_bf16(uint32_t a, uint32_t b) {
 
 // Column sums over the 32 lanes of a warp, one accumulator row per lane: on return lane l holds the sum over all lanes of
 // v[l] (NV == 32) or of v[l & 15] (NV == 16).  Transpose-reduce: each step halves the columns a lane is responsible for,
-// 31 shuffles in total instead of 5 per column.  v is destroyed.
+// 31 shuffles in total instead of 5 per column.  The arrays are destroyed; element 0 holds the result.
 template <int N>
-__device__ __forceinline__ void colsum_step(float* v, int lane) {
+__device__ __forceinline__ void colsum_step(float* a, float* b, int lane) {      // two independent reductions interleaved (ILP)
     const bool up = (lane & N) != 0;
 #pragma unroll
     for (int i = 0; i < N; ++i) {
-        const float keep = up ? v[i + N] : v[i];
-        const float send = up ? v[i] : v[i + N];
-        v[i] = keep + __shfl_xor_sync(0xffffffffu, send, N);
+        const float ka = up ? a[i + N] : a[i], sa = up ? a[i] : a[i + N];
+        const float kb = up ? b[i + N] : b[i], sb = up ? b[i] : b[i + N];
+        a[i] = ka + __shfl_xor_sync(0xffffffffu, sa, N);
+        b[i] = kb + __shfl_xor_sync(0xffffffffu, sb, N);
     }
 }
 template <int NV>
-__device__ __forceinline__ float warp_colsum(float (&v)[NV], int lane) {
-    if (NV == 32) colsum_step<16>(v, lane);
+__device__ __forceinline__ void warp_colsum2(float (&a)[NV], float (&b)[NV], int lane) {
+    if constexpr (NV == 32) colsum_step<16>(a, b, lane);
     else {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] += __shfl_xor_sync(0xffffffffu, v[i], 16);
+        for (int i = 0; i < 16; ++i) { a[i] += __shfl_xor_sync(0xffffffffu, a[i], 16); b[i] += __shfl_xor_sync(0xffffffffu, b[i], 16); }
     }
-    colsum_step<8>(v, lane);
-    colsum_step<4>(v, lane);
-    colsum_step<2>(v, lane);
-    colsum_step<1>(v, lane);
-    return v[0];
+    colsum_step<8>(a, b, lane);
+    colsum_step<4>(a, b, lane);
+    colsum_step<2>(a, b, lane);
+    colsum_step<1>(a, b, lane);
 }
 
 // One chunk of NV accumulator columns of one pixel row (this thread's): bias / affine / ReLU, bf16 pack, 16 B stores, and -
@@ -136,23 +139,18 @@ __device__ __forceinline__ void epilogue_chunk(uint32_t (&v)[NV], int col0, int 
                 *reinterpret_cast<uint4*>(out + 8 * q) = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
     }
     if (ep.stats) {
-        float a[NV];
+        float a[NV], b[NV];
 #pragma unroll
         for (int j = 0; j < NV / 2; ++j) {
             a[2 * j] = valid ? __uint_as_float(pk[j] << 16) : 0.f;
             a[2 * j + 1] = valid ? __uint_as_float(pk[j] & 0xffff0000u) : 0.f;
+            b[2 * j] = a[2 * j] * a[2 * j];
+            b[2 * j + 1] = a[2 * j + 1] * a[2 * j + 1];
         }
-        const float s = warp_colsum<NV>(a, lane);
-#pragma unroll
-        for (int j = 0; j < NV / 2; ++j) {
-            const float lo = valid ? __uint_as_float(pk[j] << 16) : 0.f, hi = valid ? __uint_as_float(pk[j] & 0xffff0000u) : 0.f;
-            a[2 * j] = lo * lo;
-            a[2 * j + 1] = hi * hi;
-        }
-        const float q = warp_colsum<NV>(a, lane);
+        warp_colsum2<NV>(a, b, lane);
         if (NV == 32 || lane < 16) {
-            stat_s[lane] += (double)s;
-            stat_q[lane] += (double)q;
+            stat_s[lane] += (double)a[0];
+            stat_q[lane] += (double)b[0];
         }
     }
 }

@@ -45,22 +45,35 @@ __device__ inline ChanThread chan_thread(int cp, int vch) {
 
 // Sum v[j] over the pixel lanes of the CTA (threads that share threadIdx.x % vch); result valid
 // in lane 0.  sh: NV * 256 doubles; all NV values go through ONE tree (log2(lanes) barriers in total).
+#ifndef MSX_BN_MINBLOCKS
+#define MSX_BN_MINBLOCKS 1          // CTAs per SM the reduction kernels are compiled for (register cap)
+#endif
+#ifdef MSX_BN_SMALL_SMEM
+constexpr int kLaneReduceRounds = 2;   // half the shared memory (16 KB for bf16): the values go through the tree in two rounds
+#else
+constexpr int kLaneReduceRounds = 1;
+#endif
 template <int NV>
 __device__ inline void lane_reduce(double (&v)[NV], double* sh, int vch, int lane, int lanes) {
     int p2 = 1;
     while (p2 < lanes) p2 <<= 1;
+    constexpr int H = NV / kLaneReduceRounds;
 #pragma unroll
-    for (int j = 0; j < NV; ++j) sh[j * 256 + threadIdx.x] = v[j];
-    __syncthreads();
-    for (int off = p2 >> 1; off > 0; off >>= 1) {
-        if (lane < off && lane + off < lanes) {
+    for (int r = 0; r < kLaneReduceRounds; ++r) {
+        if (r) __syncthreads();
 #pragma unroll
-            for (int j = 0; j < NV; ++j) sh[j * 256 + threadIdx.x] += sh[j * 256 + threadIdx.x + off * vch];
-        }
+        for (int j = 0; j < H; ++j) sh[j * 256 + threadIdx.x] = v[r * H + j];
         __syncthreads();
-    }
+        for (int off = p2 >> 1; off > 0; off >>= 1) {
+            if (lane < off && lane + off < lanes) {
 #pragma unroll
-    for (int j = 0; j < NV; ++j) v[j] = sh[j * 256 + threadIdx.x];
+                for (int j = 0; j < H; ++j) sh[j * 256 + threadIdx.x] += sh[j * 256 + threadIdx.x + off * vch];
+            }
+            __syncthreads();
+        }
+#pragma unroll
+        for (int j = 0; j < H; ++j) v[r * H + j] = sh[j * 256 + threadIdx.x];
+    }
 }
 
 inline int reduce_grid(int64_t pixels, int lanes) {
@@ -78,10 +91,10 @@ inline int stream_grid(int64_t pixels, int lanes) {
 
 // ---- statistics ---------------------------------------------------------------------------
 template <typename T>
-__global__ void __launch_bounds__(256) bn_stats_kernel(const T* __restrict__ x, int ld, int64_t pixels, int cp, int vch,
+__global__ void __launch_bounds__(256, MSX_BN_MINBLOCKS) bn_stats_kernel(const T* __restrict__ x, int ld, int64_t pixels, int cp, int vch,
                                                        double* partials, const BnFinalize fin) {
     constexpr int VEC = Vec<T>::N;
-    __shared__ double sh[2 * VEC * 256];
+    __shared__ double sh[2 * VEC * 256 / kLaneReduceRounds];
     __shared__ int last_flag;
     const ChanThread t = chan_thread<VEC>(cp, vch);
     double acc[2 * VEC];
@@ -290,13 +303,13 @@ __global__ void bn_bwd_coeffs_kernel(const double* __restrict__ sums, int cp, in
 
 // g = dz * [relu mask];  partial sums of g and g*xhat.
 template <typename T>
-__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const T* __restrict__ x, int ldx, const T* __restrict__ dz, int lddz,
+__global__ void __launch_bounds__(256, MSX_BN_MINBLOCKS) bn_bwd_reduce_kernel(const T* __restrict__ x, int ldx, const T* __restrict__ dz, int lddz,
                                                             int64_t pixels, int cp, int vch, int channels,
                                                             const float* __restrict__ mean, const float* __restrict__ invstd,
                                                             const float* __restrict__ gamma, const float* __restrict__ beta,
                                                             int relu, double* partials, const BnBwdFinalize fin) {
     constexpr int VEC = Vec<T>::N;
-    __shared__ double shm[2 * VEC * 256];
+    __shared__ double shm[2 * VEC * 256 / kLaneReduceRounds];
     __shared__ int last_flag;
     const ChanThread t = chan_thread<VEC>(cp, vch);
     float mu[VEC], is[VEC], ga[VEC], be[VEC];
@@ -418,12 +431,12 @@ struct SumArgs {
     int n;
 };
 template <typename T, bool STATS>
-__global__ void __launch_bounds__(256) sum_stats_kernel(SumArgs a, int up2x, int H, int W, T* __restrict__ s, int lds,
+__global__ void __launch_bounds__(256, MSX_BN_MINBLOCKS) sum_stats_kernel(SumArgs a, int up2x, int H, int W, T* __restrict__ s, int lds,
                                                         int64_t pixels, int cp, int vch, double* partials,
                                                         const float* __restrict__ scale = nullptr, const float* __restrict__ shift = nullptr,
                                                         int relu = 0, const BnFinalize fin = BnFinalize{}) {
     constexpr int VEC = Vec<T>::N;
-    __shared__ double sh[STATS ? 2 * VEC * 256 : 1];
+    __shared__ double sh[STATS ? 2 * VEC * 256 / kLaneReduceRounds : 1];
     __shared__ int last_flag;
     const ChanThread t = chan_thread<VEC>(cp, vch);
     // inference: eval-mode BN affine (+ReLU) applied to the sum before it is stored (STATS == false only)
