@@ -8,6 +8,10 @@
 // chunk of <= 64 vectors when the tensor has more channels than that.
 #include <stdlib.h>
 
+#include <map>
+#include <mutex>
+#include <utility>
+
 #include "common.cuh"
 
 namespace msx {
@@ -424,6 +428,194 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const T* __restrict__
     }
 }
 
+// ---- bf16 fast paths of the two BatchNorm-backward passes -------------------------------------------------------------
+// ncu (round 2, C = 17 at 16 x 352 x 352): the generic kernels above sat at 39 % (reduce) and 56 % (apply) of DRAM peak with
+// 147 / 98 registers per thread - ONE or two CTAs per SM, 12-23 % of the warp slots, i.e. too few bytes in flight, not a
+// bandwidth limit.  These variants keep the per-channel state small (fp32 partial sums for the few dozen pixels a thread
+// visits, converted to double only for the cross-thread tree; folded coefficients), hold loaded vectors packed, and are
+// compiled for three CTAs per SM with eight 16-byte loads in flight per thread.  fp32 tensors (the parity mode) keep the
+// double-accumulating generic kernels.
+__device__ __forceinline__ uint4 ldg16(const bf16* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+__device__ __forceinline__ void unpack8(const uint4& r, float (&v)[8]) {
+    v[0] = __uint_as_float(r.x << 16); v[1] = __uint_as_float(r.x & 0xffff0000u);
+    v[2] = __uint_as_float(r.y << 16); v[3] = __uint_as_float(r.y & 0xffff0000u);
+    v[4] = __uint_as_float(r.z << 16); v[5] = __uint_as_float(r.z & 0xffff0000u);
+    v[6] = __uint_as_float(r.w << 16); v[7] = __uint_as_float(r.w & 0xffff0000u);
+}
+
+// 16 doubles through an 8-wide tree in two rounds (16 KB of shared memory instead of 32)
+__device__ inline void lane_reduce_2x8(double (&v)[16], double* sh, int vch, int lane, int lanes) {
+    int p2 = 1;
+    while (p2 < lanes) p2 <<= 1;
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        if (r) __syncthreads();
+#pragma unroll
+        for (int j = 0; j < 8; ++j) sh[j * 256 + threadIdx.x] = v[r * 8 + j];
+        __syncthreads();
+        for (int off = p2 >> 1; off > 0; off >>= 1) {
+            if (lane < off && lane + off < lanes) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) sh[j * 256 + threadIdx.x] += sh[j * 256 + threadIdx.x + off * vch];
+            }
+            __syncthreads();
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[r * 8 + j] = sh[j * 256 + threadIdx.x];
+    }
+}
+
+__global__ void __launch_bounds__(256, 3) bn_bwd_reduce_bf16_kernel(const bf16* __restrict__ x, int ldx, const bf16* __restrict__ dz, int lddz,
+                                                                    int64_t pixels, int cp, int vch, int channels,
+                                                                    const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                                    const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                                    int relu, double* partials, const BnBwdFinalize fin) {
+    __shared__ double shm[8 * 256];
+    __shared__ int last_flag;
+    const ChanThread t = chan_thread<8>(cp, vch);
+    float mu[8], sc[8], be[8], fs[8], fq[8];          // sc = invstd * gamma; fq = sum g * (x - mean), scaled by invstd at the end
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int c = t.c0 + j;
+        const bool ok = t.active && c < channels;
+        mu[j] = ok ? mean[c] : 0.f;
+        sc[j] = ok ? invstd[c] * gamma[c] : 0.f;
+        be[j] = ok ? beta[c] : 0.f;
+        fs[j] = 0.f; fq[j] = 0.f;
+    }
+    if (t.active) {
+        const int64_t step = (int64_t)gridDim.x * t.lanes;
+        int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane;
+        auto body = [&](const uint4& rv, const uint4& rg) {
+            float v[8], g[8];
+            unpack8(rv, v);
+            unpack8(rg, g);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float d = v[j] - mu[j];
+                const float out = d * sc[j] + be[j];             // the forward's expression: same ReLU mask
+                const float gg = (relu && !(out > 0.f)) ? 0.f : g[j];
+                fs[j] += gg;
+                fq[j] = fmaf(gg, d, fq[j]);
+            }
+        };
+        for (; p + 3 * step < pixels; p += 4 * step) {           // 8 independent 16 B loads in flight per thread
+            uint4 rv[4], rg[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                rv[u] = ldg16(x + (p + u * step) * ldx + t.c0);
+                rg[u] = ldg16(dz + (p + u * step) * lddz + t.c0);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) body(rv[u], rg[u]);
+        }
+        for (; p < pixels; p += step) body(ldg16(x + p * ldx + t.c0), ldg16(dz + p * lddz + t.c0));
+    }
+    double acc[16];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int c = t.c0 + j;
+        acc[j] = (double)fs[j];
+        acc[8 + j] = (t.active && c < channels) ? (double)fq[j] * (double)invstd[c] : 0.0;
+    }
+    lane_reduce_2x8(acc, shm, vch, t.lane, t.lanes);
+    if (t.active && t.lane == 0) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            partials[((int64_t)blockIdx.x * 2 + 0) * cp + t.c0 + j] = acc[j];
+            partials[((int64_t)blockIdx.x * 2 + 1) * cp + t.c0 + j] = acc[8 + j];
+        }
+    }
+    if (fin.ticket && ticket_is_last(fin.ticket, gridDim.x * gridDim.y, &last_flag)) bn_bwd_finalize_all(fin, partials, gridDim.x);
+}
+
+// dx = gamma*invstd*(g - c1 - xhat*c2) with the per-channel constants folded: dx = a*g + e*(x - mean) + f,
+// a = gamma*invstd, e = -a*invstd*c2, f = -a*c1
+__global__ void __launch_bounds__(256, 3) bn_bwd_apply_bf16_kernel(const bf16* __restrict__ x, int ldx, const bf16* __restrict__ dz, int lddz,
+                                                                   bf16* __restrict__ dx, int lddx, int64_t pixels, int cp, int vch, int channels,
+                                                                   const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                                   const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                                   const float* __restrict__ c1, const float* __restrict__ c2, int relu) {
+    const ChanThread t = chan_thread<8>(cp, vch);
+    if (!t.active) return;
+    float mu[8], sc[8], be[8], e[8], f[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int c = t.c0 + j;
+        const bool ok = c < channels;
+        const float is = ok ? invstd[c] : 0.f;
+        mu[j] = ok ? mean[c] : 0.f;
+        sc[j] = ok ? is * gamma[c] : 0.f;
+        be[j] = ok ? beta[c] : 0.f;
+        e[j] = ok ? -sc[j] * is * c2[c] : 0.f;
+        f[j] = ok ? -sc[j] * c1[c] : 0.f;
+    }
+    const int64_t step = (int64_t)gridDim.x * t.lanes;
+    int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane;
+    auto body = [&](const uint4& rv, const uint4& rg, bf16* out) {
+        float v[8], g[8];
+        unpack8(rv, v);
+        unpack8(rg, g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float d = v[j] - mu[j];
+            const float o = d * sc[j] + be[j];
+            const float gg = (relu && !(o > 0.f)) ? 0.f : g[j];
+            v[j] = fmaf(sc[j], gg, fmaf(e[j], d, f[j]));
+        }
+        Vec<bf16>::store(out, v);
+    };
+    for (; p + 3 * step < pixels; p += 4 * step) {
+        uint4 rv[4], rg[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            rv[u] = ldg16(x + (p + u * step) * ldx + t.c0);
+            rg[u] = ldg16(dz + (p + u * step) * lddz + t.c0);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) body(rv[u], rg[u], dx + (p + u * step) * lddx + t.c0);
+    }
+    for (; p < pixels; p += step) body(ldg16(x + p * ldx + t.c0), ldg16(dz + p * lddz + t.c0), dx + p * lddx + t.c0);
+}
+
+// y = relu((x - mean) * (invstd * gamma) + beta), bf16: packed loads, four pixels in flight, grid = one resident wave
+__global__ void __launch_bounds__(256, 4) bn_apply_bf16_kernel(const bf16* __restrict__ x, int ldx, bf16* __restrict__ z, int ldz,
+                                                               int64_t pixels, int cp, int vch, int channels,
+                                                               const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                               const float* __restrict__ gamma, const float* __restrict__ beta, int relu) {
+    const ChanThread t = chan_thread<8>(cp, vch);
+    if (!t.active) return;
+    float mu[8], sc[8], sh[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int c = t.c0 + j;
+        const bool ok = c < channels;
+        mu[j] = ok ? mean[c] : 0.f;
+        sc[j] = ok ? invstd[c] * gamma[c] : 0.f;
+        sh[j] = ok ? beta[c] : 0.f;
+    }
+    const int64_t step = (int64_t)gridDim.x * t.lanes;
+    int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane;
+    auto body = [&](const uint4& rv, bf16* out) {
+        float v[8];
+        unpack8(rv, v);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float r = (v[j] - mu[j]) * sc[j] + sh[j];
+            v[j] = relu ? fmaxf(r, 0.f) : r;
+        }
+        Vec<bf16>::store(out, v);
+    };
+    for (; p + 3 * step < pixels; p += 4 * step) {
+        uint4 rv[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) rv[u] = ldg16(x + (p + u * step) * ldx + t.c0);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) body(rv[u], z + (p + u * step) * ldz + t.c0);
+    }
+    for (; p < pixels; p += step) body(ldg16(x + p * ldx + t.c0), z + p * ldz + t.c0);
+}
+
 // ---- n-way sum (+ nearest 2x upsample of input 0) with fused statistics --------------------
 struct SumArgs {
     const void* x[8];
@@ -514,6 +706,112 @@ __global__ void __launch_bounds__(256, MSX_BN_MINBLOCKS) sum_stats_kernel(SumArg
         for (int j = 0; j < VEC; ++j) {
             partials[((int64_t)blockIdx.x * 2 + 0) * cp + t.c0 + j] = acc[j];
             partials[((int64_t)blockIdx.x * 2 + 1) * cp + t.c0 + j] = acc[VEC + j];
+        }
+    }
+    if (partials && fin.ticket && ticket_is_last(fin.ticket, gridDim.x * gridDim.y, &last_flag)) bn_finalize_all(fin, gridDim.x);
+}
+
+// bf16 fast path of the n-way sum (see the note above the BatchNorm-backward fast paths): U pixels x NMAX inputs = eight
+// packed 16-byte loads in flight per thread, fp32 running statistics of the stored (bf16-rounded) sums.
+template <int U, int NMAX, bool STATS>
+__device__ __forceinline__ void sum_pixels_bf16(const SumArgs& a, int up2x, int H, int W, const int64_t (&p)[U], int c0, bf16* __restrict__ s, int lds,
+                                                const float (&asc)[8], const float (&ash)[8], bool affine, int relu, float (&fs)[8], float (&fq)[8]) {
+    uint4 r[U][NMAX];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        int64_t p0 = p[u];
+        if (up2x) {
+            const int xw = (int)(p[u] % W);
+            const int64_t q = p[u] / W;
+            const int yh = (int)(q % H);
+            p0 = ((q / H) * (H >> 1) + (yh >> 1)) * (W >> 1) + (xw >> 1);
+        }
+        r[u][0] = ldg16(static_cast<const bf16*>(a.x[0]) + p0 * a.ld[0] + c0);
+#pragma unroll
+        for (int i = 1; i < NMAX; ++i)
+            if (i < a.n) r[u][i] = ldg16(static_cast<const bf16*>(a.x[i]) + p[u] * a.ld[i] + c0);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        float v[8];
+        unpack8(r[u][0], v);
+#pragma unroll
+        for (int i = 1; i < NMAX; ++i)
+            if (i < a.n) {
+                float w[8];
+                unpack8(r[u][i], w);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[j] += w[j];
+            }
+        if (!STATS && (affine || relu)) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (affine) v[j] = fmaf(v[j], asc[j], ash[j]);
+                if (relu) v[j] = fmaxf(v[j], 0.f);
+            }
+        }
+        uint32_t w4[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+            w4[j] = *reinterpret_cast<uint32_t*>(&h);
+        }
+        *reinterpret_cast<uint4*>(s + p[u] * lds + c0) = make_uint4(w4[0], w4[1], w4[2], w4[3]);
+        if (STATS) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float lo = __uint_as_float(w4[j] << 16), hi = __uint_as_float(w4[j] & 0xffff0000u);
+                fs[2 * j] += lo; fq[2 * j] = fmaf(lo, lo, fq[2 * j]);
+                fs[2 * j + 1] += hi; fq[2 * j + 1] = fmaf(hi, hi, fq[2 * j + 1]);
+            }
+        }
+    }
+}
+
+template <bool STATS>
+__global__ void __launch_bounds__(256, 3) sum_bf16_kernel(SumArgs a, int up2x, int H, int W, bf16* __restrict__ s, int lds, int64_t pixels,
+                                                          int cp, int vch, double* partials, const float* __restrict__ scale,
+                                                          const float* __restrict__ shift, int relu, const BnFinalize fin) {
+    __shared__ double sh[STATS ? 8 * 256 : 1];
+    __shared__ int last_flag;
+    const ChanThread t = chan_thread<8>(cp, vch);
+    float asc[8], ash[8], fs[8], fq[8];
+    const bool affine = !STATS && scale != nullptr;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        asc[j] = (affine && t.active) ? scale[t.c0 + j] : 1.f;
+        ash[j] = (affine && t.active) ? shift[t.c0 + j] : 0.f;
+        fs[j] = 0.f; fq[j] = 0.f;
+    }
+    if (t.active) {
+        const int64_t step = (int64_t)gridDim.x * t.lanes;
+        int64_t p = (int64_t)blockIdx.x * t.lanes + t.lane;
+        if (a.n <= 2) {
+            for (; p + 3 * step < pixels; p += 4 * step) {
+                const int64_t pp[4] = {p, p + step, p + 2 * step, p + 3 * step};
+                sum_pixels_bf16<4, 2, STATS>(a, up2x, H, W, pp, t.c0, s, lds, asc, ash, affine, relu, fs, fq);
+            }
+        } else if (a.n <= 4) {
+            for (; p + step < pixels; p += 2 * step) {
+                const int64_t pp[2] = {p, p + step};
+                sum_pixels_bf16<2, 4, STATS>(a, up2x, H, W, pp, t.c0, s, lds, asc, ash, affine, relu, fs, fq);
+            }
+        }
+        for (; p < pixels; p += step) {
+            const int64_t pp[1] = {p};
+            sum_pixels_bf16<1, 8, STATS>(a, up2x, H, W, pp, t.c0, s, lds, asc, ash, affine, relu, fs, fq);
+        }
+    }
+    if (!STATS) return;
+    double acc[16];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { acc[j] = (double)fs[j]; acc[8 + j] = (double)fq[j]; }
+    lane_reduce_2x8(acc, sh, vch, t.lane, t.lanes);
+    if (t.active && t.lane == 0 && partials) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            partials[((int64_t)blockIdx.x * 2 + 0) * cp + t.c0 + j] = acc[j];
+            partials[((int64_t)blockIdx.x * 2 + 1) * cp + t.c0 + j] = acc[8 + j];
         }
     }
     if (partials && fin.ticket && ticket_is_last(fin.ticket, gridDim.x * gridDim.y, &last_flag)) bn_finalize_all(fin, gridDim.x);
@@ -652,12 +950,50 @@ __global__ void channel_sum_finalize_kernel(const double* __restrict__ partials,
     if ((threadIdx.x & 31) == 0) out[c] = (float)s;
 }
 
+// CTAs of `kernel` (256 threads, no dynamic smem) that one resident wave holds on the current device; cached per kernel
+inline int resident_ctas(const void* kernel) {
+    static std::mutex mu;
+    static std::map<std::pair<int, const void*>, int> cache;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> lk(mu);
+    auto it = cache.find({dev, kernel});
+    if (it != cache.end()) return it->second;
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, 256, 0) != cudaSuccess || per_sm < 1) per_sm = 2;
+    const int n = per_sm * kNumSMs;
+    cache[{dev, kernel}] = n;
+    return n;
+}
+inline int wave_grid(const void* kernel, int64_t pixels, int lanes, int per_iter, int cap = 1 << 30) {
+    int64_t g = cdiv64(pixels, (int64_t)lanes * per_iter);
+    const int r = resident_ctas(kernel);
+    if (g > r) g = r;
+    if (g > cap) g = cap;
+    return g < 1 ? 1 : (int)g;
+}
+
 inline int check_ld(int ld, int channels, const char* what) {
     if (ld % 8 != 0 || ld < round_up(channels, 8))
         return set_error(MSX_ERR_INVALID, "%s: pixel stride %d must be a multiple of 8 and >= round_up(%d, 8)", what, ld, channels);
     return MSX_OK;
 }
 
+}  // namespace
+
+namespace {
+template <bool STATS>
+int sum_launch_bf16(const SumArgs& a, int up2x, int h, int w, void* s, int lds, int64_t pixels, int channels, double* partials,
+                    const float* scale, const float* shift, int relu, const BnFinalize& fin, int* nblk_out, cudaStream_t st) {
+    const ChanCfg c = chan_cfg<8>(channels);
+    const int per_iter = a.n <= 2 ? 4 : (a.n <= 4 ? 2 : 1);
+    const int g = wave_grid(reinterpret_cast<const void*>(sum_bf16_kernel<STATS>), pixels, c.lanes, per_iter * 2, STATS ? kMaxPartialBlocks : (1 << 30));
+    { ProfScope ps__(K_SUM, st, (double)pixels * channels * 2.0 * (a.n + 1.0), 0);
+      sum_bf16_kernel<STATS><<<dim3(g, c.nchunk), 256, 0, st>>>(a, up2x, h, w, static_cast<bf16*>(s), lds, pixels, c.cp, c.vch, partials, scale, shift, relu, fin); }
+    if (nblk_out) *nblk_out = g;
+    MSX_LAUNCH_CHECK();
+    return MSX_OK;
+}
 }  // namespace
 
 // ---- launchers (internal) -------------------------------------------------------------------
@@ -738,6 +1074,14 @@ int bn_apply_launch(int dtype, const void* x, int ldx, void* z, int ldz, int64_t
                     cudaStream_t st) {
     MSX_TRY(check_ld(ldx, channels, "bn_apply x"));
     MSX_TRY(check_ld(ldz, channels, "bn_apply z"));
+    if (dtype == MSX_BF16) {
+        const ChanCfg c = chan_cfg<8>(channels);
+        const int g = wave_grid(reinterpret_cast<const void*>(bn_apply_bf16_kernel), pixels, c.lanes, 4);
+        { ProfScope ps__(K_BN_APPLY, st, 2.0 * (double)pixels * channels * 2.0, 0); bn_apply_bf16_kernel<<<dim3(g, c.nchunk), 256, 0, st>>>(
+            static_cast<const bf16*>(x), ldx, static_cast<bf16*>(z), ldz, pixels, c.cp, c.vch, channels, mean, invstd, gamma, beta, relu); }
+        MSX_LAUNCH_CHECK();
+        return MSX_OK;
+    }
     MSX_DISPATCH_DTYPE(dtype, T, {
         const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
         { ProfScope ps__(K_BN_APPLY, st, 2.0 * (double)pixels * channels * (double)sizeof(T), 0); bn_apply_kernel<T><<<dim3(stream_grid(pixels, c.lanes), c.nchunk), 256, 0, st>>>(
@@ -763,6 +1107,15 @@ int bn_bwd_reduce_launch(int dtype, const void* x, int ldx, const void* dz, int 
     }
     f.sums = sums; f.dgamma = dgamma; f.dbeta = dbeta; f.c1 = c1; f.c2 = c2;
     f.count = pixels; f.channels = channels; f.cp = round_up(channels, 8); f.eval_mode = (flags & MSX_BN_EVAL) ? 1 : 0;
+    if (dtype == MSX_BF16) {
+        const ChanCfg c = chan_cfg<8>(channels);
+        const int g = wave_grid(reinterpret_cast<const void*>(bn_bwd_reduce_bf16_kernel), pixels, c.lanes, 8, kMaxPartialBlocks);
+        { ProfScope ps__(K_BN_BWD_REDUCE, st, 2.0 * (double)pixels * channels * 2.0, 0); bn_bwd_reduce_bf16_kernel<<<dim3(g, c.nchunk), 256, 0, st>>>(
+            static_cast<const bf16*>(x), ldx, static_cast<const bf16*>(dz), lddz, pixels, c.cp, c.vch, channels, mean, invstd, gamma, beta, relu, partials, f); }
+        if (!f.ticket) { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_bwd_finalize_kernel<<<(f.cp * 32 + 127) / 128, 128, 0, st>>>(partials, g, f); }
+        MSX_LAUNCH_CHECK();
+        return MSX_OK;
+    }
     MSX_DISPATCH_DTYPE(dtype, T, {
         const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
         const int g = reduce_grid(pixels, c.lanes);
@@ -779,6 +1132,15 @@ int bn_bwd_apply_launch(int dtype, const void* x, int ldx, const void* dz, int l
                         const float* c1, const float* c2, void* dx, int lddx, cudaStream_t st) {
     const int relu = flags & MSX_BN_RELU;
     MSX_TRY(check_ld(lddx, channels, "bn_bwd dx"));
+    if (dtype == MSX_BF16) {
+        const ChanCfg c = chan_cfg<8>(channels);
+        const int g = wave_grid(reinterpret_cast<const void*>(bn_bwd_apply_bf16_kernel), pixels, c.lanes, 4);
+        { ProfScope ps__(K_BN_BWD_APPLY, st, 3.0 * (double)pixels * channels * 2.0, 0); bn_bwd_apply_bf16_kernel<<<dim3(g, c.nchunk), 256, 0, st>>>(
+            static_cast<const bf16*>(x), ldx, static_cast<const bf16*>(dz), lddz, static_cast<bf16*>(dx), lddx, pixels, c.cp, c.vch, channels,
+            mean, invstd, gamma, beta, c1, c2, relu); }
+        MSX_LAUNCH_CHECK();
+        return MSX_OK;
+    }
     MSX_DISPATCH_DTYPE(dtype, T, {
         const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
         { ProfScope ps__(K_BN_BWD_APPLY, st, 3.0 * (double)pixels * channels * (double)sizeof(T), 0); bn_bwd_apply_kernel<T><<<dim3(stream_grid(pixels, c.lanes), c.nchunk), 256, 0, st>>>(
@@ -854,6 +1216,7 @@ int msx_sum_bn_act_fwd(int dtype, int n_in, const void* const* host_xs, const in
             a.x[i] = host_xs[i];
             a.ld[i] = host_ldxs[i];
         }
+        if (dtype == MSX_BF16) return sum_launch_bf16<false>(a, up2x_first, h, w, z, ldz, pixels, channels, nullptr, scale, shift, relu, BnFinalize{}, nullptr, st);
         MSX_DISPATCH_DTYPE(dtype, T, {
             const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
             { ProfScope ps__(K_SUM, st, (double)pixels * channels * (double)sizeof(T) * (n_in + 1.0), 0); sum_stats_kernel<T, false><<<dim3(stream_grid(pixels, c.lanes), c.nchunk), 256, 0, st>>>(
@@ -872,6 +1235,9 @@ int msx_sum_bn_act_fwd(int dtype, int n_in, const void* const* host_xs, const in
             a.x[i] = host_xs[i];
             a.ld[i] = host_ldxs[i];
         }
+        if (dtype == MSX_BF16) {
+            MSX_TRY(sum_launch_bf16<true>(a, up2x_first, h, w, s, lds, pixels, channels, training ? partials : nullptr, nullptr, nullptr, 0, fin, &nblk, st));
+        } else
         MSX_DISPATCH_DTYPE(dtype, T, {
             const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
             nblk = reduce_grid(pixels, c.lanes);
@@ -901,6 +1267,7 @@ int msx_sum_n(int dtype, int n_in, const void* const* host_xs, const int32_t* ho
         a.x[i] = host_xs[i];
         a.ld[i] = host_ldxs[i];
     }
+    if (dtype == MSX_BF16) return sum_launch_bf16<false>(a, 0, 1, 1, out, ldout, pixels, channels, nullptr, nullptr, nullptr, 0, BnFinalize{}, nullptr, as_stream(stream));
     MSX_DISPATCH_DTYPE(dtype, T, {
         const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
         { ProfScope ps__(K_SUM, as_stream(stream), (double)pixels * channels * (double)sizeof(T) * (n_in + 1.0), 0); sum_stats_kernel<T, false><<<dim3(stream_grid(pixels, c.lanes), c.nchunk), 256, 0, as_stream(stream)>>>(
@@ -923,6 +1290,7 @@ int msx_sum_act(int dtype, int n_in, const void* const* host_xs, const int32_t* 
         a.ld[i] = host_ldxs[i];
     }
     const int64_t pixels = (int64_t)n * h * w;
+    if (dtype == MSX_BF16) return sum_launch_bf16<false>(a, up2x_first, h, w, out, ldout, pixels, channels, nullptr, nullptr, nullptr, relu, BnFinalize{}, nullptr, as_stream(stream));
     MSX_DISPATCH_DTYPE(dtype, T, {
         const ChanCfg c = chan_cfg<Vec<T>::N>(channels);
         { ProfScope ps__(K_SUM, as_stream(stream), (double)pixels * channels * (double)sizeof(T) * (n_in + 1.0), 0); sum_stats_kernel<T, false><<<dim3(stream_grid(pixels, c.lanes), c.nchunk), 256, 0, as_stream(stream)>>>(
