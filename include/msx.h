@@ -166,6 +166,29 @@ int msx_bn_act_bwd(int dtype, const void* s, int32_t lds, const void* dz, int32_
                    const float* gamma, const float* beta, const float* save_mean, const float* save_invstd,
                    int relu, void* ds, int32_t ldds, float* dgamma, float* dbeta,
                    void* ws, size_t ws_bytes, void* stream);
+/* SyncBatchNorm (utils/parallel.py:37-38: nn.SyncBatchNorm.convert_sync_batchnorm, the reference's DEFAULT synBN=True;
+ * torch/nn/modules/_functions.py SyncBatchNorm): the per-rank halves of a BatchNorm whose statistics span all ranks.  The
+ * caller all-reduces (sum) the small `sums` buffer between the halves - double[2*cp + 1], cp = round_up(channels, 8):
+ * per-channel sum, per-channel sum of squares, then this rank's sample count.
+ *   forward : msx_bn_stats_sums -> all-reduce -> msx_bn_finalize_sums (mean / invstd over ALL ranks' samples, running
+ *             statistics with the global unbiased variance, num_batches_tracked) -> msx_bn_apply
+ *   backward: msx_bn_bwd_reduce_sums (dgamma / dbeta stay per-rank, as in torch; sums = [sum g, sum g*xhat]) -> all-reduce
+ *             -> msx_bn_bwd_apply_sums (count_dev: the all-reduced forward buffer's last element)
+ * ws: msx_ws_bytes_bn(channels). */
+int msx_bn_stats_sums(int dtype, const void* x, int32_t ldx, int64_t pixels, int32_t channels, double* sums,
+                      void* ws, size_t ws_bytes, void* stream);
+int msx_bn_finalize_sums(const double* sums, int32_t channels, float eps, float momentum, float* save_mean, float* save_invstd,
+                         float* running_mean, float* running_var, int64_t* num_batches_tracked, void* stream);
+int msx_bn_apply(int dtype, const void* x, int32_t ldx, void* z, int32_t ldz, int64_t pixels, int32_t channels,
+                 const float* mean, const float* invstd, const float* gamma, const float* beta, int relu, void* stream);
+int msx_bn_bwd_reduce_sums(int dtype, const void* x, int32_t ldx, const void* dz, int32_t lddz, int64_t pixels, int32_t channels,
+                           const float* gamma, const float* beta, const float* save_mean, const float* save_invstd, int relu,
+                           float* dgamma, float* dbeta, double* sums, void* ws, size_t ws_bytes, void* stream);
+int msx_bn_bwd_apply_sums(int dtype, const void* x, int32_t ldx, const void* dz, int32_t lddz, int64_t pixels, int32_t channels,
+                          const float* gamma, const float* beta, const float* save_mean, const float* save_invstd, int relu,
+                          const double* sums, const double* count_dev, void* dx, int32_t lddx,
+                          void* ws, size_t ws_bytes, void* stream);
+
 /* out = sum_i xs[i] (n_in <= 8): gradient accumulation where one activation feeds several
  * consumers (DUCK.in_bn output feeds nine convolutions, models/ducknet.py:144-149). */
 int msx_sum_n(int dtype, int n_in, const void* const* host_xs, const int32_t* host_ldxs,

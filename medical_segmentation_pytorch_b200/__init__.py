@@ -10,7 +10,7 @@ from .loss import CrossEntropyLoss, DiceBCELoss, OhemCELoss, get_loss_fn, kd_los
 from .metrics import Dice, JaccardIndex, eval_sweep, get_seg_metrics
 from .graph import CapturedStep, capture_step
 from .optim import FusedOptimizer, ModelEma, get_ema_model, get_optimizer, get_scheduler
-from .parallel import (DistributedDataParallelB200, de_parallel, destroy_ddp_process, is_parallel, parallel_model,
+from .parallel import (DistributedDataParallelB200, convert_sync_batchnorm, de_parallel, destroy_ddp_process, is_parallel, parallel_model,
                        sampler_set_epoch, set_device)
 from .teacher import SmpUnet
 from .unet import UNet
@@ -49,6 +49,6 @@ def get_teacher_model(config, device):
 
 
 __all__ = ['UNet', 'DuckNet', 'SmpUnet', 'get_model', 'get_teacher_model', 'get_loss_fn', 'kd_loss_fn', 'get_seg_metrics', 'eval_sweep', 'parallel_model',
-           'de_parallel', 'is_parallel', 'set_device', 'destroy_ddp_process', 'sampler_set_epoch', 'get_optimizer',
+           'de_parallel', 'convert_sync_batchnorm', 'is_parallel', 'set_device', 'destroy_ddp_process', 'sampler_set_epoch', 'get_optimizer',
            'get_ema_model', 'get_scheduler', 'capture_step', 'CapturedStep', 'FusedOptimizer', 'ModelEma', 'CrossEntropyLoss', 'OhemCELoss', 'DiceBCELoss',
            'JaccardIndex', 'Dice', 'DistributedDataParallelB200', 'MsxError']

@@ -70,6 +70,11 @@ def _load():
                                          p, i32, p, p, p, sz, p]),
         'msx_bn_act_bwd': (C.c_int, [C.c_int, p, i32, p, i32, i64, i32, p, p, p, p, C.c_int, p, i32, p, p, p, sz, p]),
         'msx_bn_act_bwd_static': (C.c_int, [C.c_int, p, i32, p, i32, i64, i32, p, p, p, p, C.c_int, p, i32, p, p, p]),
+        'msx_bn_stats_sums': (C.c_int, [C.c_int, p, i32, i64, i32, p, p, sz, p]),
+        'msx_bn_finalize_sums': (C.c_int, [p, i32, f32, f32, p, p, p, p, p, p]),
+        'msx_bn_apply': (C.c_int, [C.c_int, p, i32, p, i32, i64, i32, p, p, p, p, C.c_int, p]),
+        'msx_bn_bwd_reduce_sums': (C.c_int, [C.c_int, p, i32, p, i32, i64, i32, p, p, p, p, C.c_int, p, p, p, p, sz, p]),
+        'msx_bn_bwd_apply_sums': (C.c_int, [C.c_int, p, i32, p, i32, i64, i32, p, p, p, p, C.c_int, p, p, p, i32, p, sz, p]),
         'msx_sum_n': (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(i32), i64, i32, p, i32, p]),
         'msx_sum_act': (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_void_p), C.POINTER(i32), C.c_int, i32, i32, i32, i32, C.c_int, p, i32, p]),
         'msx_upsample2x_bwd': (C.c_int, [C.c_int, p, i32, i32, i32, i32, i32, p, i32, p]),

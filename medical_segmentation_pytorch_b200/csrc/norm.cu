@@ -150,6 +150,7 @@ __global__ void bn_finalize_kernel(int nblk, const BnFinalize f) {
     const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (c == 0 && lane == 0 && f.nbt && !f.sums) *f.nbt += 1;
+    if (c == 0 && lane == 0 && f.sums) f.sums[2 * f.cp] = (double)f.count;      // this rank's sample count, reduced with the sums
     if (c >= f.cp) return;
     if (c >= f.channels) {
         if (lane == 0) {
@@ -166,11 +167,12 @@ __global__ void bn_finalize_kernel(int nblk, const BnFinalize f) {
 }
 
 // SyncBatchNorm: per-channel [sum, sum of squares] (doubles, already reduced over ranks) -> mean / invstd / running stats
-__global__ void bn_finalize_sums_kernel(const double* __restrict__ sums, const BnFinalize f) {
+__global__ void bn_finalize_sums_kernel(const double* __restrict__ sums, BnFinalize f) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c == 0 && f.nbt) *f.nbt += 1;
     if (c >= f.cp) return;
     if (c >= f.channels) { f.mean[c] = 0.f; f.invstd[c] = 0.f; return; }
+    f.count = (long long)(sums[2 * f.cp] + 0.5);               // samples over all ranks
     bn_finalize_one(f, c, sums[c], sums[f.cp + c]);
 }
 
@@ -298,9 +300,10 @@ __global__ void bn_bwd_finalize_kernel(const double* partials, int nblk, const B
     f.c2[c] = f.eval_mode ? 0.f : (float)(q / (double)f.count);
 }
 
-__global__ void bn_bwd_coeffs_kernel(const double* __restrict__ sums, int cp, int channels, double count, float* c1, float* c2) {
+__global__ void bn_bwd_coeffs_kernel(const double* __restrict__ sums, int cp, int channels, const double* __restrict__ count_dev, float* c1, float* c2) {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= cp) return;
+    const double count = *count_dev;
     c1[c] = c < channels ? (float)(sums[c] / count) : 0.f;
     c2[c] = c < channels ? (float)(sums[cp + c] / count) : 0.f;
 }
@@ -1306,6 +1309,57 @@ int msx_bn_act_bwd(int dtype, const void* s, int32_t lds, const void* dz, int32_
     MSX_REQUIRE(s && dz && ds && gamma && beta && save_mean && save_invstd, "bn_act_bwd: null pointer");
     return bn_bwd_launch(dtype, s, lds, dz, lddz, pixels, channels, gamma, beta, save_mean, save_invstd, relu, ds, ldds,
                          dgamma, dbeta, ws, ws_bytes, as_stream(stream));
+}
+
+// ---- SyncBatchNorm pieces (utils/parallel.py:37-38): the per-rank halves around the caller's all-reduce ----
+int msx_bn_stats_sums(int dtype, const void* x, int32_t ldx, int64_t pixels, int32_t channels, double* sums, void* ws, size_t ws_bytes,
+                      void* stream) {
+    MSX_REQUIRE(x && sums && ws, "bn_stats_sums: null pointer");
+    if (ws_bytes < bn_partials_bytes(channels)) return set_error(MSX_ERR_WORKSPACE, "bn_stats_sums: workspace %zu < %zu", ws_bytes, bn_partials_bytes(channels));
+    BnFinalize f;
+    MSX_TRY(bn_finalize_args(&f, static_cast<double*>(ws), channels, pixels, 0.f, 0.f, nullptr, nullptr, nullptr, nullptr, nullptr, sums));
+    f.ticket = nullptr;
+    return bn_stats_launch(dtype, x, ldx, pixels, channels, static_cast<double*>(ws), &f, nullptr, as_stream(stream));
+}
+
+int msx_bn_finalize_sums(const double* sums, int32_t channels, float eps, float momentum, float* save_mean, float* save_invstd,
+                         float* running_mean, float* running_var, int64_t* num_batches_tracked, void* stream) {
+    MSX_REQUIRE(sums && save_mean && save_invstd, "bn_finalize_sums: null pointer");
+    BnFinalize f;
+    MSX_TRY(bn_finalize_args(&f, nullptr, channels, 0, eps, momentum, save_mean, save_invstd, running_mean, running_var, num_batches_tracked, nullptr));
+    f.ticket = nullptr;
+    return bn_finalize_sums_launch(sums, f, as_stream(stream));
+}
+
+int msx_bn_apply(int dtype, const void* x, int32_t ldx, void* z, int32_t ldz, int64_t pixels, int32_t channels, const float* mean,
+                 const float* invstd, const float* gamma, const float* beta, int relu, void* stream) {
+    MSX_REQUIRE(x && z && mean && invstd && gamma && beta, "bn_apply: null pointer");
+    return bn_apply_launch(dtype, x, ldx, z, ldz, pixels, channels, mean, invstd, gamma, beta, relu, as_stream(stream));
+}
+
+int msx_bn_bwd_reduce_sums(int dtype, const void* x, int32_t ldx, const void* dz, int32_t lddz, int64_t pixels, int32_t channels,
+                           const float* gamma, const float* beta, const float* save_mean, const float* save_invstd, int relu,
+                           float* dgamma, float* dbeta, double* sums, void* ws, size_t ws_bytes, void* stream) {
+    MSX_REQUIRE(x && dz && gamma && beta && save_mean && save_invstd && sums && ws, "bn_bwd_reduce_sums: null pointer");
+    if (ws_bytes < bn_partials_bytes(channels)) return set_error(MSX_ERR_WORKSPACE, "bn_bwd_reduce_sums: workspace %zu < %zu", ws_bytes, bn_partials_bytes(channels));
+    const int cp = round_up(channels, 8);
+    double* partials = static_cast<double*>(ws);
+    float* c1 = reinterpret_cast<float*>(partials + (size_t)kMaxPartialBlocks * 2 * cp);
+    return bn_bwd_reduce_launch(dtype, x, ldx, dz, lddz, pixels, channels, gamma, beta, save_mean, save_invstd, relu, dgamma, dbeta,
+                                partials, c1, c1 + cp, sums, as_stream(stream));
+}
+
+int msx_bn_bwd_apply_sums(int dtype, const void* x, int32_t ldx, const void* dz, int32_t lddz, int64_t pixels, int32_t channels,
+                          const float* gamma, const float* beta, const float* save_mean, const float* save_invstd, int relu,
+                          const double* sums, const double* count_dev, void* dx, int32_t lddx, void* ws, size_t ws_bytes, void* stream) {
+    MSX_REQUIRE(x && dz && dx && gamma && beta && save_mean && save_invstd && sums && count_dev && ws, "bn_bwd_apply_sums: null pointer");
+    if (ws_bytes < bn_partials_bytes(channels)) return set_error(MSX_ERR_WORKSPACE, "bn_bwd_apply_sums: workspace %zu < %zu", ws_bytes, bn_partials_bytes(channels));
+    const int cp = round_up(channels, 8);
+    float* c1 = reinterpret_cast<float*>(static_cast<double*>(ws) + (size_t)kMaxPartialBlocks * 2 * cp);
+    cudaStream_t st = as_stream(stream);
+    { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_bwd_coeffs_kernel<<<(cp + 127) / 128, 128, 0, st>>>(sums, cp, channels, count_dev, c1, c1 + cp); }
+    MSX_LAUNCH_CHECK();
+    return bn_bwd_apply_launch(dtype, x, ldx, dz, lddz, pixels, channels, gamma, beta, save_mean, save_invstd, relu, c1, c1 + cp, dx, lddx, st);
 }
 
 int msx_upsample2x_bwd(int dtype, const void* ds, int32_t ldds, int32_t n, int32_t h, int32_t w, int32_t channels,

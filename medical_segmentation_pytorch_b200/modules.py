@@ -51,11 +51,26 @@ def _geom_of(conv):
                     out_pad=conv.output_padding[0] if t else 0)
 
 
+def _sync_group(bn):
+    """The process group a BatchNorm synchronises its batch statistics over (parallel_model with synBN=True), or None."""
+    g = getattr(bn, '_msx_sync_group', None)
+    if g is None or not bn.training:
+        return None
+    import torch.distributed as dist
+    return g if dist.is_initialized() and dist.get_world_size(g) > 1 else None
+
+
 def conv_bn_act(x, conv, bn, relu, slot=None):
     """Shared forward of ConvBNAct / DeConvBNAct."""
     if not hasattr(conv, '_msx_geom'):
         conv._msx_geom = _geom_of(conv)
     momentum = 0.1 if bn.momentum is None else bn.momentum
+    group = _sync_group(bn)
+    if group is not None:                       # SyncBatchNorm: conv, then statistics over all ranks (ops.SyncBNActFn)
+        y = ops.Conv2dFn.apply(x.t, conv.weight, conv._msx_geom, conv.bias)
+        z = ops.SyncBNActFn.apply(y, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.num_batches_tracked,
+                                  conv.out_channels, bn.eps, momentum, relu, slot, group)
+        return Act(z, conv.out_channels)
     # inference: eval mode and nothing that could be differentiated -> BN + ReLU run in the conv epilogue
     infer = not bn.training and not (torch.is_grad_enabled() and (x.t.requires_grad or conv.weight.requires_grad or bn.weight.requires_grad
                                                                   or bn.bias.requires_grad or (conv.bias is not None and conv.bias.requires_grad)))
@@ -74,6 +89,11 @@ def sum_bn_act(xs, bn, relu=1, up2x=False, slot=None):
     """(sum of Acts) -> BN -> ReLU; xs[0] may be at half resolution when up2x."""
     c = xs[0].c
     momentum = 0.1 if bn.momentum is None else bn.momentum
+    group = _sync_group(bn)
+    if group is not None:
+        s = ops.SumFn.apply(c, up2x, *[a.t for a in xs]) if (len(xs) > 1 or up2x) else xs[0].t
+        return Act(ops.SyncBNActFn.apply(s, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.num_batches_tracked,
+                                         c, bn.eps, momentum, relu, slot, group), c)
     infer = not bn.training and not (torch.is_grad_enabled() and (bn.weight.requires_grad or bn.bias.requires_grad
                                                                   or any(a.t.requires_grad for a in xs)))
     z = ops.SumBNActFn.apply(bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.num_batches_tracked, c, bn.eps,

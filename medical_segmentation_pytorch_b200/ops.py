@@ -260,7 +260,9 @@ class Conv2dFn(torch.autograd.Function):
     """Bias-free conv without BN (ResidualBlock.upper_branch, models/ducknet.py:93) -> msx_conv2d_{fwd,bwd}."""
 
     @staticmethod
-    def forward(ctx, x, weight, g):
+    def forward(ctx, x, weight, g, *rest):             # rest: optionally the bias (ConvTranspose2d before a SyncBatchNorm)
+        bias = rest[0] if rest else None
+        ctx.nrest = len(rest)
         n, h, w, _ = x.shape
         oh, ow = g.out_hw(h, w)
         cp = rup(g.cout)
@@ -268,8 +270,9 @@ class Conv2dFn(torch.autograd.Function):
         d = _desc(g, x, cp, oh, ow)
         pre = packplan.lookup(_f32(weight))
         pk = pre[0] if pre else L.scratch('pack', lib.msx_conv_packed_bytes(C.byref(d)), x.device)
-        L.check(lib.msx_conv2d_fwd(C.byref(d), L.ptr(x), None if pre else L.ptr(weight), None, L.ptr(pk), L.ptr(y), L.stream()))
+        L.check(lib.msx_conv2d_fwd(C.byref(d), L.ptr(x), None if pre else L.ptr(weight), L.ptr(_f32(bias)), L.ptr(pk), L.ptr(y), L.stream()))
         ctx.d, ctx.pk_b = d, (pre[1] if pre else None)
+        ctx.bias = bias
         ctx.save_for_backward(x, weight)
         return y
 
@@ -283,11 +286,14 @@ class Conv2dFn(torch.autograd.Function):
             d.ldy = ld_of(dy)
         dx = _grad_like_input(x) if ctx.needs_input_grad[0] else None
         dw = _pgrad(weight)
+        bias = ctx.bias
+        db = _pgrad(bias) if bias is not None else None
         ws = L.workspace(lib.msx_ws_bytes_conv(C.byref(d)), x.device)
         pk = ctx.pk_b if ctx.pk_b is not None else L.scratch('pack', lib.msx_conv_packed_bytes(C.byref(d)), x.device)
-        L.check(lib.msx_conv2d_bwd(C.byref(d), L.ptr(x), None if ctx.pk_b is not None else L.ptr(weight), L.ptr(dy), L.ptr(pk), L.ptr(dx), L.ptr(dw), None,
+        L.check(lib.msx_conv2d_bwd(C.byref(d), L.ptr(x), None if ctx.pk_b is not None else L.ptr(weight), L.ptr(dy), L.ptr(pk), L.ptr(dx), L.ptr(dw), L.ptr(db),
                                    L.ptr(ws), ws.numel(), L.stream()))
-        return dx, _pdone(weight, dw), None
+        db = _pdone(bias, db) if bias is not None else None          # arena order: conv.bias before conv.weight
+        return (dx, _pdone(weight, dw), None) + ((db,) if ctx.nrest else ())
 
 
 # ---- sibling branches on side streams ---------------------------------------------------------
@@ -440,6 +446,91 @@ class SumBNActFn(torch.autograd.Function):
                 grads[i] = None
         dbeta, dgamma = _pdone(beta, dbeta), _pdone(gamma, dgamma)
         return (dgamma, dbeta) + (None,) * 11 + tuple(grads)
+
+
+# ---- SyncBatchNorm (utils/parallel.py:37-38) -----------------------------------------------------
+def _all_reduce_sum(buf, group):
+    """Sum ``buf`` (a small double tensor on the device) over the ranks of ``group``.  NCCL reduces it in place on the
+    current stream (capturable); a gloo group - the CPU-side tests - gets a host round trip."""
+    import torch.distributed as dist
+    if dist.get_backend(group) == 'nccl':
+        dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=group)
+    else:
+        host = buf.cpu()
+        dist.all_reduce(host, op=dist.ReduceOp.SUM, group=group)
+        buf.copy_(host)
+
+
+class SyncBNActFn(torch.autograd.Function):
+    """BatchNorm over the samples of ALL ranks (+ReLU) of an already formed tensor ``s`` (a raw conv output or a sum):
+    msx_bn_stats_sums -> all-reduce of [sum, sum of squares, count] -> msx_bn_finalize_sums -> msx_bn_apply, and in backward
+    msx_bn_bwd_reduce_sums -> all-reduce of [sum g, sum g*xhat] -> msx_bn_bwd_apply_sums; the arithmetic of
+    torch.nn.SyncBatchNorm (weight / bias gradients stay per-rank and are averaged by DDP like every other parameter)."""
+
+    @staticmethod
+    def forward(ctx, s, gamma, beta, rm, rv, nbt, c, eps, momentum, relu, slot, group):
+        n, h, w, cp = s.shape
+        dev = s.device
+        code = L.dtype_code(s.dtype)
+        z = _out_tensor(slot, n, h, w, cp, s.dtype, dev)
+        mean = torch.empty(cp, dtype=torch.float32, device=dev)
+        invstd = torch.empty(cp, dtype=torch.float32, device=dev)
+        sums = torch.empty(2 * cp + 1, dtype=torch.float64, device=dev)
+        ws = L.workspace(lib.msx_ws_bytes_bn(c), dev)
+        L.check(lib.msx_bn_stats_sums(code, L.ptr(s), ld_of(s), n * h * w, c, L.ptr(sums), L.ptr(ws), ws.numel(), L.stream()))
+        _all_reduce_sum(sums, group)
+        L.check(lib.msx_bn_finalize_sums(L.ptr(sums), c, eps, momentum, L.ptr(mean), L.ptr(invstd), L.ptr(rm), L.ptr(rv), L.ptr(nbt), L.stream()))
+        L.check(lib.msx_bn_apply(code, L.ptr(s), ld_of(s), L.ptr(z), ld_of(z), n * h * w, c, L.ptr(mean), L.ptr(invstd),
+                                 L.ptr(_f32(gamma)), L.ptr(_f32(beta)), int(relu), L.stream()))
+        ctx.c, ctx.relu, ctx.group = c, int(relu), group
+        ctx.save_for_backward(s, gamma, beta, mean, invstd, sums)
+        return z
+
+    @staticmethod
+    def backward(ctx, dz):
+        s, gamma, beta, mean, invstd, fsums = ctx.saved_tensors
+        dz = as_act_layout(dz)
+        n, h, w, cp = s.shape
+        dev = s.device
+        code = L.dtype_code(s.dtype)
+        ds = torch.empty(n, h, w, cp, dtype=s.dtype, device=dev)
+        dgamma, dbeta = _pgrad(gamma), _pgrad(beta)
+        bsums = torch.empty(2 * cp, dtype=torch.float64, device=dev)
+        ws = L.workspace(lib.msx_ws_bytes_bn(ctx.c), dev)
+        L.check(lib.msx_bn_bwd_reduce_sums(code, L.ptr(s), ld_of(s), L.ptr(dz), ld_of(dz), n * h * w, ctx.c, L.ptr(gamma), L.ptr(beta),
+                                           L.ptr(mean), L.ptr(invstd), ctx.relu, L.ptr(dgamma), L.ptr(dbeta), L.ptr(bsums),
+                                           L.ptr(ws), ws.numel(), L.stream()))
+        _all_reduce_sum(bsums, ctx.group)
+        L.check(lib.msx_bn_bwd_apply_sums(code, L.ptr(s), ld_of(s), L.ptr(dz), ld_of(dz), n * h * w, ctx.c, L.ptr(gamma), L.ptr(beta),
+                                          L.ptr(mean), L.ptr(invstd), ctx.relu, L.ptr(bsums), L.ptr(fsums[2 * cp:]), L.ptr(ds), cp,
+                                          L.ptr(ws), ws.numel(), L.stream()))
+        dbeta, dgamma = _pdone(beta, dbeta), _pdone(gamma, dgamma)
+        return (ds, dgamma, dbeta) + (None,) * 9
+
+
+class SumFn(torch.autograd.Function):
+    """sum of inputs (first optionally nearest-2x upsampled) as its own node: the SyncBatchNorm path of sum -> BN."""
+
+    @staticmethod
+    def forward(ctx, c, up2x, *xs):
+        ref = xs[1] if up2x else xs[0]
+        n, h, w, cp = ref.shape
+        out = torch.empty(n, h, w, cp, dtype=ref.dtype, device=ref.device)
+        ptrs, lds = _ptr_arrays(xs)
+        L.check(lib.msx_sum_act(L.dtype_code(ref.dtype), len(xs), ptrs, lds, int(up2x), n, h, w, c, 0, L.ptr(out), cp, L.stream()))
+        ctx.c, ctx.up2x, ctx.nx, ctx.x0_shape = c, up2x, len(xs), xs[0].shape
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        g = as_act_layout(g)
+        grads = [g] * ctx.nx
+        if ctx.up2x:
+            n, h, w, cp = g.shape
+            da = torch.empty(ctx.x0_shape, dtype=g.dtype, device=g.device)
+            L.check(lib.msx_upsample2x_bwd(L.dtype_code(g.dtype), L.ptr(g), ld_of(g), n, h, w, ctx.c, L.ptr(da), ld_of(da), L.stream()))
+            grads[0] = da
+        return (None, None) + tuple(grads)
 
 
 def sum_n(ts, c):

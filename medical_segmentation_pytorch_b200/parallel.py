@@ -7,10 +7,9 @@ before every training forward (broadcast_buffers=True) - here as ONE flat messag
 averaged over ranks in buckets filled in reverse registration order (first bucket 1 MiB, then 25 MiB)
 and each bucket's all-reduce is issued on a side stream as soon as its last gradient has been
 written, overlapping the rest of backward.  BatchNorm statistics stay per-GPU (north_star; the
-reference's ``synBN=False`` setting - SURVEY.md §0.2 D4).
+reference's ``synBN=False`` setting - SURVEY.md §0.2 D4) unless ``config.synBN`` asks for SyncBatchNorm
+(the reference's default): then every BatchNorm reduces [sum, sum of squares, count] over the ranks (convert_sync_batchnorm).
 """
-import warnings
-
 import torch
 import torch.distributed as dist
 import torch.nn as nn
@@ -137,6 +136,17 @@ class DistributedDataParallelB200(nn.Module):
         return self.module.load_state_dict(*args, **kwargs)
 
 
+def convert_sync_batchnorm(model, process_group=None):
+    """nn.SyncBatchNorm.convert_sync_batchnorm (utils/parallel.py:38) for these modules: every BatchNorm2d keeps its
+    class, parameters and state_dict keys and is marked to take its training-mode statistics over all ranks of
+    ``process_group`` (modules._sync_group -> ops.SyncBNActFn).  Eval mode and single-process runs are unchanged."""
+    group = process_group if process_group is not None else (dist.group.WORLD if dist.is_initialized() else None)
+    for m in model.modules():
+        if isinstance(m, nn.BatchNorm2d):
+            m._msx_sync_group = group
+    return model
+
+
 def is_parallel(model):
     return type(model) in (nn.parallel.DataParallel, nn.parallel.DistributedDataParallel, DistributedDataParallelB200)
 
@@ -166,8 +176,7 @@ def parallel_model(config, model, rank, device):
     """utils/parallel.py:35-44."""
     if config.DDP:
         if getattr(config, 'synBN', False):
-            warnings.warn('synBN=True requested: this build keeps BatchNorm statistics per GPU '
-                          '(the reference\'s synBN=False behaviour); SyncBatchNorm is not implemented.')
+            convert_sync_batchnorm(model)
         return DistributedDataParallelB200(model.to(device))
     model.to(device)
     return model

@@ -399,3 +399,83 @@ def test_eval_sweep_fused_head_argmax_confmat_is_bit_exact(arch, base, dtype):
         bad.compute()
     with pytest.raises(ValueError):
         msx.eval_sweep(model.train(), x, t, [iou])
+
+
+def _syncbn_worker(rank, world, port, q):
+    """Two processes on ONE GPU (gloo carries the small all-reduces): each runs its shard through a SyncBatchNorm'ed
+    ConvBNAct -> DeConvBNAct -> ResidualBlock chain and returns outputs, input gradients, parameter gradients and buffers."""
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        import medical_segmentation_pytorch_b200 as msx
+        from medical_segmentation_pytorch_b200.ducknet import ResidualBlock
+        from medical_segmentation_pytorch_b200.modules import ConvBNAct, DeConvBNAct
+        from gpu_util import from_act, to_act
+        torch.manual_seed(3)
+        net = torch.nn.Sequential(ConvBNAct(5, 17, 3), DeConvBNAct(17, 12), ResidualBlock(12, 20, 'relu')).to(DEV)
+        msx.convert_sync_batchnorm(net)
+        net.train()
+        g = torch.Generator().manual_seed(100 + rank)
+        n = 2 + rank                                                    # unequal shard sizes: the count travels with the sums
+        x = torch.randn(n, 5, 12, 16, generator=g)
+        dz = torch.randn(n, 20, 24, 32, generator=g)
+        a = to_act(x, torch.float32, requires_grad=True)
+        out = net(a)
+        out.t.backward(to_act(dz, torch.float32).t)
+        torch.cuda.synchronize()
+        res = {'x': x, 'dz': dz, 'z': from_act(out.t.detach(), 20), 'dx': from_act(a.t.grad, 5),
+               'grads': {k: p.grad.detach().cpu() for k, p in net.named_parameters()},
+               'bufs': {k: b.detach().cpu() for k, b in net.named_buffers()}}
+        q.put((rank, res))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_sync_batchnorm_world2_matches_one_process_on_the_whole_batch():
+    """synBN=True (the reference's default, configs/base_config.py:91; utils/parallel.py:37-38): batch statistics over the
+    samples of all ranks.  Oracle: the same layers with plain nn.BatchNorm2d in float64 in ONE process on the concatenated
+    batch - outputs, input gradients and running statistics must match per shard; weight / bias gradients of every layer
+    are per-rank partial sums whose total is the single-process gradient (DDP then averages them, as it does for torch's
+    SyncBatchNorm)."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    port = 29500 + (os.getpid() * 7) % 2000
+    procs = [ctx.Process(target=_syncbn_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=240) for _ in procs)
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    torch.manual_seed(3)
+    from medical_segmentation_pytorch_b200.ducknet import ResidualBlock
+    from medical_segmentation_pytorch_b200.modules import ConvBNAct, DeConvBNAct
+    mine = torch.nn.Sequential(ConvBNAct(5, 17, 3), DeConvBNAct(17, 12), ResidualBlock(12, 20, 'relu'))   # same seed: same weights
+    sd = {k: v.double() if v.is_floating_point() else v for k, v in mine.state_dict().items()}
+
+    def bn(x, pfx, relu=True):
+        y = torch.nn.functional.batch_norm(x, sd[pfx + '.running_mean'], sd[pfx + '.running_var'], P[pfx + '.weight'], P[pfx + '.bias'], True, 0.1, 1e-5)
+        return torch.relu(y) if relu else y
+    P = {k: v.clone().requires_grad_(True) for k, v in sd.items() if v.is_floating_point() and 'running' not in k}
+    x = torch.cat([got[0]['x'], got[1]['x']]).double().requires_grad_(True)
+    F = torch.nn.functional
+    h = bn(F.conv2d(x, P['0.0.weight'], None, 1, 1), '0.1')
+    h = bn(F.conv_transpose2d(h, P['1.up_conv.0.weight'], P['1.up_conv.0.bias'], 2, 1, 1), '1.up_conv.1')
+    up = F.conv2d(h, P['2.upper_branch.weight'])
+    low = bn(F.conv2d(bn(F.conv2d(h, P['2.lower_branch.0.0.weight'], None, 1, 1), '2.lower_branch.0.1'), P['2.lower_branch.1.0.weight'], None, 1, 1), '2.lower_branch.1.1')
+    z = bn(up + low, '2.bn.0')
+    z.backward(torch.cat([got[0]['dz'], got[1]['dz']]).double())
+    n0 = got[0]['x'].shape[0]
+    for r, sl in ((0, slice(0, n0)), (1, slice(n0, None))):
+        assert rel(got[r]['z'], z[sl]) < 1e-5 and rel(got[r]['dx'], x.grad[sl]) < 1e-5, r
+        for k in got[r]['bufs']:
+            if 'running' in k:
+                assert rel(got[r]['bufs'][k], sd[k]) < 1e-5, (r, k)          # F.batch_norm updated sd in place
+            else:
+                assert int(got[r]['bufs'][k]) == 1
+    for k, p in P.items():
+        total = got[0]['grads'][k].double() + got[1]['grads'][k].double()
+        if float(p.grad.norm()) > 1e-9:
+            assert rel(total, p.grad) < 2e-5, k

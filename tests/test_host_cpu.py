@@ -188,3 +188,22 @@ def test_reference_lr_policies_drive_the_fused_optimizer():
     C.lr_policy = 'nope'
     with pytest.raises(NotImplementedError):
         msx.get_scheduler(C, opt)
+
+
+def test_parallel_model_with_synbn_marks_every_batchnorm():
+    """utils/parallel.py:35-39 with the reference's default synBN=True: BatchNorms are switched to cross-rank statistics
+    (same classes, same state_dict keys), and nothing changes for synBN=False."""
+    import medical_segmentation_pytorch_b200 as msx
+
+    class C:
+        DDP, synBN = True, True
+    m = msx.UNet(2, 3, 8)
+    keys = list(m.state_dict().keys())
+    w = msx.parallel_model(C, m, 0, torch.device('cpu'))
+    bns = [x for x in m.modules() if isinstance(x, torch.nn.BatchNorm2d)]
+    assert msx.is_parallel(w) and bns and all(hasattr(b, '_msx_sync_group') for b in bns)
+    assert list(w.state_dict().keys()) == keys
+    C.synBN = False
+    m2 = msx.UNet(2, 3, 8)
+    msx.parallel_model(C, m2, 0, torch.device('cpu'))
+    assert not any(hasattr(b, '_msx_sync_group') for b in m2.modules())
