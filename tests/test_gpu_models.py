@@ -424,9 +424,10 @@ def _syncbn_worker(rank, world, port, q):
         out = net(a)
         out.t.backward(to_act(dz, torch.float32).t)
         torch.cuda.synchronize()
-        res = {'x': x, 'dz': dz, 'z': from_act(out.t.detach(), 20), 'dx': from_act(a.t.grad, 5),
-               'grads': {k: p.grad.detach().cpu() for k, p in net.named_parameters()},
-               'bufs': {k: b.detach().cpu() for k, b in net.named_buffers()}}
+        # numpy (pickled by value): torch tensors travel as file descriptors that die with this process
+        res = {'x': x.numpy(), 'dz': dz.numpy(), 'z': from_act(out.t.detach(), 20).numpy(), 'dx': from_act(a.t.grad, 5).numpy(),
+               'grads': {k: p.grad.detach().cpu().numpy() for k, p in net.named_parameters()},
+               'bufs': {k: b.detach().cpu().numpy() for k, b in net.named_buffers()}}
         q.put((rank, res))
     finally:
         dist.destroy_process_group()
@@ -449,6 +450,8 @@ def test_sync_batchnorm_world2_matches_one_process_on_the_whole_batch():
     for p in procs:
         p.join(60)
         assert p.exitcode == 0
+    tt = lambda d: {k: (tt(v) if isinstance(v, dict) else torch.from_numpy(np.asarray(v))) for k, v in d.items()}   # noqa: E731
+    got = {r: tt(v) for r, v in got.items()}
     torch.manual_seed(3)
     from medical_segmentation_pytorch_b200.ducknet import ResidualBlock
     from medical_segmentation_pytorch_b200.modules import ConvBNAct, DeConvBNAct
