@@ -1024,7 +1024,9 @@ void wgrad_plan(const msx_conv_desc* d, WgParams& p) {
     p.tmem_cols = cols;
     p.Apad = p.a_tiles * 128; p.Bpad = p.b_tiles * p.TN;
     const int64_t units0 = (int64_t)p.a_tiles * p.b_tiles * p.tap_groups;
-    int64_t splits = (kNumSMs + units0 - 1) / units0;
+    // one CTA per SM and one wave: as many pixel splits as fit in 148 CTAs.  (Rounding UP gave 150-162 CTAs for the
+    // 136- / 272- / 512-channel layers: a second wave of a dozen CTAs that doubled the kernel's time.)
+    int64_t splits = units0 <= kNumSMs ? kNumSMs / units0 : 1;
     if (splits > p.pix_tiles) splits = p.pix_tiles;
     if (splits < 1) splits = 1;
     p.splits = (int)splits;
@@ -1339,6 +1341,27 @@ int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const
     p.Nc = Nc; p.ncp = round_up(Nc, 8); p.ldd = fwd_pass ? d->ldy : d->ldx;
     const int Np = round_up(Nc, 16);
     p.n_tiles = (Np + 255) / 256;
+    {
+        // Output-channel tiling by a small cost model: rounds of the persistent grid x time of one K-step, which is
+        // bound by the operand fetch (~32 cycles for the 128-row A tile + N/4 for B).  Few-pixel layers (11x11, 22x22) fill
+        // more SMs with narrower N tiles: 544 -> 544 at 11x11 is 16 x 3 = 48 tiles of N = 192 by default, 144 tiles of N = 64
+        // here; 272 channels at 22x22 go from 160 tiles (two rounds for 12 stragglers) to 240 narrower ones.
+        const bool four_phase = (d->transposed ? fwd_pass : !fwd_pass) && d->stride == 2;
+        const int gh = four_phase ? (p.Hd + 1) / 2 : p.Hd, gw = four_phase ? (p.Wd + 1) / 2 : p.Wd;
+        int tw0, th0;
+        pick_tile(gh, gw, tw0, th0);
+        const int64_t m_tiles = (int64_t)((gw + tw0 - 1) / tw0) * ((gh + th0 - 1) / th0) * p.N;
+        double best = 1e30;
+        int best_n = p.n_tiles;
+        for (int nt = p.n_tiles; nt <= p.n_tiles + 8 && nt * 16 <= Np; ++nt) {
+            const int bn = round_up((Np + nt - 1) / nt, 16);
+            if ((bn * (nt - 1)) >= Np) continue;                 // last tile would be empty
+            const double rounds = (double)((m_tiles * nt + kNumSMs - 1) / kNumSMs);
+            const double cost = rounds * (32.0 + bn / 4.0);
+            if (cost < best * 0.97) { best = cost; best_n = nt; }   // prefer fewer tiles unless clearly better
+        }
+        p.n_tiles = best_n;
+    }
     p.BN = round_up((Np + p.n_tiles - 1) / p.n_tiles, 16);
     p.chunk = p.Kp <= 32 ? 32 : 64;
     p.kchunks = (p.Kp + p.chunk - 1) / p.chunk;

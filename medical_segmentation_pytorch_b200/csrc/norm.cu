@@ -142,13 +142,34 @@ __global__ void __launch_bounds__(256, MSX_BN_MINBLOCKS) bn_stats_kernel(const T
     if (fin.ticket && ticket_is_last(fin.ticket, gridDim.x * gridDim.y, &last_flag)) bn_finalize_all(fin, gridDim.x);
 }
 
-// Stand-alone fold + finalize: one warp per channel over many CTAs.  Measured (round 2): letting the reduction launch's last
+// Fold of one channel by a whole 128-thread block (fixed order): every thread takes rows tid, tid + 128, ... (at most
+// four independent loads for <= 592 rows), then warp shuffles and one pass over the four warp sums.  One L2 round trip
+// instead of the four to five a single warp needs - these kernels are pure latency on the step's critical path.
+__device__ inline void fold_partials_block(const double* partials, int nblk, int cp, int c, double& s, double& q, double* sh) {
+    double a = 0.0, b = 0.0;
+    for (int r = threadIdx.x; r < nblk; r += 128) {
+        a += __ldcg(partials + ((int64_t)r * 2 + 0) * cp + c);
+        b += __ldcg(partials + ((int64_t)r * 2 + 1) * cp + c);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        a += __shfl_xor_sync(0xffffffffu, a, o);
+        b += __shfl_xor_sync(0xffffffffu, b, o);
+    }
+    if ((threadIdx.x & 31) == 0) { sh[(threadIdx.x >> 5) * 2] = a; sh[(threadIdx.x >> 5) * 2 + 1] = b; }
+    __syncthreads();
+    s = (sh[0] + sh[2]) + (sh[4] + sh[6]);
+    q = (sh[1] + sh[3]) + (sh[5] + sh[7]);
+}
+
+// Stand-alone fold + finalize: one 128-thread block per channel.  Measured (round 2): letting the reduction launch's last
 // CTA do this instead (tickets, common.cuh) removes a launch but serialises the fold of all channels in ONE CTA, which
 // costs more than the launch for every layer wider than ~40 channels (bn_bwd_reduce 6.8 -> 15.2 ms per DUCKNet-17 step),
 // so the in-kernel path is only taken up to ticket_max_cp() channels (default 0: never).
-__global__ void bn_finalize_kernel(int nblk, const BnFinalize f) {
-    const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int lane = threadIdx.x & 31;
+__global__ void __launch_bounds__(128) bn_finalize_kernel(int nblk, const BnFinalize f) {
+    __shared__ double sh[8];
+    const int c = blockIdx.x;
+    const int lane = threadIdx.x;
     if (c == 0 && lane == 0 && f.nbt && !f.sums) *f.nbt += 1;
     if (c == 0 && lane == 0 && f.sums) f.sums[2 * f.cp] = (double)f.count;      // this rank's sample count, reduced with the sums
     if (c >= f.cp) return;
@@ -160,7 +181,7 @@ __global__ void bn_finalize_kernel(int nblk, const BnFinalize f) {
         return;
     }
     double s, q;
-    fold_partials(f.partials, nblk, f.cp, c, s, q);
+    fold_partials_block(f.partials, nblk, f.cp, c, s, q, sh);
     if (lane != 0) return;
     if (f.sums) { f.sums[c] = s; f.sums[f.cp + c] = q; }
     else bn_finalize_one(f, c, s, q);
@@ -279,9 +300,10 @@ __device__ inline void bn_bwd_finalize_all(const BnBwdFinalize& f, const double*
     }
 }
 
-__global__ void bn_bwd_finalize_kernel(const double* partials, int nblk, const BnBwdFinalize f) {
-    const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int lane = threadIdx.x & 31;
+__global__ void __launch_bounds__(128) bn_bwd_finalize_kernel(const double* partials, int nblk, const BnBwdFinalize f) {
+    __shared__ double sh[8];
+    const int c = blockIdx.x;
+    const int lane = threadIdx.x;
     if (c >= f.cp) return;
     if (c >= f.channels) {
         if (lane == 0) {
@@ -291,7 +313,7 @@ __global__ void bn_bwd_finalize_kernel(const double* partials, int nblk, const B
         return;
     }
     double s, q;
-    fold_partials(partials, nblk, f.cp, c, s, q);
+    fold_partials_block(partials, nblk, f.cp, c, s, q, sh);
     if (lane != 0) return;
     if (f.dbeta) f.dbeta[c] = (float)s;
     if (f.dgamma) f.dgamma[c] = (float)q;
@@ -1012,7 +1034,7 @@ int ticket_max_cp() {
 
 // fold nblk partial rows and finalize, as its own launch (what every reduction uses when its BnFinalize has no ticket)
 int bn_finalize_launch(const BnFinalize& f, int nblk, cudaStream_t st) {
-    { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_finalize_kernel<<<(f.cp * 32 + 127) / 128, 128, 0, st>>>(nblk, f); }
+    { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_finalize_kernel<<<f.cp, 128, 0, st>>>(nblk, f); }
     MSX_LAUNCH_CHECK();
     return MSX_OK;
 }
@@ -1115,7 +1137,7 @@ int bn_bwd_reduce_launch(int dtype, const void* x, int ldx, const void* dz, int 
         const int g = wave_grid(reinterpret_cast<const void*>(bn_bwd_reduce_bf16_kernel), pixels, c.lanes, 8, kMaxPartialBlocks);
         { ProfScope ps__(K_BN_BWD_REDUCE, st, 2.0 * (double)pixels * channels * 2.0, 0); bn_bwd_reduce_bf16_kernel<<<dim3(g, c.nchunk), 256, 0, st>>>(
             static_cast<const bf16*>(x), ldx, static_cast<const bf16*>(dz), lddz, pixels, c.cp, c.vch, channels, mean, invstd, gamma, beta, relu, partials, f); }
-        if (!f.ticket) { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_bwd_finalize_kernel<<<(f.cp * 32 + 127) / 128, 128, 0, st>>>(partials, g, f); }
+        if (!f.ticket) { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_bwd_finalize_kernel<<<f.cp, 128, 0, st>>>(partials, g, f); }
         MSX_LAUNCH_CHECK();
         return MSX_OK;
     }
@@ -1124,7 +1146,7 @@ int bn_bwd_reduce_launch(int dtype, const void* x, int ldx, const void* dz, int 
         const int g = reduce_grid(pixels, c.lanes);
         { ProfScope ps__(K_BN_BWD_REDUCE, st, 2.0 * (double)pixels * channels * (double)sizeof(T), 0); bn_bwd_reduce_kernel<T><<<dim3(g, c.nchunk), 256, 0, st>>>(static_cast<const T*>(x), ldx, static_cast<const T*>(dz), lddz,
                                                                  pixels, c.cp, c.vch, channels, mean, invstd, gamma, beta, relu, partials, f); }
-        if (!f.ticket) { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_bwd_finalize_kernel<<<(f.cp * 32 + 127) / 128, 128, 0, st>>>(partials, g, f); }
+        if (!f.ticket) { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_bwd_finalize_kernel<<<f.cp, 128, 0, st>>>(partials, g, f); }
     });
     MSX_LAUNCH_CHECK();
     return MSX_OK;
