@@ -58,6 +58,8 @@ struct TcParams {
     int n_tiles, BN;      // tiling of the output-channel axis
     TapTable taps;
     int kchunks, chunk;   // K chunks per tap, channels per chunk (64 or 32)
+    int tail;             // 0, or the box width (16 | 32 channels) of the LAST chunk when the channel count leaves a short tail
+    uint32_t a_bytes_tail, b_bytes_tail;
     int Kp;               // padded reduction channels (multiple of 8)
     int Nc, ncp, ldd;     // output channels, round_up(Nc, 8), destination pixel stride
     int stages;
@@ -270,6 +272,7 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t row_bytes
 
 __global__ void __launch_bounds__(kHaloThreads, 1)
 conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CUtensorMap tmB,
+               const __grid_constant__ PhaseMaps tmA_tail, const __grid_constant__ CUtensorMap tmB_tail,
                bf16* __restrict__ dst, const ConvEpilogue ep, const __grid_constant__ TcParams p) {
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;             // swizzle atoms need 1024 B alignment
@@ -318,12 +321,21 @@ conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CU
                 for (int tap = 0; tap < taps; ++tap) {
                     const int sy = y0 + p.taps.dy[tap], sx = x0 + p.taps.dx[tap];
                     const CUtensorMap* mapA = &tmA.m[p.taps.map[tap]];
+                    const CUtensorMap* mapAt = &tmA_tail.m[p.taps.map[tap]];
                     const int wtap = p.taps.wtap[tap];
                     for (int kc = 0; kc < p.kchunks; ++kc) {
                         mbar_wait(bar_empty + 8 * stage, phase ^ 1);
-                        mbar_expect_tx(bar_full + 8 * stage, p.a_bytes + p.b_bytes);
-                        tma_load_4d(sA + stage * p.a_stage, mapA, bar_full + 8 * stage, kc * p.chunk, sx, sy, img);
-                        tma_load_3d(sB + stage * p.b_stage, &tmB, bar_full + 8 * stage, kc * p.chunk, nt * p.BN, wtap);
+                        if (p.tail && kc == p.kchunks - 1) {
+                            // short channel tail (72 = 64 + 8, 136 = 128 + 8, ...): a 16- or 32-channel box with the
+                            // matching narrower swizzle instead of a zero-filled 64-channel one - a quarter / half of the fill
+                            mbar_expect_tx(bar_full + 8 * stage, p.a_bytes_tail + p.b_bytes_tail);
+                            tma_load_4d(sA + stage * p.a_stage, mapAt, bar_full + 8 * stage, kc * p.chunk, sx, sy, img);
+                            tma_load_3d(sB + stage * p.b_stage, &tmB_tail, bar_full + 8 * stage, kc * p.chunk, nt * p.BN, wtap);
+                        } else {
+                            mbar_expect_tx(bar_full + 8 * stage, p.a_bytes + p.b_bytes);
+                            tma_load_4d(sA + stage * p.a_stage, mapA, bar_full + 8 * stage, kc * p.chunk, sx, sy, img);
+                            tma_load_3d(sB + stage * p.b_stage, &tmB, bar_full + 8 * stage, kc * p.chunk, nt * p.BN, wtap);
+                        }
                         if (++stage == p.stages) { stage = 0; phase ^= 1; }
                     }
                 }
@@ -340,6 +352,9 @@ conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CU
             const uint32_t a_step = p.a_stage >> 4, b_step = p.b_stage >> 4;
             const int full_ksteps = p.chunk / 16;
             const int last_ksteps = (p.Kp - (p.kchunks - 1) * p.chunk + 15) / 16;
+            // tail chunk: rows of 32 B (SWIZZLE_32B, layout 6) or 64 B (SWIZZLE_64B, layout 4), 8-row groups densely packed
+            const uint32_t tail_row = (uint32_t)p.tail * 2;
+            const uint32_t hi_tail = (uint32_t)((8 * tail_row) >> 4) | (1u << 14) | ((tail_row == 32 ? 6u : 4u) << 29);
             const int kchunks = p.kchunks, stages = p.stages, BN = p.BN, total = p.total_tiles;
             int stage = 0;
             uint32_t phase = 0;
@@ -354,11 +369,13 @@ conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CU
                     for (int kc = 0; kc < kchunks; ++kc) {
                         mbar_wait(bar_full + 8 * stage, phase);              // TMA bytes have landed
                         tc_fence_after();
+                        const bool is_tail = p.tail && kc == kchunks - 1;
                         const int ksteps = kc == kchunks - 1 ? last_ksteps : full_ksteps;
+                        const uint32_t hik = is_tail ? hi_tail : hi;
                         const uint32_t da = a_lo0 + stage * a_step, db = b_lo0 + stage * b_step;
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
-                            if (k < ksteps) { umma_bf16_lhr(tmem_d, da + 2 * k, hi, db + 2 * k, hi, idesc, acc); acc = 1; }   // +32 B per K=16 step
+                            if (k < ksteps) { umma_bf16_lhr(tmem_d, da + 2 * k, hik, db + 2 * k, hik, idesc, acc); acc = 1; }   // +32 B per K=16 step
                         umma_commit(bar_empty + 8 * stage);                  // frees the smem stage when the MMAs retire
                         if (++stage == stages) { stage = 0; phase ^= 1; }
                     }
@@ -1027,6 +1044,7 @@ void wgrad_plan(const msx_conv_desc* d, WgParams& p) {
     // one CTA per SM and one wave: as many pixel splits as fit in 148 CTAs.  (Rounding UP gave 150-162 CTAs for the
     // 136- / 272- / 512-channel layers: a second wave of a dozen CTAs that doubled the kernel's time.)
     int64_t splits = units0 <= kNumSMs ? kNumSMs / units0 : 1;
+    if (splits < 2) splits = (kNumSMs + units0 - 1) / units0;     // 75-148 units: two half-size CTAs per unit measured faster than one (544 ch: 45 vs 63 us)
     if (splits > p.pix_tiles) splits = p.pix_tiles;
     if (splits < 1) splits = 1;
     p.splits = (int)splits;
@@ -1263,7 +1281,7 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
 // shifted box of one phase, so zero padding stays TMA out-of-bounds fill.
 static int make_src_maps(PhaseMaps& maps, const void* src, int Kp, int N, int Hs, int Ws, int lds, int stride,
                          int chunk, int tw, int th, unsigned used_mask) {
-    const CUtensorMapSwizzle sw = chunk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+    const CUtensorMapSwizzle sw = chunk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : (chunk == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
     cuuint32_t box[4] = {(cuuint32_t)chunk, (cuuint32_t)tw, (cuuint32_t)th, 1};
     if (stride == 1) {
         cuuint64_t dims[4] = {(cuuint64_t)Kp, (cuuint64_t)Ws, (cuuint64_t)Hs, (cuuint64_t)N};
@@ -1367,6 +1385,12 @@ int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const
     p.kchunks = (p.Kp + p.chunk - 1) / p.chunk;
     const uint32_t row_bytes = p.chunk * 2;
     p.b_bytes = (uint32_t)p.BN * row_bytes;
+    {
+        static const int tail_on = [] { const char* e = getenv("MSX_TC_TAIL"); return e ? atoi(e) : 1; }();
+        const int rem = p.Kp % 64;                               // DUCK-Net's 17 * 2^k widths: 72 -> 8, 136 -> 8, 272 -> 16, 544 -> 32
+        p.tail = (tail_on && p.chunk == 64 && p.kchunks >= 2 && rem > 0 && rem <= 32) ? (rem <= 16 ? 16 : 32) : 0;
+        p.b_bytes_tail = (uint32_t)p.BN * p.tail * 2;
+    }
     p.a_stage = 128 * row_bytes;                                 // full 128-row operand tile
     p.b_stage = (p.b_bytes + 1023u) & ~1023u;
     const int nphase = (!f_form && d->stride == 2) ? 4 : 1;      // b-form stride 2: one launch per destination phase
@@ -1379,12 +1403,17 @@ int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const
     p.tmem_cols = cols;
     const size_t smem = 1024 + (size_t)p.stages * (p.a_stage + p.b_stage) + 16 * kMaxStages + 64 + stat_bytes;
     const CUtensorMapSwizzle sw = p.chunk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
-    CUtensorMap tmB;
+    CUtensorMap tmB, tmB_tail;
     {
         cuuint64_t dims[3] = {(cuuint64_t)p.Kp, (cuuint64_t)Np, (cuuint64_t)(d->kh * d->kw)};
         cuuint64_t strides[2] = {(cuuint64_t)p.Kp * 2, (cuuint64_t)p.Kp * 2 * Np};
         cuuint32_t box[3] = {(cuuint32_t)p.chunk, (cuuint32_t)p.BN, 1};
         MSX_TRY(make_map(&tmB, 3, packed, dims, strides, box, sw));
+        tmB_tail = tmB;
+        if (p.tail) {
+            cuuint32_t boxt[3] = {(cuuint32_t)p.tail, (cuuint32_t)p.BN, 1};
+            MSX_TRY(make_map(&tmB_tail, 3, packed, dims, strides, boxt, p.tail == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B));
+        }
     }
     MSX_TRY(ensure_big_smem(reinterpret_cast<const void*>(conv_tc_kernel)));
     for (int ph = 0; ph < nphase; ++ph) {
@@ -1398,13 +1427,16 @@ int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const
         p.tiles_y = (p.H + p.th - 1) / p.th;
         p.total_tiles = p.tiles_x * p.tiles_y * p.N * p.n_tiles;
         p.a_bytes = (uint32_t)p.tw * p.th * row_bytes;
-        PhaseMaps maps;
+        p.a_bytes_tail = (uint32_t)p.tw * p.th * p.tail * 2;
+        PhaseMaps maps, maps_tail;
         MSX_TRY(make_src_maps(maps, src, p.Kp, p.N, Hs, Ws, lds, f_form ? d->stride : 1, p.chunk, p.tw, p.th, mask));
+        if (p.tail) MSX_TRY(make_src_maps(maps_tail, src, p.Kp, p.N, Hs, Ws, lds, f_form ? d->stride : 1, p.tail, p.tw, p.th, mask));
+        else maps_tail = maps;
         const int grid = p.total_tiles < kNumSMs ? p.total_tiles : kNumSMs;
         const double Mg = (double)p.N * p.H * p.W, Ms = (double)p.N * Hs * Ws / nphase;
         {
             ProfScope ps__(K_CONV_TC, st, (Mg * Nc + Ms * K) * 2.0, 2.0 * Mg * Nc * K * p.taps.n);
-            conv_tc_kernel<<<grid, kHaloThreads, smem, st>>>(maps, tmB, static_cast<bf16*>(dst), ep, p);
+            conv_tc_kernel<<<grid, kHaloThreads, smem, st>>>(maps, tmB, maps_tail, tmB_tail, static_cast<bf16*>(dst), ep, p);
         }
         MSX_LAUNCH_CHECK();
         if (ep.stats && !ep.bnf.ticket) MSX_TRY(bn_finalize_launch(ep.bnf, grid, st));
