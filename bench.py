@@ -191,7 +191,7 @@ def loss_metric_leg(msx, _lib, dev, pk, n=256, h=352, reps=5):
 class Workload:
     """One rank's training step of a BASELINE config: model + loss + fused optimizer + EMA on static input buffers."""
 
-    def __init__(self, msx, name, batch, size, bf16, dev, world, rank, kd=None):
+    def __init__(self, msx, name, batch, size, bf16, dev, world, rank, kd=None, sync_bn=False):
         import torch
         from medical_segmentation_pytorch_b200.flat import FlatBuffers, FlatParams
         from medical_segmentation_pytorch_b200.synth import synth_batch
@@ -207,6 +207,8 @@ class Workload:
         self.model.train()
         FlatParams(self.model)
         FlatBuffers(self.model)
+        if sync_bn and world > 1:                                      # utils/parallel.py:37-38 (the reference's default synBN=True)
+            msx.convert_sync_batchnorm(self.model)
         self.net = msx.DistributedDataParallelB200(self.model) if world > 1 else self.model
         self.opt = msx.FusedOptimizer(self.net, 'adam', lr=0.1 * 0.01 * world)   # utils/optimizer.py:15 with my_config.py:23
         self.ema = msx.ModelEma(self.net)
@@ -255,6 +257,7 @@ def main():
     ap.add_argument('--ncu', action='store_true', help='short eager run for an ncu launch list: 1 warm-up + 1 step, no graph / e2e / profile pass')
     ap.add_argument('--kd', default=None, metavar='ENCODER', help="BASELINE config 5: add a frozen smp.Unet(<ENCODER>, e.g. resnet101) teacher forward "
                     "and the KL distillation term (T = 4, coefficient 1) to every step")
+    ap.add_argument('--sync-bn', action='store_true', help='SyncBatchNorm (the reference default synBN=True) instead of per-GPU statistics (north_star); N > 1 only')
     ap.add_argument('--no-branch-streams', action='store_true', help='run sibling DUCK branches one after another on one stream')
     ap.add_argument('--no-graph', action='store_true', help='launch every kernel from Python instead of replaying one CUDA graph per step')
     args = ap.parse_args()
@@ -328,7 +331,7 @@ def main():
                 replay = None
         return replay, err, per_step
 
-    wl = Workload(msx, args.model, B, S, bf16, dev, world, rank, args.kd)
+    wl = Workload(msx, args.model, B, S, bf16, dev, world, rank, args.kd, args.sync_bn)
     replay, graph_err, launches_per_step = capture(wl, args.warmup)
 
     def run_step():
@@ -455,7 +458,7 @@ def main():
         'metric': 'train_imgs_per_sec', 'value': value, 'unit': 'img/s', 'n_gpus': world, 'steps': args.steps, 'warmup': args.warmup,
         'ms_per_step': ms / args.steps, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None,
         'dtype': 'bf16' if bf16 else 'f32', 'data': 'synthetic',
-        'config': {'workload': f'{workload_name} training step (fwd+CE+' + (f'frozen smp.Unet({args.kd}) teacher fwd+KD(kl,T=4)+' if args.kd else '') + f'bwd+Adam+EMA copy), {S}x{S}, batch {B}/GPU, num_class 2, per-GPU BN',
+        'config': {'workload': f'{workload_name} training step (fwd+CE+' + (f'frozen smp.Unet({args.kd}) teacher fwd+KD(kl,T=4)+' if args.kd else '') + f'bwd+Adam+EMA copy), {S}x{S}, batch {B}/GPU, num_class 2, ' + ('SyncBatchNorm' if args.sync_bn and world > 1 else 'per-GPU BN'),
                    'global_batch': B * world, 'parallelism': f'dp{world}', 'l2': 'per-step working set >> 126 MB L2 (no flush needed)',
                    'seed': 'weights manual_seed(1); data PCG64(1+rank)',
                    'launch': 'one CUDA graph replay per step (msx.capture_step)' if graph_on else 'eager Python launches' + (f' (graph capture failed: {graph_err})' if graph_err else '')},

@@ -64,7 +64,8 @@ class DistributedDataParallelB200(nn.Module):
                 order[m]._msx_bucket = b
                 order[m]._msx_ready = self._make_ready(order[m])
         self._callback_queued = False
-        self._avg_native = self.is_cuda        # NCCL has ReduceOp.AVG; gloo does not
+        # NCCL has ReduceOp.AVG; gloo (CPU tensors, or the one-GPU multi-process tests) does not
+        self._avg_native = self.is_cuda and dist.is_initialized() and dist.get_backend(self.pg) == 'nccl'
         if self.world > 1:
             dist.broadcast(self.flat.data, src=0, group=self.pg)
             dist.broadcast(self.fbuf.fdata, src=0, group=self.pg)

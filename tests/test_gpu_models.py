@@ -482,3 +482,69 @@ def test_sync_batchnorm_world2_matches_one_process_on_the_whole_batch():
         total = got[0]['grads'][k].double() + got[1]['grads'][k].double()
         if float(p.grad.norm()) > 1e-9:
             assert rel(total, p.grad) < 2e-5, k
+
+
+def _ddp_worker(rank, world, port, q):
+    """Two ranks on ONE GPU over gloo: the real CUDA backward (side streams, arena gradients, bucket-ready callbacks from
+    the kernels' Python shims) with the bucketed all-reduce, against plain per-rank gradients averaged explicitly."""
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        import medical_segmentation_pytorch_b200 as msx
+        import medical_segmentation_pytorch_b200.parallel as par
+        from medical_segmentation_pytorch_b200.flat import FlatParams
+        torch.manual_seed(1 + rank)                          # different init per rank: the wrap must broadcast rank 0's
+        a = msx.DuckNet(num_class=2, n_channel=3, base_channel=4).to(DEV).train()
+        b = msx.DuckNet(num_class=2, n_channel=3, base_channel=4).to(DEV).train()
+        FlatParams(a)
+        old = par.compute_buckets
+        par.compute_buckets = lambda sizes: old(sizes, 16 * 1024, 128 * 1024)       # many buckets on a small model
+        ddp = msx.DistributedDataParallelB200(a)
+        par.compute_buckets = old
+        b.load_state_dict(a.state_dict())
+        loss_fn = msx.get_loss_fn(Cfg(), DEV)
+        bad, nb = [], len(ddp.buckets)
+        for step in range(4):
+            bf16 = step % 2 == 1
+            g = torch.Generator().manual_seed(100 * step + rank)
+            x = torch.randn(2, 3, 64, 64, generator=g).to(DEV)
+            t = torch.randint(0, 2, (2, 64, 64), generator=g).to(DEV)
+            for p in b.parameters():
+                p.grad = None
+            with torch.autocast('cuda', dtype=torch.bfloat16, enabled=bf16):
+                loss_fn(ddp(x), t).backward()
+                loss_fn(b(x), t).backward()
+            torch.cuda.synchronize()
+            for (n, pa), pb in zip(a.named_parameters(), b.parameters()):
+                ref = pb.grad.detach().cpu()
+                dist.all_reduce(ref, op=dist.ReduceOp.SUM)
+                ref = (ref / world).to(DEV)
+                if not torch.allclose(pa.grad, ref, rtol=1e-6, atol=1e-9):
+                    bad.append((step, n, float((pa.grad - ref).abs().max())))
+            for ba, bb in zip(a.buffers(), b.buffers()):
+                bb.copy_(ba)
+        w = [p.detach().float().sum().item() for p in a.parameters()][:8]
+        q.put((rank, bad[:5], nb, w))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_ddp_bucketed_allreduce_world2_on_cuda_kernels():
+    """DistributedDataParallelB200 with the CUDA backward (the CPU test in test_host_cpu.py drives the bucket logic with
+    torch CPU modules): two ranks, >= 5 buckets, fp32 and bf16 steps; the arena gradients after backward equal the
+    per-rank gradients averaged by one explicit all-reduce (sum / world: same rounding as the gloo path, within 1 ulp
+    of NCCL's AVG), parameters were broadcast from rank 0, every bucket is re-armed."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    port = 29500 + (os.getpid() * 13 + 5) % 2000
+    procs = [ctx.Process(target=_ddp_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict((r, (bad, nb, w)) for r, bad, nb, w in (q.get(timeout=300) for _ in procs))
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    assert got[0][0] == [] and got[1][0] == [], (got[0][0], got[1][0])
+    assert got[0][1] >= 5 and got[0][2] == got[1][2]
