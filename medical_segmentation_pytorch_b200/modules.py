@@ -53,11 +53,14 @@ def _geom_of(conv):
 
 def _sync_group(bn):
     """The process group a BatchNorm synchronises its batch statistics over (parallel_model with synBN=True), or None."""
-    g = getattr(bn, '_msx_sync_group', None)
-    if g is None or not bn.training:
+    ref = getattr(bn, '_msx_sync_group', None)
+    if ref is None or not bn.training:
         return None
     import torch.distributed as dist
-    return g if dist.is_initialized() and dist.get_world_size(g) > 1 else None
+    if not dist.is_initialized():
+        return None
+    g = ref.group if ref.group is not None else dist.group.WORLD
+    return g if dist.get_world_size(g) > 1 else None
 
 
 def conv_bn_act(x, conv, bn, relu, slot=None):

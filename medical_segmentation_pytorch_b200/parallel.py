@@ -137,6 +137,17 @@ class DistributedDataParallelB200(nn.Module):
         return self.module.load_state_dict(*args, **kwargs)
 
 
+class SyncGroupRef:
+    """Holder of the process group a BatchNorm synchronises over; survives copy.deepcopy of the model (ModelEma, the
+    reference's get_ema_model) - a ProcessGroup itself cannot be copied."""
+
+    def __init__(self, group):
+        self.group = group
+
+    def __deepcopy__(self, memo):
+        return self
+
+
 def convert_sync_batchnorm(model, process_group=None):
     """nn.SyncBatchNorm.convert_sync_batchnorm (utils/parallel.py:38) for these modules: every BatchNorm2d keeps its
     class, parameters and state_dict keys and is marked to take its training-mode statistics over all ranks of
@@ -144,7 +155,7 @@ def convert_sync_batchnorm(model, process_group=None):
     group = process_group if process_group is not None else (dist.group.WORLD if dist.is_initialized() else None)
     for m in model.modules():
         if isinstance(m, nn.BatchNorm2d):
-            m._msx_sync_group = group
+            m._msx_sync_group = SyncGroupRef(group)
     return model
 
 
