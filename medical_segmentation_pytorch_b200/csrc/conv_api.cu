@@ -16,8 +16,6 @@ int conv_gather_simt(const msx_conv_desc* d, bool fwd_pass, const void* src, con
 size_t conv_wgrad_ws_bytes(const msx_conv_desc* d);
 int conv_wgrad_simt(const msx_conv_desc* d, const void* x, const void* dy, float* dw, void* ws, size_t ws_bytes,
                     cudaStream_t st);
-bool conv1x1_small_supported(const msx_conv_desc* d, bool fwd_pass);
-int conv1x1_small(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const ConvEpilogue& ep, void* dst, cudaStream_t st);
 // tcgen05 engine (conv_tc.cu)
 bool conv_tc_supported(const msx_conv_desc* d, bool fwd_pass);
 bool conv_tc_gather_supported(const msx_conv_desc* d, bool fwd_pass);
@@ -26,17 +24,6 @@ int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const
 
 size_t conv_wgrad_tc_ws_bytes(const msx_conv_desc* d);
 int conv_wgrad_tc(const msx_conv_desc* d, const void* x, const void* dy, float* dw, void* ws, size_t ws_bytes, cudaStream_t st);
-
-// MSX_FUSED_STATS=0: statistics by the stand-alone pass everywhere (measurement / bisecting switch, read once)
-static bool fused_stats_enabled() {
-    static const bool on = [] { const char* e = getenv("MSX_FUSED_STATS"); return !(e && atoi(e) == 0); }();
-    return on;
-}
-
-static bool small_1x1_enabled() {
-    static const bool on = [] { const char* e = getenv("MSX_SMALL_1X1"); return !(e && atoi(e) == 0); }();
-    return on;
-}
 
 static bool want_tc(const msx_conv_desc* d) {
     return d->engine == MSX_ENGINE_TCGEN05 || (d->engine == MSX_ENGINE_AUTO && d->dtype == MSX_BF16);
@@ -51,9 +38,6 @@ static int conv_gather(const msx_conv_desc* d, bool fwd_pass, const void* src, c
                        void* dst, cudaStream_t st, bool* stats_fused = nullptr) {
     if (stats_fused) *stats_fused = false;
     const bool want_tc = d->engine == MSX_ENGINE_TCGEN05 || (d->engine == MSX_ENGINE_AUTO && d->dtype == MSX_BF16);
-    // 1x1 with <= 40 channels on both sides is a bandwidth op the TMA row rate makes the tensor-core kernel slow at
-    if (d->engine == MSX_ENGINE_AUTO && !ep.stats && small_1x1_enabled() && conv1x1_small_supported(d, fwd_pass))
-        return conv1x1_small(d, fwd_pass, src, packed, ep, dst, st);
     if (want_tc && conv_tc_gather_supported(d, fwd_pass)) return conv_gather_tc(d, fwd_pass, src, packed, ep, dst, st, stats_fused);
     if (d->engine == MSX_ENGINE_TCGEN05)
         return set_error(MSX_ERR_UNSUPPORTED, "conv: tcgen05 engine requested for a shape/dtype it does not support");
@@ -62,6 +46,12 @@ static int conv_gather(const msx_conv_desc* d, bool fwd_pass, const void* src, c
 static int conv_gather(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const float* bias,
                        void* dst, cudaStream_t st) {
     return conv_gather(d, fwd_pass, src, packed, conv_epilogue(bias), dst, st);
+}
+
+// MSX_FUSED_STATS=0: statistics by the stand-alone pass everywhere (measurement / bisecting switch, read once)
+static bool fused_stats_enabled() {
+    static const bool on = [] { const char* e = getenv("MSX_FUSED_STATS"); return !(e && atoi(e) == 0); }();
+    return on;
 }
 
 static size_t ws_conv_bytes(const msx_conv_desc* d) {

@@ -446,106 +446,6 @@ int conv_pack_launch(const msx_conv_desc* d, int mode, const float* w, void* pac
     return MSX_OK;
 }
 
-// ---- 1x1 convolutions with few channels (bf16) ------------------------------------------------------------------
-// DUCK-Net's ResidualBlock shortcuts at the two finest levels (17 / 34 channels, models/ducknet.py:93): a 1x1 conv of a
-// 17-channel tensor is a bandwidth op (289 MACs per pixel against 68 bytes), and ncu showed the tcgen05 halo kernel
-// bound on it by the TMA unit's row rate (one 48-byte pixel row per ~8 cycles: 62-72 us at 16x352x352 where the
-// traffic needs ~30).  Here a thread owns two pixels, keeps their NV*8 fp32 outputs in registers, walks the real input
-// channels and reads the weights (fp32, transposed to [k][n]) from shared memory as broadcast float4s - each weight
-// read serves both pixels.  Same operand as the tensor-core path: packed [Np][Kp] bf16, dst[p][n] = sum_k src[p][k]*W[n][k].
-template <int NV>
-__global__ void __launch_bounds__(256) conv1x1_small_bf16_kernel(const bf16* __restrict__ src, int lds, const bf16* __restrict__ wp, int K, int Kp,
-                                                                 int Nc, bf16* __restrict__ dst, int ldd, int64_t pixels, const ConvEpilogue ep) {
-    constexpr int NO = NV * 8;
-    extern __shared__ float wsm[];                       // [Kp][NO]
-    for (int i = threadIdx.x; i < Kp * NO; i += blockDim.x) {
-        const int k = i / NO, n = i - k * NO;
-        wsm[i] = __bfloat162float(wp[(int64_t)n * Kp + k]);          // rows n >= Nc and columns k >= K of the packed operand are zero
-    }
-    __syncthreads();
-    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    for (int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; p < pixels; p += 2 * stride) {
-        const int64_t p1 = p + stride;
-        const bool has1 = p1 < pixels;
-        float a0[NO], a1[NO];
-#pragma unroll
-        for (int n = 0; n < NO; ++n) { a0[n] = 0.f; a1[n] = 0.f; }
-        const bf16* s0 = src + p * lds;
-        const bf16* s1 = src + (has1 ? p1 : p) * lds;
-        for (int k0 = 0; k0 < K; k0 += 8) {
-            float v0[8], v1[8];
-            Vec<bf16>::load(s0 + k0, v0);
-            Vec<bf16>::load(s1 + k0, v1);
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                if (k0 + j < K) {
-                    const float4* wr = reinterpret_cast<const float4*>(wsm + (k0 + j) * NO);
-#pragma unroll
-                    for (int q = 0; q < NO / 4; ++q) {
-                        const float4 w4 = wr[q];
-                        a0[4 * q] = fmaf(v0[j], w4.x, a0[4 * q]);         a1[4 * q] = fmaf(v1[j], w4.x, a1[4 * q]);
-                        a0[4 * q + 1] = fmaf(v0[j], w4.y, a0[4 * q + 1]); a1[4 * q + 1] = fmaf(v1[j], w4.y, a1[4 * q + 1]);
-                        a0[4 * q + 2] = fmaf(v0[j], w4.z, a0[4 * q + 2]); a1[4 * q + 2] = fmaf(v1[j], w4.z, a1[4 * q + 2]);
-                        a0[4 * q + 3] = fmaf(v0[j], w4.w, a0[4 * q + 3]); a1[4 * q + 3] = fmaf(v1[j], w4.w, a1[4 * q + 3]);
-                    }
-                }
-            }
-        }
-        auto finish = [&](float (&a)[NO], bf16* out) {
-#pragma unroll
-            for (int n = 0; n < NO; ++n) {
-                float f = a[n];
-                if (n < Nc) {
-                    if (ep.bias) f += ep.bias[n];
-                    if (ep.scale) f = fmaf(f, ep.scale[n], ep.shift[n]);
-                    if (ep.relu) f = fmaxf(f, 0.f);
-                } else f = 0.f;
-                a[n] = f;
-            }
-#pragma unroll
-            for (int v = 0; v < NV; ++v) {
-                float t8[8];
-#pragma unroll
-                for (int j = 0; j < 8; ++j) t8[j] = a[8 * v + j];
-                Vec<bf16>::store(out + 8 * v, t8);
-            }
-        };
-        finish(a0, dst + p * ldd);
-        if (has1) finish(a1, dst + p1 * ldd);
-    }
-}
-
-bool conv1x1_small_supported(const msx_conv_desc* d, bool fwd_pass) {
-    if (d->dtype != MSX_BF16 || d->kh != 1 || d->kw != 1 || d->stride != 1 || d->transposed || d->pad_h || d->pad_w) return false;
-    int Nc, K;
-    pass_dims(d, fwd_pass, Nc, K);
-    return round_up(K, 8) <= 40 && round_up(Nc, 8) <= 40;
-}
-
-int conv1x1_small(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const ConvEpilogue& ep, void* dst, cudaStream_t st) {
-    int Nc, K;
-    pass_dims(d, fwd_pass, Nc, K);
-    const int Kp = round_up(K, 8), nv = round_up(Nc, 8) / 8;
-    const int lds = fwd_pass ? d->ldx : d->ldy, ldd = fwd_pass ? d->ldy : d->ldx;
-    const int64_t pixels = (int64_t)d->n * d->h * d->w;
-    const size_t smem = (size_t)Kp * nv * 8 * sizeof(float);
-    int64_t g = cdiv64(pixels, 256 * 2);
-    if (g > kNumSMs * 4) g = kNumSMs * 4;
-    if (g < 1) g = 1;
-    ConvEpilogue e = ep;
-    e.stats = 0;
-#define MSX_C11(NVV) case NVV: { ProfScope ps__(K_CONV_SIMT, st, (double)pixels * (K + Nc) * 2.0, 2.0 * (double)pixels * Nc * K); \
-        conv1x1_small_bf16_kernel<NVV><<<(unsigned)g, 256, smem, st>>>(static_cast<const bf16*>(src), lds, static_cast<const bf16*>(packed), K, Kp, Nc, static_cast<bf16*>(dst), ldd, pixels, e); } break;
-    switch (nv) {
-        MSX_C11(1) MSX_C11(2) MSX_C11(3) MSX_C11(4) MSX_C11(5)
-        default: return set_error(MSX_ERR_UNSUPPORTED, "conv1x1_small: %d output channels", Nc);
-    }
-#undef MSX_C11
-    MSX_LAUNCH_CHECK();
-    note_conv_engine(MSX_ENGINE_SIMT);
-    return MSX_OK;
-}
-
 // fwd_pass: module forward (x->y) else data gradient (dy->dx).
 int conv_gather_simt(const msx_conv_desc* d, bool fwd_pass, const void* src, const void* packed, const ConvEpilogue& ep,
                      void* dst, cudaStream_t st) {
