@@ -548,3 +548,49 @@ def test_ddp_bucketed_allreduce_world2_on_cuda_kernels():
         assert p.exitcode == 0
     assert got[0][0] == [] and got[1][0] == [], (got[0][0], got[1][0])
     assert got[0][1] >= 5 and got[0][2] == got[1][2]
+
+
+@pytest.mark.parametrize('kind', ['sgd', 'adam'])
+def test_capture_step_follows_the_lr_schedule(kind):
+    """msx.capture_step: the reference's step body as one CUDA graph.  Scalars a kernel receives by value are frozen into a
+    graph, so the fused optimizer reads lr / momentum / betas from a device array that a graph node refreshes from pinned
+    host memory at every replay: a replay after `param_groups[0]['lr'] = 0` must leave the parameters untouched, and a
+    replay with the lr restored must move them by exactly what an eager step with that lr does."""
+    import medical_segmentation_pytorch_b200 as msx
+    from medical_segmentation_pytorch_b200.synth import synth_batch
+    torch.manual_seed(4)
+    a = msx.UNet(2, 3, 8).to(DEV).train()
+    b = msx.UNet(2, 3, 8).to(DEV).train()
+    b.load_state_dict(a.state_dict())
+    x, t = synth_batch(2, 32, 32, seed=2)
+    x, t = x.to(DEV), t.to(DEV)
+    lf = msx.get_loss_fn(Cfg(), DEV)
+    opts = [msx.FusedOptimizer(m, kind, lr=0.05) for m in (a, b)]
+
+    def make_step(m, o):
+        def step():
+            o.zero_grad()
+            loss = lf(m(x), t)
+            loss.backward()
+            o.step()
+            return loss
+        return step
+    step_a, step_b = make_step(a, opts[0]), make_step(b, opts[1])
+    replay = msx.capture_step(step_a, warmup=2, optimizers=[opts[0]])        # 2 eager steps + the capture pass (a no-op on data)
+    for _ in range(2):
+        step_b().detach()
+    flat = lambda m: torch.cat([p.detach().flatten() for p in m.parameters()])   # noqa: E731
+    assert rel(flat(a), flat(b)) < 1e-6                                      # capture itself does not execute the step
+    for lr in (0.05, 0.0, 0.02):
+        opts[0].param_groups[0]['lr'] = lr
+        opts[1].param_groups[0]['lr'] = lr
+        before = flat(a).clone()
+        loss = replay()
+        step_b().detach()
+        torch.cuda.synchronize()
+        assert torch.isfinite(loss).item()
+        if lr == 0.0:
+            assert torch.equal(flat(a), before)
+        else:
+            assert not torch.equal(flat(a), before)
+        assert rel(flat(a), flat(b)) < 2e-5, lr
