@@ -451,6 +451,9 @@ struct HaloParams {
     int Wh, Hh, BN, ksteps, Nc, ncp, ldd;
     int stages, tmem_cols, nacc;   // nacc TMEM accumulators in flight (hides the commit -> epilogue -> release round trip)
     uint32_t a_bytes, a_stage, b_tap_bytes;
+    // channel tail (68 channels = 64 + a 16-wide box, SWIZZLE_32B): a second, 32 B-per-pixel patch after the main one in
+    // every stage and a second set of resident weights after the main ones; one more K step per tap
+    uint32_t a_tail_off, a_bytes_tail, b_tail_bytes, b_tail_base;
     int issuers;                   // 1 or 2 MMA-issuing warps
     int tw, boxes_x, total_boxes;  // tw == 2 (pair mode): one TMA box covers two tiles side by side; issuer / epilogue group j takes tile j
 #ifdef MSX_ABLATION
@@ -472,14 +475,16 @@ __device__ __forceinline__ uint64_t umma_desc_halo(uint32_t saddr, uint32_t sbo_
     return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(sbo_bytes >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
 
-template <int TAPS, int KSTEPS>
+template <int TAPS, int KSTEPS, bool TAIL>
 __global__ void __launch_bounds__(kHaloThreads2, 1)
 conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmAt, const __grid_constant__ CUtensorMap tmBt,
                     bf16* __restrict__ dst, const ConvEpilogue ep, const HaloParams p) {
     extern __shared__ uint8_t smem_raw[];
     const int taps = p.kh * p.kw;
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-    const uint32_t sB = base, sA = base + ((taps * p.b_tap_bytes + 1023u) & ~1023u);
+    const uint32_t sB = base, sBt = base + p.b_tail_base;
+    const uint32_t sA = base + ((p.b_tail_base + (TAIL ? taps * p.b_tail_bytes : 0u) + 1023u) & ~1023u);
     const uint32_t bars = sA + p.stages * p.a_stage;
     const uint32_t bar_full = bars, bar_empty = bars + 8 * kMaxStages;
     const uint32_t bar_tfull = bars + 16 * kMaxStages, bar_tempty = bar_tfull + 8 * kMaxAcc, bar_w = bar_tempty + 8 * kMaxAcc;
@@ -515,8 +520,10 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (warp == 0) {
         // (a second TMA-issuing warp on alternate tiles was measured: no gain - the per-box cost is in the TMA unit)
         if (lane == 0) {
-            mbar_expect_tx(bar_w, taps * p.b_tap_bytes);                       // resident weights, once per CTA
+            mbar_expect_tx(bar_w, taps * (p.b_tap_bytes + (TAIL ? p.b_tail_bytes : 0u)));      // resident weights, once per CTA
             for (int tap = 0; tap < taps; ++tap) tma_load_3d(sB + tap * p.b_tap_bytes, &tmB, bar_w, 0, 0, tap);
+            if (TAIL)
+                for (int tap = 0; tap < taps; ++tap) tma_load_3d(sBt + tap * p.b_tail_bytes, &tmBt, bar_w, 64, 0, tap);
             int stage = 0;
             uint32_t phase = 0;
             for (int t = blockIdx.x; t < total_units; t += gridDim.x) {
@@ -526,8 +533,9 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 mbar_wait(bar_empty + 8 * stage, phase ^ 1);
                 if (MSX_DBG(p, 4)) mbar_arrive(bar_full + 8 * stage);
                 else {
-                    mbar_expect_tx(bar_full + 8 * stage, p.a_bytes);
+                    mbar_expect_tx(bar_full + 8 * stage, p.a_bytes + (TAIL ? p.a_bytes_tail : 0u));
                     tma_load_4d(sA + stage * p.a_stage, &tmA, bar_full + 8 * stage, 0, x0 + p.ox_min, y0 + p.oy_min, img);
+                    if (TAIL) tma_load_4d(sA + stage * p.a_stage + p.a_tail_off, &tmAt, bar_full + 8 * stage, 64, x0 + p.ox_min, y0 + p.oy_min, img);
                 }
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
@@ -541,14 +549,20 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             // The issuing thread is latency bound on its own instruction stream (measured: the issue loop, not
             // TMA, MMA or the epilogue, set the tile rate), so TAPS / KSTEPS are template constants, the loops
             // are fully unrolled without predicates and per-tap address offsets live in registers.
-            uint32_t a_off[TAPS], b_lo[TAPS];
+            uint32_t a_off[TAPS], b_lo[TAPS], a_off_t[TAIL ? TAPS : 1], b_lo_t[TAIL ? TAPS : 1];
 #pragma unroll
             for (int tap = 0; tap < TAPS; ++tap) {
                 const int r = tap / p.kw, s = tap - r * p.kw;
                 const int ry = r * p.mul_t + p.off_h - p.oy_min, sx = s * p.mul_t + p.off_w - p.ox_min;
                 a_off[tap] = (uint32_t)((ry * p.Wh + sx) * 128) >> 4;
                 b_lo[tap] = (((sB + tap * p.b_tap_bytes) & 0x3FFFFu) >> 4) | (1u << 16);
+                if (TAIL) {
+                    a_off_t[tap] = (uint32_t)((ry * p.Wh + sx) * 32) >> 4;          // 32 B per pixel row in the tail patch
+                    b_lo_t[tap] = (((sBt + tap * p.b_tail_bytes) & 0x3FFFFu) >> 4) | (1u << 16);
+                }
             }
+            const uint32_t hi_a_t = (uint32_t)((p.Wh * 32) >> 4) | (1u << 14) | (6u << 29);     // SBO, version 1, SWIZZLE_32B
+            const uint32_t hi_b_t = (uint32_t)(256 >> 4) | (1u << 14) | (6u << 29);
             const uint32_t hi_a = (uint32_t)((p.Wh * 128) >> 4) | (1u << 14) | (2u << 29);     // SBO, version 1, SWIZZLE_128B
             const uint32_t hi_b = (uint32_t)(1024 >> 4) | (1u << 14) | (2u << 29);
             const int nacc = p.nacc, stages = p.stages, total = total_units, BN = p.BN;
@@ -573,6 +587,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         if (tap == 0 && k == 0) umma_bf16_lh<0>(tmem_d, a_lo + a_off[tap], hi_a, b_lo[tap], hi_b, idesc);
                         else umma_bf16_lh<1>(tmem_d, a_lo + a_off[tap] + 2 * k, hi_a, b_lo[tap] + 2 * k, hi_b, idesc);
                     }
+                    if (TAIL) umma_bf16_lh<1>(tmem_d, a_lo + (p.a_tail_off >> 4) + a_off_t[tap], hi_a_t, b_lo_t[tap], hi_b_t, idesc);
                 }
                 }
                 if (MSX_DBG(p, 16)) { mbar_arrive(bar_empty + 8 * stage); mbar_arrive(bar_tfull + 8 * as); }
@@ -1175,8 +1190,11 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     if (mode == 0) return MSX_OK;
     const int K = fwd_pass ? d->cin : d->cout, Nc = fwd_pass ? d->cout : d->cin;
     const int Kp = round_up(K, 8), Np = round_up(Nc, 16), taps = d->kh * d->kw;
-    if (Kp > 64 || Np > 256 || taps > 9) return MSX_OK;         // taps == 1 (1x1): no halo, but resident weights + lean issue loop
-    if ((size_t)taps * Np * 128 > 80 * 1024) return MSX_OK;
+    // 64 < Kp <= 80 (DUCK-Net's 68 channels): the last 16 channels travel as a second, 32 B-per-pixel patch (SWIZZLE_32B)
+    static const int halo_tail_on = [] { const char* e = getenv("MSX_HALO_TAIL"); return e ? atoi(e) : 1; }();
+    const bool tail = Kp > 64 && Kp <= 80 && halo_tail_on;
+    if ((Kp > 64 && !tail) || Np > 256 || taps > 9) return MSX_OK;         // taps == 1 (1x1): no halo, but resident weights + lean issue loop
+    if ((size_t)taps * Np * (tail ? 160 : 128) > (tail ? 120u : 80u) * 1024) return MSX_OK;
     const int span_w = (d->kw - 1) * d->dil, span_h = (d->kh - 1) * d->dil;
     if (8 + span_w > 16) return MSX_OK;
     HaloParams p;
@@ -1192,11 +1210,14 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     // absolute shared-memory address, so the row pitch need not be a multiple of the 1024 B swizzle period.
     static const int tight = [] { const char* e = getenv("MSX_HALO_TIGHT"); return e ? atoi(e) : 1; }();
     p.Hh = 16 + span_h;
-    p.BN = Np; p.ksteps = (Kp + 15) / 16;
+    p.BN = Np; p.ksteps = tail ? 4 : (Kp + 15) / 16;
     p.Nc = Nc; p.ncp = round_up(Nc, 8); p.ldd = fwd_pass ? d->ldy : d->ldx;
     p.b_tap_bytes = (uint32_t)p.BN * 128;
+    p.b_tail_bytes = tail ? (uint32_t)p.BN * 32 : 0;
+    p.b_tail_base = ((uint32_t)taps * p.b_tap_bytes + 1023u) & ~1023u;
     const uint32_t stat_bytes = ep.stats ? stat_smem_bytes(p.ncp) : 0;
-    const uint32_t bres = (((uint32_t)taps * p.b_tap_bytes + 1023u) & ~1023u) + stat_bytes;      // resident bytes: weights + statistics
+    const uint32_t budget = tail ? 214u * 1024u : kSmemBudget;     // 115 KB of resident weights: three stages only just fit
+    const uint32_t bres = ((p.b_tail_base + (uint32_t)taps * p.b_tail_bytes + 1023u) & ~1023u) + stat_bytes;      // resident bytes: weights + statistics
     p.nacc = 512 / p.BN < kMaxAcc ? 512 / p.BN : kMaxAcc;
     if (p.nacc % 2) --p.nacc;                                     // two epilogue groups alternate tiles
 #ifdef MSX_ABLATION
@@ -1211,12 +1232,14 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     // so the per-box cost of the TMA unit is not what bounds these layers.  Kept for the next round's layout work.
     p.boxes_x = (p.tiles_x + 1) / 2;
     p.total_boxes = p.boxes_x * p.tiles_y * p.N;
-    p.tw = (want_pair && tight && p.issuers == 2 && (p.tiles_x % 2 == 0 || p.tiles_x >= 9)) ? 2 : 1;
+    p.tw = (want_pair && !tail && tight && p.issuers == 2 && (p.tiles_x % 2 == 0 || p.tiles_x >= 9)) ? 2 : 1;
     for (;;) {
         p.Wh = p.tw == 2 ? 16 + span_w : (tight ? 8 + span_w : (span_w > 0 ? 16 : 8));
         p.a_bytes = (uint32_t)p.Hh * p.Wh * 128;
-        p.a_stage = (p.a_bytes + 1023u) & ~1023u;
-        int stages = bres + 2 * p.a_stage <= kSmemBudget ? (int)((kSmemBudget - bres) / p.a_stage) : 0;
+        p.a_tail_off = (p.a_bytes + 1023u) & ~1023u;
+        p.a_bytes_tail = tail ? (uint32_t)p.Hh * p.Wh * 32 : 0;
+        p.a_stage = (p.a_tail_off + p.a_bytes_tail + 1023u) & ~1023u;
+        int stages = bres + 2 * p.a_stage <= budget ? (int)((budget - bres) / p.a_stage) : 0;
         p.stages = stages > kMaxStages ? kMaxStages : stages;
         if (p.stages >= 2 || p.tw == 1) break;
         p.tw = 1;                                                 // the wide box does not leave room for two stages
@@ -1239,35 +1262,48 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     while (cols < p.nacc * p.BN) cols <<= 1;
     p.tmem_cols = cols;
     const int lds = fwd_pass ? d->ldx : d->ldy;
-    CUtensorMap tmA, tmB;
+    CUtensorMap tmA, tmB, tmAt, tmBt;
     {
         cuuint64_t dims[4] = {(cuuint64_t)Kp, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.N};
         cuuint64_t strides[3] = {(cuuint64_t)lds * 2, (cuuint64_t)lds * 2 * p.W, (cuuint64_t)lds * 2 * p.W * p.H};
         cuuint32_t box[4] = {64, (cuuint32_t)p.Wh, (cuuint32_t)p.Hh, 1};
         MSX_TRY(make_map(&tmA, 4, src, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B));
+        tmAt = tmA;
+        if (tail) {
+            cuuint32_t boxt[4] = {16, (cuuint32_t)p.Wh, (cuuint32_t)p.Hh, 1};
+            MSX_TRY(make_map(&tmAt, 4, src, dims, strides, boxt, CU_TENSOR_MAP_SWIZZLE_32B));
+        }
     }
     {
         cuuint64_t dims[3] = {(cuuint64_t)Kp, (cuuint64_t)Np, (cuuint64_t)taps};
         cuuint64_t strides[2] = {(cuuint64_t)Kp * 2, (cuuint64_t)Kp * 2 * Np};
         cuuint32_t box[3] = {64, (cuuint32_t)p.BN, 1};
         MSX_TRY(make_map(&tmB, 3, packed, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B));
+        tmBt = tmB;
+        if (tail) {
+            cuuint32_t boxt[3] = {16, (cuuint32_t)p.BN, 1};
+            MSX_TRY(make_map(&tmBt, 3, packed, dims, strides, boxt, CU_TENSOR_MAP_SWIZZLE_32B));
+        }
     }
     const size_t smem = 1024 + bres + (size_t)p.stages * p.a_stage + 16 * kMaxStages + 16 * kMaxAcc + 96;
     const int units = p.tw == 2 ? p.total_boxes : p.total_tiles;
     const int grid = units < kNumSMs ? units : kNumSMs;
     const double M = (double)p.N * p.H * p.W;
-    typedef void (*HaloKernel)(const CUtensorMap, const CUtensorMap, bf16*, const ConvEpilogue, const HaloParams);
+    typedef void (*HaloKernel)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const CUtensorMap, bf16*, const ConvEpilogue, const HaloParams);
     HaloKernel kern = nullptr;
-#define MSX_HALO_CASE(T, K) if (taps == T && p.ksteps == K) kern = conv_tc_halo_kernel<T, K>;
+#define MSX_HALO_CASE(T, K) if (taps == T && p.ksteps == K && !tail) kern = conv_tc_halo_kernel<T, K, false>;
     MSX_HALO_CASE(9, 1) MSX_HALO_CASE(9, 2) MSX_HALO_CASE(9, 3) MSX_HALO_CASE(9, 4)
     MSX_HALO_CASE(7, 1) MSX_HALO_CASE(7, 2) MSX_HALO_CASE(7, 3) MSX_HALO_CASE(7, 4)
     MSX_HALO_CASE(1, 1) MSX_HALO_CASE(1, 2) MSX_HALO_CASE(1, 3) MSX_HALO_CASE(1, 4)
 #undef MSX_HALO_CASE
+    if (tail && taps == 9) kern = conv_tc_halo_kernel<9, 4, true>;
+    if (tail && taps == 7) kern = conv_tc_halo_kernel<7, 4, true>;
+    if (tail && taps == 1) kern = conv_tc_halo_kernel<1, 4, true>;
     if (!kern) return MSX_OK;                                     // other tap counts: streaming kernel
     MSX_TRY(ensure_big_smem(reinterpret_cast<const void*>(kern)));     // > 48 KB dynamic smem: once per device and instantiation
     {
         ProfScope ps__(K_CONV_TC, st, M * (K + Nc) * 2.0, 2.0 * M * Nc * K * taps);
-        kern<<<grid, kHaloThreads2, smem, st>>>(tmA, tmB, static_cast<bf16*>(dst), ep, p);
+        kern<<<grid, kHaloThreads2, smem, st>>>(tmA, tmB, tmAt, tmBt, static_cast<bf16*>(dst), ep, p);
     }
     MSX_LAUNCH_CHECK();
     if (ep.stats && !ep.bnf.ticket) MSX_TRY(bn_finalize_launch(ep.bnf, grid, st));

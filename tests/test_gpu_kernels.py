@@ -86,6 +86,12 @@ TC_CASES = [
     (64, 64, 1, 1, 1, 24, 40, 2),       # K = 4
     (3, 17, 1, 1, 1, 32, 32, 2),        # K = 1 (DUCK(3 -> 17) shortcuts)
     (34, 17, 1, 1, 1, 32, 32, 2),       # up-path shortcut 2b -> b
+    (68, 68, 3, 3, 1, 24, 40, 2),       # halo kernel with a channel tail: 64 + a 16-wide SWIZZLE_32B patch (fprop and dgrad)
+    (68, 68, 3, 3, 2, 32, 32, 2),
+    (68, 34, 3, 3, 1, 24, 24, 2),       # fprop with the tail (K = 68), dgrad without (K = 34)
+    (68, 68, 1, 7, 1, 16, 40, 2),
+    (68, 68, 7, 1, 1, 40, 16, 2),
+    (68, 68, 1, 1, 1, 24, 24, 3),
 ]
 
 
@@ -204,6 +210,7 @@ BN_FUSED_CASES = [
     (3, 17, 3, 1, 1, 33, 47, 3),        # ragged tiles: rows past the image must not enter the statistics
     (34, 34, 3, 1, 2, 24, 24, 2),       # halo kernel, 40 columns: one 32-chunk + one 16-chunk
     (64, 64, 1, 1, 1, 24, 40, 2),       # 1x1 halo kernel, two 32-column chunks
+    (68, 68, 3, 1, 1, 24, 40, 2),       # halo kernel with the channel tail, 72 stored columns (32 + 32 + 16)
     (17, 17, (1, 7), 1, 1, 20, 40, 2),
     (136, 136, 3, 1, 1, 22, 22, 2),     # streaming kernel, 136 columns
     (272, 136, 3, 1, 1, 11, 11, 2),
