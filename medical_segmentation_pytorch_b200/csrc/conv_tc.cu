@@ -1134,58 +1134,23 @@ bool conv_tc_gather_supported(const msx_conv_desc* d, bool fwd_pass) {
     return d->h % 2 == 0 && d->w % 2 == 0 && d->h == 2 * d->oh && d->w == 2 * d->ow;
 }
 
-static size_t wgrad_ws_one(const msx_conv_desc* d) {
+size_t conv_wgrad_tc_ws_bytes(const msx_conv_desc* d) {
     WgParams p;
     wgrad_plan(d, p);
     return (size_t)p.splits * p.kh * p.kw * p.Apad * (size_t)p.Bpad * sizeof(float);
 }
 
-// 64 < Cin <= 128 at stride 1 (DUCK-Net's 68 channels): the x side does not fit the halo mode's one 64-channel group and
-// the streaming mode re-fetches the x tile once per tap (L2 -> shared-memory bound: 59 us at 16x88x88).  Two halo-mode
-// passes instead - input channels [0, 64) and [64, Cin) - each writing its slice of dW; dy is read twice.
-static bool wgrad_split_b(const msx_conv_desc* d, msx_conv_desc* d1, msx_conv_desc* d2) {
-    static const int on = [] { const char* e = getenv("MSX_WGRAD_SPLIT"); return e ? atoi(e) : 1; }();
-    if (!on || d->stride != 1 || d->transposed || d->cin <= 64 || d->cin > 128) return false;
-    *d1 = *d; d1->cin = 64;
-    *d2 = *d; d2->cin = d->cin - 64;
-    WgParams p;
-    wgrad_plan(d1, p);
-    return p.halo != 0;
-}
-
-size_t conv_wgrad_tc_ws_bytes(const msx_conv_desc* d) {
-    size_t n = wgrad_ws_one(d);
-    msx_conv_desc d1, d2;
-    if (wgrad_split_b(d, &d1, &d2)) {
-        const size_t a = wgrad_ws_one(&d1), b = wgrad_ws_one(&d2);
-        if (a > n) n = a;
-        if (b > n) n = b;
-    }
-    return n;
-}
-
-int wgrad_reduce_launch(const float* partial, int splits, int taps, int A, int B, int Apad, int Bpad, float* dw, cudaStream_t st, int Btot, int b_off);
+int wgrad_reduce_launch(const float* partial, int splits, int taps, int A, int B, int Apad, int Bpad, float* dw, cudaStream_t st);
 
 // x: module input (big side, cin), dy: gradient of the module output (small side, cout); dw: [cout][cin][kh][kw] fp32.
 static int make_src_maps(PhaseMaps& maps, const void* src, int Kp, int N, int Hs, int Ws, int lds, int stride,
                          int chunk, int tw, int th, unsigned used_mask);
 static unsigned build_taps(const msx_conv_desc* d, bool f_form, int pa, int pb, TapTable& t);
 
-static int conv_wgrad_tc_one(const msx_conv_desc* d, const void* x, const void* dy, float* dw, void* ws, size_t ws_bytes, cudaStream_t st, int Btot, int b_off);
-
 int conv_wgrad_tc(const msx_conv_desc* d, const void* x, const void* dy, float* dw, void* ws, size_t ws_bytes, cudaStream_t st) {
-    msx_conv_desc d1, d2;
-    if (wgrad_split_b(d, &d1, &d2)) {
-        MSX_TRY(conv_wgrad_tc_one(&d1, x, dy, dw, ws, ws_bytes, st, d->cin, 0));
-        return conv_wgrad_tc_one(&d2, static_cast<const bf16*>(x) + 64, dy, dw, ws, ws_bytes, st, d->cin, 64);
-    }
-    return conv_wgrad_tc_one(d, x, dy, dw, ws, ws_bytes, st, 0, 0);
-}
-
-static int conv_wgrad_tc_one(const msx_conv_desc* d, const void* x, const void* dy, float* dw, void* ws, size_t ws_bytes, cudaStream_t st, int Btot, int b_off) {
     WgParams p;
     wgrad_plan(d, p);
-    const size_t need = wgrad_ws_one(d);
+    const size_t need = conv_wgrad_tc_ws_bytes(d);
     if (ws_bytes < need) return set_error(MSX_ERR_WORKSPACE, "conv wgrad (tcgen05): workspace %zu < %zu", ws_bytes, need);
     const void* small = d->transposed ? x : dy;
     const void* big = d->transposed ? dy : x;
@@ -1213,7 +1178,7 @@ static int conv_wgrad_tc_one(const msx_conv_desc* d, const void* x, const void* 
         wgrad_tc_kernel<<<grid, kThreads, smem, st>>>(tmS, tmG, static_cast<float*>(ws), p);
     }
     MSX_LAUNCH_CHECK();
-    return wgrad_reduce_launch(static_cast<const float*>(ws), p.splits, taps, A, B, p.Apad, p.Bpad, dw, st, Btot, b_off);
+    return wgrad_reduce_launch(static_cast<const float*>(ws), p.splits, taps, A, B, p.Apad, p.Bpad, dw, st);
 }
 
 static inline uint32_t stat_smem_bytes(int ncp) { return 16u * (uint32_t)((ncp + 31) & ~31) * 8u + 16u; }
