@@ -754,6 +754,12 @@ struct WgParams {
     int halo, Wh, Hh;                 // halo mode: one x patch (+halo) per pixel tile serves every tap
     TapTable taps;                    // streaming mode: per tap, which phase view of the big side and which shift
     int TNa, G, ncg;                  // tap-stacked mode (halo == 2): N = dy channels, G x-taps share one MMA's M axis
+    // halo == 2 with rowN > 0: the kh filter ROWS are stacked on the MMA's N axis as well.  The x patch then carries no
+    // y halo; the dy patch does (HhA = 16 + (kh-1)*dil rows) and is the MN-major B operand whose N groups - rowN channels
+    // each - are dil image rows apart (block j <-> filter row kh-1-j).  One MMA covers G x kh taps: a 3x3 at <= 32
+    // channels needs 8 MMAs per 128-pixel tile instead of 24.
+    int rowN, HhA;
+    uint32_t a_box_bytes;             // bytes of one dy TMA box
 };
 
 // MN-major operand descriptor: MN groups `lbo` bytes apart, 8-row (K) groups 8*row_bytes apart.
@@ -813,15 +819,16 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
             for (int64_t t = t_beg; t < t_end; ++t) {
                 const int img = (int)(t / tiles_per_img), rem = (int)(t % tiles_per_img);
                 const int y0 = (rem / p.tiles_x) * p.th, x0 = (rem % p.tiles_x) * p.tw;
+                const int ya = p.rowN ? y0 - (p.kh - 1) * p.dil + p.pad_h : y0;        // rows stacked on N: dy patch with the y halo
                 mbar_wait(barA_empty + 8 * stA, phA ^ 1);
-                mbar_expect_tx(barA_full + 8 * stA, groupsA * 128 * rbA);
+                mbar_expect_tx(barA_full + 8 * stA, groupsA * p.a_box_bytes);
                 for (int g = 0; g < groupsA; ++g)
-                    tma_load_4d(sA + stA * p.a_stage + g * 128 * rbA, &tmS, barA_full + 8 * stA, a0 + g * p.chunkA, x0, y0, img);
+                    tma_load_4d(sA + stA * p.a_stage + g * 128 * rbA, &tmS, barA_full + 8 * stA, a0 + g * p.chunkA, x0, ya, img);
                 if (++stA == SA) { stA = 0; phA ^= 1; }
                 if (p.halo) {
                     mbar_wait(barB_empty + 8 * stB, phB ^ 1);
                     mbar_expect_tx(barB_full + 8 * stB, (uint32_t)p.Hh * p.Wh * rbB);
-                    tma_load_4d(sB + stB * p.b_stage, &tmG.m[0], barB_full + 8 * stB, b0, x0 - p.pad_w, y0 - p.pad_h, img);
+                    tma_load_4d(sB + stB * p.b_stage, &tmG.m[0], barB_full + 8 * stB, b0, x0 - p.pad_w, p.rowN ? y0 : y0 - p.pad_h, img);
                     if (++stB == p.stagesB) { stB = 0; phB ^= 1; }
                 } else {
                     for (int k = 0; k < ntap; ++k) {
@@ -849,23 +856,27 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
                 // MN groups only ONE PIXEL apart (LBO = dil * row bytes): the G groups of one MMA are the same window
                 // shifted by 0..G-1 taps in x, so M = 128 carries G taps x (32|64) channels instead of 17 useful rows,
                 // and a 3x3 needs 3 MMAs per K-step instead of 9.  D[(s, ci)][co] lives in kh * ncg accumulators.
+                const int accN = p.rowN ? p.kh * p.rowN : p.TNa;                   // columns of one accumulator
                 const uint32_t idesc2 = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) |
-                                        ((uint32_t)(p.TNa >> 3) << 17) | ((128u >> 4) << 24);
+                                        ((uint32_t)(accN >> 3) << 17) | ((128u >> 4) << 24);
                 constexpr int kMaxAccQ = 9;
-                const int nq = p.kh * p.ncg;
+                const int nq = p.rowN ? p.ncg : p.kh * p.ncg;
                 uint32_t x_off[kMaxAccQ];
 #pragma unroll
                 for (int q = 0; q < kMaxAccQ; ++q) {
-                    const int r = q / p.ncg, cg = q - r * p.ncg;
+                    const int r = p.rowN ? 0 : q / p.ncg, cg = p.rowN ? q : q - r * p.ncg;
                     x_off[q] = (uint32_t)((r * p.dil * p.Wh + cg * p.G * p.dil) * (int)rbB) >> 4;
                 }
                 const uint32_t hi_x = (uint32_t)((p.Wh * rbB) >> 4) | (1u << 14) | ((rbB == 128 ? 2u : 4u) << 29);
                 const uint32_t hi_y = ((8 * rbA) >> 4) | (1u << 14) | ((rbA == 128 ? 2u : 4u) << 29);
                 const uint32_t x_lo0 = ((sB & 0x3FFFFu) >> 4) | ((((uint32_t)p.dil * rbB) >> 4) << 16);
-                const uint32_t y_lo0 = ((sA & 0x3FFFFu) >> 4) | ((((128 * rbA) >> 4) & 0x3FFFu) << 16);
+                // dy operand: N groups 128 pixel rows apart (several channel groups of one tile), or - rows stacked on N -
+                // dil image rows (8 pixels each) apart: the same channels seen through kh shifted windows
+                const uint32_t y_lbo = p.rowN ? (uint32_t)p.dil * 8u * rbA : 128u * rbA;
+                const uint32_t y_lo0 = ((sA & 0x3FFFFu) >> 4) | (((y_lbo >> 4) & 0x3FFFu) << 16);
                 const uint32_t x_kk = (uint32_t)(2 * p.Wh * rbB) >> 4, y_kk = (16 * rbA) >> 4;
                 const uint32_t a_st = p.a_stage >> 4, b_st = p.b_stage >> 4;
-                const int stagesB = p.stagesB, TNa = p.TNa;
+                const int stagesB = p.stagesB, TNa = accN;
                 for (int64_t t = t_beg; t < t_end; ++t) {
                     mbar_wait(barA_full + 8 * stA, phA);
                     mbar_wait(barB_full + 8 * stB, phB);
@@ -962,13 +973,15 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
         if (p.halo == 2) {
             const int g = row / p.chunkB, ci = row - g * p.chunkB;
             const int nq = p.kh * p.ncg;
+            const int blk = p.rowN ? p.rowN : p.TNa;                 // columns of one (filter row, x-tap group) block
             for (int q = 0; q < nq; ++q) {
-                const int r = q / p.ncg, cg = q - r * p.ncg;
+                // tap-stacked: q = r * ncg + cg; rows on N as well: q = cg * kh + j with block j holding filter row kh-1-j
+                const int r = p.rowN ? p.kh - 1 - q % p.kh : q / p.ncg, cg = p.rowN ? q / p.kh : q % p.ncg;
                 const int sx = cg * p.G + g;
                 const bool ok = sx < p.kw && ci < p.Bp;
                 float* out = partial + (((int64_t)split * taps + r * p.kw + sx) * p.Apad) * p.Bpad + ci;
-                const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + q * p.TNa;
-                for (int c0 = 0; c0 < p.TNa; c0 += 16) {
+                const uint32_t taddr = tmem_base + ((uint32_t)(quad * 32) << 16) + q * blk;
+                for (int c0 = 0; c0 < blk; c0 += 16) {
                     uint32_t v[16];
                     if (t_end > t_beg) { tmem_ld16(taddr + c0, v); tmem_ld_wait(); }
                     else {
@@ -1082,7 +1095,7 @@ void wgrad_plan(const msx_conv_desc* d, WgParams& p) {
             p.b_stage = ((uint32_t)p.Hh * p.Wh * 128u + 1023u) & ~1023u;
         }
     }
-    p.TNa = 0; p.G = 0; p.ncg = 0;
+    p.TNa = 0; p.G = 0; p.ncg = 0; p.rowN = 0; p.HhA = 0;
     if (p.halo == 1 && p.Ap <= 128 && halo_mode() != 3) {
         // tap-stacked variant: see the halo == 2 branch of wgrad_tc_kernel
         const int chunkB = p.Bp <= 32 ? 32 : 64, G = 128 / chunkB, ncg = (p.kw + G - 1) / G;
@@ -1097,6 +1110,20 @@ void wgrad_plan(const msx_conv_desc* d, WgParams& p) {
             int cols2 = 32;
             while (cols2 < p.kh * ncg * TNa) cols2 <<= 1;
             p.tmem_cols = cols2;
+            // filter rows on the N axis too (see WgParams::rowN): the dy side must be ONE channel group
+            static const int rows_on_n = [] { const char* e = getenv("MSX_WGRAD_ROWS_ON_N"); return e ? atoi(e) : 1; }();
+            const int rowN = p.Ap <= 32 ? 32 : 64;
+            if (rows_on_n && p.kh >= 2 && p.Ap <= rowN && p.kh * rowN <= 256 && ncg * p.kh * rowN <= 512) {
+                p.rowN = rowN;
+                p.chunkA = rowN;
+                p.HhA = 16 + (p.kh - 1) * p.dil;
+                p.Hh = 16;                                              // x patch: x halo only
+                p.Wh = (ncg * G - 1) * p.dil + 8;                       // exactly as wide as the stacked taps reach
+                p.b_stage = ((uint32_t)p.Hh * p.Wh * (chunkB * 2) + 1023u) & ~1023u;
+                int cols3 = 32;
+                while (cols3 < ncg * p.kh * rowN) cols3 <<= 1;
+                p.tmem_cols = cols3;
+            }
         }
     }
     // dy ring: 4 stages when a stage is small (few channels); the stage is as large as the boxes that fill it
@@ -1106,6 +1133,12 @@ void wgrad_plan(const msx_conv_desc* d, WgParams& p) {
         const uint32_t need = (uint32_t)groupsA * 128u * (p.chunkA * 2);
         p.SA = (sa_env == 4 && need <= 16 * 1024) ? 4 : 2;
         if (p.SA == 4) p.a_stage = (need + 1023u) & ~1023u;
+        p.a_box_bytes = 128u * (p.chunkA * 2);
+        if (p.rowN) {                                                   // one dy box of HhA x 8 pixels
+            p.a_box_bytes = (uint32_t)p.HhA * 8u * (p.chunkA * 2);
+            p.a_stage = (p.a_box_bytes + 1023u) & ~1023u;
+            p.SA = p.a_stage <= 24 * 1024 ? 4 : 2;
+        }
     }
     int sb = (int)((kSmemBudget - p.SA * p.a_stage) / p.b_stage);
     p.stagesB = sb > kMaxStages ? kMaxStages : (sb < 2 ? 2 : sb);
@@ -1164,7 +1197,7 @@ int conv_wgrad_tc(const msx_conv_desc* d, const void* x, const void* dy, float* 
     {
         cuuint64_t dims[4] = {(cuuint64_t)p.Ap, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.N};
         cuuint64_t strides[3] = {(cuuint64_t)lda * 2, (cuuint64_t)lda * 2 * p.W, (cuuint64_t)lda * 2 * p.W * p.H};
-        cuuint32_t box[4] = {(cuuint32_t)p.chunkA, (cuuint32_t)p.tw, (cuuint32_t)p.th, 1};
+        cuuint32_t box[4] = {(cuuint32_t)p.chunkA, (cuuint32_t)p.tw, (cuuint32_t)(p.rowN ? p.HhA : p.th), 1};
         MSX_TRY(make_map(&tmS, 4, small, dims, strides, box, p.chunkA == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B));
     }
     MSX_TRY(make_src_maps(tmG, big, p.Bp, p.N, Hb, Wb, ldb, d->stride, p.chunkB, p.halo ? p.Wh : p.tw, p.halo ? p.Hh : p.th, mask));
