@@ -454,6 +454,8 @@ struct HaloParams {
     // channel tail (68 channels = 64 + a 16-wide box, SWIZZLE_32B): a second, 32 B-per-pixel patch after the main one in
     // every stage and a second set of resident weights after the main ones; one more K step per tap
     uint32_t a_tail_off, a_bytes_tail, b_tail_bytes, b_tail_base;
+    uint32_t rb;                   // bytes of one pixel row in shared memory: 128 (64-channel box, SWIZZLE_128B) or, for K <= 32
+                                   // channels, 64 (32-channel box, SWIZZLE_64B): the TMA unit's time per row follows the bytes it writes
     int issuers;                   // 1 or 2 MMA-issuing warps
     int tw, boxes_x, total_boxes;  // tw == 2 (pair mode): one TMA box covers two tiles side by side; issuer / epilogue group j takes tile j
 #ifdef MSX_ABLATION
@@ -554,7 +556,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             for (int tap = 0; tap < TAPS; ++tap) {
                 const int r = tap / p.kw, s = tap - r * p.kw;
                 const int ry = r * p.mul_t + p.off_h - p.oy_min, sx = s * p.mul_t + p.off_w - p.ox_min;
-                a_off[tap] = (uint32_t)((ry * p.Wh + sx) * 128) >> 4;
+                a_off[tap] = (uint32_t)((ry * p.Wh + sx) * (int)p.rb) >> 4;
                 b_lo[tap] = (((sB + tap * p.b_tap_bytes) & 0x3FFFFu) >> 4) | (1u << 16);
                 if (TAIL) {
                     a_off_t[tap] = (uint32_t)((ry * p.Wh + sx) * 32) >> 4;          // 32 B per pixel row in the tail patch
@@ -563,11 +565,12 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
             const uint32_t hi_a_t = (uint32_t)((p.Wh * 32) >> 4) | (1u << 14) | (6u << 29);     // SBO, version 1, SWIZZLE_32B
             const uint32_t hi_b_t = (uint32_t)(256 >> 4) | (1u << 14) | (6u << 29);
-            const uint32_t hi_a = (uint32_t)((p.Wh * 128) >> 4) | (1u << 14) | (2u << 29);     // SBO, version 1, SWIZZLE_128B
-            const uint32_t hi_b = (uint32_t)(1024 >> 4) | (1u << 14) | (2u << 29);
+            const uint32_t lay = p.rb == 128 ? 2u : 4u;                                        // SWIZZLE_128B : SWIZZLE_64B
+            const uint32_t hi_a = (uint32_t)((p.Wh * p.rb) >> 4) | (1u << 14) | (lay << 29);     // SBO, version 1, swizzle
+            const uint32_t hi_b = (uint32_t)((8 * p.rb) >> 4) | (1u << 14) | (lay << 29);
             const int nacc = p.nacc, stages = p.stages, total = total_units, BN = p.BN;
-            // pair mode: both issuers walk every box; issuer `me` computes the tile at x offset 8 * me (64 descriptor units)
-            const uint32_t a_stage16 = p.a_stage >> 4, a_lo0 = (((sA & 0x3FFFFu) >> 4) | (1u << 16)) + (pair ? me * 64 : 0);
+            // pair mode: both issuers walk every box; issuer `me` computes the tile at x offset 8 * me (8 pixel rows)
+            const uint32_t a_stage16 = p.a_stage >> 4, a_lo0 = (((sA & 0x3FFFFu) >> 4) | (1u << 16)) + (pair ? me * (int)((8 * p.rb) >> 4) : 0);
             mbar_wait(bar_w, 0);
             tc_fence_after();
             const int step = pair ? 1 : p.issuers, astep = pair ? 2 : p.issuers;
@@ -1245,7 +1248,9 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     p.Hh = 16 + span_h;
     p.BN = Np; p.ksteps = tail ? 4 : (Kp + 15) / 16;
     p.Nc = Nc; p.ncp = round_up(Nc, 8); p.ldd = fwd_pass ? d->ldy : d->ldx;
-    p.b_tap_bytes = (uint32_t)p.BN * 128;
+    static const int rows64 = [] { const char* e = getenv("MSX_HALO_ROWS64"); return e ? atoi(e) : 1; }();
+    p.rb = (Kp <= 32 && rows64) ? 64u : 128u;
+    p.b_tap_bytes = (uint32_t)p.BN * p.rb;
     p.b_tail_bytes = tail ? (uint32_t)p.BN * 32 : 0;
     p.b_tail_base = ((uint32_t)taps * p.b_tap_bytes + 1023u) & ~1023u;
     const uint32_t stat_bytes = ep.stats ? stat_smem_bytes(p.ncp) : 0;
@@ -1268,7 +1273,7 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     p.tw = (want_pair && !tail && tight && p.issuers == 2 && (p.tiles_x % 2 == 0 || p.tiles_x >= 9)) ? 2 : 1;
     for (;;) {
         p.Wh = p.tw == 2 ? 16 + span_w : (tight ? 8 + span_w : (span_w > 0 ? 16 : 8));
-        p.a_bytes = (uint32_t)p.Hh * p.Wh * 128;
+        p.a_bytes = (uint32_t)p.Hh * p.Wh * p.rb;
         p.a_tail_off = (p.a_bytes + 1023u) & ~1023u;
         p.a_bytes_tail = tail ? (uint32_t)p.Hh * p.Wh * 32 : 0;
         p.a_stage = (p.a_tail_off + p.a_bytes_tail + 1023u) & ~1023u;
@@ -1299,8 +1304,8 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     {
         cuuint64_t dims[4] = {(cuuint64_t)Kp, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.N};
         cuuint64_t strides[3] = {(cuuint64_t)lds * 2, (cuuint64_t)lds * 2 * p.W, (cuuint64_t)lds * 2 * p.W * p.H};
-        cuuint32_t box[4] = {64, (cuuint32_t)p.Wh, (cuuint32_t)p.Hh, 1};
-        MSX_TRY(make_map(&tmA, 4, src, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B));
+        cuuint32_t box[4] = {p.rb / 2, (cuuint32_t)p.Wh, (cuuint32_t)p.Hh, 1};
+        MSX_TRY(make_map(&tmA, 4, src, dims, strides, box, p.rb == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B));
         tmAt = tmA;
         if (tail) {
             cuuint32_t boxt[4] = {16, (cuuint32_t)p.Wh, (cuuint32_t)p.Hh, 1};
@@ -1310,8 +1315,8 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     {
         cuuint64_t dims[3] = {(cuuint64_t)Kp, (cuuint64_t)Np, (cuuint64_t)taps};
         cuuint64_t strides[2] = {(cuuint64_t)Kp * 2, (cuuint64_t)Kp * 2 * Np};
-        cuuint32_t box[3] = {64, (cuuint32_t)p.BN, 1};
-        MSX_TRY(make_map(&tmB, 3, packed, dims, strides, box, CU_TENSOR_MAP_SWIZZLE_128B));
+        cuuint32_t box[3] = {p.rb / 2, (cuuint32_t)p.BN, 1};
+        MSX_TRY(make_map(&tmB, 3, packed, dims, strides, box, p.rb == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B));
         tmBt = tmB;
         if (tail) {
             cuuint32_t boxt[3] = {16, (cuuint32_t)p.BN, 1};
