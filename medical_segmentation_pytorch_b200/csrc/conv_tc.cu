@@ -757,6 +757,8 @@ struct WgParams {
     int halo, Wh, Hh;                 // halo mode: one x patch (+halo) per pixel tile serves every tap
     TapTable taps;                    // streaming mode: per tap, which phase view of the big side and which shift
     int TNa, G, ncg;                  // tap-stacked mode (halo == 2): N = dy channels, G x-taps share one MMA's M axis
+    int gs;                           // pixels between the G stacked windows: dil, or 0 for a one-column filter (kw == 1: the groups
+                                      // past the first repeat it and are never read back, and the patch needs no x halo)
     // halo == 2 with rowN > 0: the kh filter ROWS are stacked on the MMA's N axis as well.  The x patch then carries no
     // y halo; the dy patch does (HhA = 16 + (kh-1)*dil rows) and is the MN-major B operand whose N groups - rowN channels
     // each - are dil image rows apart (block j <-> filter row kh-1-j).  One MMA covers G x kh taps: a 3x3 at <= 32
@@ -868,11 +870,11 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
 #pragma unroll
                 for (int q = 0; q < kMaxAccQ; ++q) {
                     const int r = p.rowN ? 0 : q / p.ncg, cg = p.rowN ? q : q - r * p.ncg;
-                    x_off[q] = (uint32_t)((r * p.dil * p.Wh + cg * p.G * p.dil) * (int)rbB) >> 4;
+                    x_off[q] = (uint32_t)((r * p.dil * p.Wh + cg * p.G * p.gs) * (int)rbB) >> 4;
                 }
                 const uint32_t hi_x = (uint32_t)((p.Wh * rbB) >> 4) | (1u << 14) | ((rbB == 128 ? 2u : 4u) << 29);
                 const uint32_t hi_y = ((8 * rbA) >> 4) | (1u << 14) | ((rbA == 128 ? 2u : 4u) << 29);
-                const uint32_t x_lo0 = ((sB & 0x3FFFFu) >> 4) | ((((uint32_t)p.dil * rbB) >> 4) << 16);
+                const uint32_t x_lo0 = ((sB & 0x3FFFFu) >> 4) | ((((uint32_t)p.gs * rbB) >> 4) << 16);
                 // dy operand: N groups 128 pixel rows apart (several channel groups of one tile), or - rows stacked on N -
                 // dil image rows (8 pixels each) apart: the same channels seen through kh shifted windows
                 const uint32_t y_lbo = p.rowN ? (uint32_t)p.dil * 8u * rbA : 128u * rbA;
@@ -1098,14 +1100,16 @@ void wgrad_plan(const msx_conv_desc* d, WgParams& p) {
             p.b_stage = ((uint32_t)p.Hh * p.Wh * 128u + 1023u) & ~1023u;
         }
     }
-    p.TNa = 0; p.G = 0; p.ncg = 0; p.rowN = 0; p.HhA = 0;
+    p.TNa = 0; p.G = 0; p.ncg = 0; p.rowN = 0; p.HhA = 0; p.gs = p.dil;
     if (p.halo == 1 && p.Ap <= 128 && halo_mode() != 3) {
         // tap-stacked variant: see the halo == 2 branch of wgrad_tc_kernel
         const int chunkB = p.Bp <= 32 ? 32 : 64, G = 128 / chunkB, ncg = (p.kw + G - 1) / G;
         const int TNa = round_up(A, 16);
-        if ((ncg * G - 1) * p.dil + 8 <= p.Wh && p.kh * ncg * TNa <= 512 && p.kh * ncg <= 9) {
+        const int gs = p.kw == 1 ? 0 : p.dil;
+        const int Wh2 = (ncg * G - 1) * gs + 8;                       // exactly as wide as the stacked windows reach
+        if (Wh2 <= 24 && p.kh * ncg * TNa <= 512 && p.kh * ncg <= 9) {
             p.halo = 2;
-            p.chunkB = chunkB; p.G = G; p.ncg = ncg; p.TNa = TNa;
+            p.chunkB = chunkB; p.G = G; p.ncg = ncg; p.TNa = TNa; p.gs = gs; p.Wh = Wh2;
             p.b_stage = ((uint32_t)p.Hh * p.Wh * (chunkB * 2) + 1023u) & ~1023u;
             p.a_tiles = 1; p.b_tiles = 1; p.tap_groups = 1; p.tg = taps;
             int64_t sp = kNumSMs < p.pix_tiles ? kNumSMs : p.pix_tiles;
@@ -1121,7 +1125,6 @@ void wgrad_plan(const msx_conv_desc* d, WgParams& p) {
                 p.chunkA = rowN;
                 p.HhA = 16 + (p.kh - 1) * p.dil;
                 p.Hh = 16;                                              // x patch: x halo only
-                p.Wh = (ncg * G - 1) * p.dil + 8;                       // exactly as wide as the stacked taps reach
                 p.b_stage = ((uint32_t)p.Hh * p.Wh * (chunkB * 2) + 1023u) & ~1023u;
                 int cols3 = 32;
                 while (cols3 < ncg * p.kh * rowN) cols3 <<= 1;

@@ -92,6 +92,8 @@ TC_CASES = [
     (68, 68, 1, 7, 1, 16, 40, 2),
     (68, 68, 7, 1, 1, 40, 16, 2),
     (68, 68, 1, 1, 1, 24, 24, 3),
+    (34, 34, 3, 3, 3, 48, 48, 2),       # wgrad: two x-tap groups of two, windows 3 pixels apart (17-pixel-wide patch)
+    (3, 17, 7, 1, 1, 64, 32, 2),        # wgrad: one-column filter, the stacked windows coincide
 ]
 
 
@@ -314,7 +316,7 @@ def test_maxpool_3s2(dtype):
     assert rel(from_act(a.t.grad, 24), xd.grad) < (1e-6 if dtype == torch.float32 else 1e-2)
 
 
-@pytest.mark.parametrize('case', [(17, 17, 3, 3, 1), (3, 17, 3, 3, 1), (17, 17, 1, 7, 1), (17, 17, 3, 3, 2)])
+@pytest.mark.parametrize('case', [(17, 17, 3, 3, 1), (3, 17, 3, 3, 1), (17, 17, 1, 7, 1), (17, 17, 3, 3, 2), (17, 17, 3, 3, 3), (17, 17, 7, 1, 1)])
 def test_wgrad_tcgen05_full_size(case):
     """Weight gradient at the benchmark's own size, 16 x 352 x 352 (tap-stacked halo mode, 148 pixel splits, 105 tiles
     accumulated in TMEM per CTA), against the float64 weight gradient of F.conv2d on the CPU."""

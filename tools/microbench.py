@@ -15,6 +15,7 @@ SHAPES = [  # cin, cout, kh, kw, dil, HW     (DUCKNet-17 layer classes)
     (3, 17, 3, 3, 1, 352), (17, 17, 3, 3, 1, 352), (17, 17, 3, 3, 2, 352), (17, 17, 1, 7, 1, 352), (17, 17, 1, 1, 1, 352),
     (34, 34, 3, 3, 1, 176), (68, 68, 3, 3, 1, 88), (136, 136, 3, 3, 1, 44), (272, 272, 3, 3, 1, 22), (544, 544, 3, 3, 1, 11),
     (32, 32, 3, 3, 1, 352), (64, 64, 3, 3, 1, 176), (128, 128, 3, 3, 1, 88), (256, 256, 3, 3, 1, 44), (512, 512, 3, 3, 1, 22),
+    (17, 17, 3, 3, 3, 352), (17, 17, 7, 1, 1, 352), (34, 34, 3, 3, 3, 176), (34, 34, 7, 1, 1, 176), (34, 34, 1, 7, 1, 176), (34, 34, 3, 3, 2, 176),   # 15-20
 ]
 
 
