@@ -21,6 +21,11 @@ void note_conv_engine(int engine) { g_engine = engine; }
 
 // ---- reduction tickets (common.cuh) ----
 static __device__ unsigned int g_tickets[kTicketSlots];        // zero at module load; every slot re-arms itself
+int pdl_enabled() {
+    static const int on = [] { const char* e = getenv("MSX_PDL"); return e ? atoi(e) : 1; }();
+    return on;
+}
+
 unsigned int* next_ticket() {
     static std::atomic<unsigned> ctr{0};
     static std::mutex mu;

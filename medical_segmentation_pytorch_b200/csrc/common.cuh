@@ -30,6 +30,28 @@ void note_conv_engine(int engine);
         if (rc__ != MSX_OK) return rc__;                                                           \
     } while (0)
 
+// ---- programmatic dependent launch ---------------------------------------------------------------------------------
+// The step is a chain of ~2 800 short kernels; about a quarter of its time does not scale with the batch (launch hand-over,
+// prologues, tails).  Kernels of the hot chain are launched with programmaticStreamSerialization: the next kernel of a stream
+// may become resident while this one drains and runs its prologue (shared-memory carve-up, mbarrier init, TMEM allocation)
+// up to pdl_wait(), which returns once every kernel before it has completed and its writes are visible.  A kernel launched
+// this way must not touch global memory before pdl_wait() - neither read a predecessor's output nor write a buffer a
+// predecessor may still read.  pdl_trigger() lets the successor's launch start; a kernel that never calls it triggers at exit.
+// MSX_PDL=0 launches the same kernels without the attribute (pdl_wait / pdl_trigger are then no-ops).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+int pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled();
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    (void)cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);      // errors surface through MSX_LAUNCH_CHECK()
+}
+
 constexpr int kNumSMs = 148;            // B200
 constexpr int kMaxPartialBlocks = 592;  // 4 CTAs per SM for the channel-reduction kernels
 

@@ -216,6 +216,8 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(const T* __restrict__ s
 // dW[(a*B + b)*taps + tap] = sum_split partial[split][tap][a][b]   (reference OIHW / IOHW layout)
 __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restrict__ partial, int splits, int taps, int A, int B,
                                                            int Apad, int Bpad, float* __restrict__ dw) {
+    pdl_wait();
+    pdl_trigger();
     // A CTA = 32 consecutive outputs x 8 slices of the split range.  Outputs are ordered (tap, a, b) with b
     // fastest so the partial reads are coalesced; each slice sums its splits in fixed order (4 loads in
     // flight), the 8 slice sums are combined in fixed order through shared memory: deterministic.
@@ -260,6 +262,8 @@ __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restri
 // Few splits (wide layers): one thread per output, reads coalesced along b.
 __global__ void __launch_bounds__(256) wgrad_reduce_flat_kernel(const float* __restrict__ partial, int splits, int taps, int A, int B,
                                                                 int Apad, int Bpad, float* __restrict__ dw) {
+    pdl_wait();
+    pdl_trigger();
     const int64_t total = (int64_t)A * B * taps;
     const int64_t zstride = (int64_t)taps * Apad * Bpad;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -525,7 +529,7 @@ int conv_wgrad_simt(const msx_conv_desc* d, const void* x, const void* dy, float
     MSX_LAUNCH_CHECK();
     const int64_t total = (int64_t)g.A * g.B * taps;
     const int rg = (int)((total + 31) / 32 < 4096 ? (total + 31) / 32 : 4096);
-    { ProfScope ps__(K_WGRAD_REDUCE, st, (double)total * 4 * (g.splits + 1), 0); if (g.splits >= 16) wgrad_reduce_kernel<<<rg, 256, 0, st>>>(static_cast<const float*>(ws), g.splits, taps, g.A, g.B, g.tiles_a * BT, g.tiles_b * BT, dw); else wgrad_reduce_flat_kernel<<<(int)((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096), 256, 0, st>>>(static_cast<const float*>(ws), g.splits, taps, g.A, g.B, g.tiles_a * BT, g.tiles_b * BT, dw); }
+    { ProfScope ps__(K_WGRAD_REDUCE, st, (double)total * 4 * (g.splits + 1), 0); if (g.splits >= 16) launch_pdl(wgrad_reduce_kernel, dim3(rg), dim3(256), 0, st, static_cast<const float*>(ws), g.splits, taps, g.A, g.B, g.tiles_a * BT, g.tiles_b * BT, dw); else launch_pdl(wgrad_reduce_flat_kernel, dim3((int)((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096)), dim3(256), 0, st, static_cast<const float*>(ws), g.splits, taps, g.A, g.B, g.tiles_a * BT, g.tiles_b * BT, dw); }
     MSX_LAUNCH_CHECK();
     return MSX_OK;
 }
@@ -535,8 +539,8 @@ int wgrad_reduce_launch(const float* partial, int splits, int taps, int A, int B
     const int rg = (int)((total + 31) / 32 < 4096 ? (total + 31) / 32 : 4096);
     {
         ProfScope ps__(K_WGRAD_REDUCE, st, (double)total * 4 * (splits + 1), 0);
-        if (splits >= 16) wgrad_reduce_kernel<<<rg, 256, 0, st>>>(partial, splits, taps, A, B, Apad, Bpad, dw);
-        else wgrad_reduce_flat_kernel<<<(int)((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096), 256, 0, st>>>(partial, splits, taps, A, B, Apad, Bpad, dw);
+        if (splits >= 16) launch_pdl(wgrad_reduce_kernel, dim3(rg), dim3(256), 0, st, partial, splits, taps, A, B, Apad, Bpad, dw);
+        else launch_pdl(wgrad_reduce_flat_kernel, dim3((int)((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096)), dim3(256), 0, st, partial, splits, taps, A, B, Apad, Bpad, dw);
     }
     MSX_LAUNCH_CHECK();
     return MSX_OK;

@@ -303,6 +303,8 @@ conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CU
     tc_fence_after();
     uint32_t tmem_base;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+    pdl_wait();               // everything above touched only shared memory, TMEM and kernel parameters (common.cuh)
+    pdl_trigger();
 
     const int taps = p.taps.n;
     const int tiles_per_img = p.tiles_x * p.tiles_y;
@@ -514,6 +516,8 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     tc_fence_after();
     uint32_t tmem_base;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+    pdl_wait();               // everything above touched only shared memory, TMEM and kernel parameters (common.cuh)
+    pdl_trigger();
     // work unit of the producer: one tile (8 x 16 pixels) or, in pair mode, a box of two tiles side by side (16 x 16)
     const bool pair = p.tw == 2;
     const int units_x = pair ? p.boxes_x : p.tiles_x, unit_w = pair ? 16 : 8;
@@ -815,6 +819,8 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
     tc_fence_after();
     uint32_t tmem_base;
     asm volatile("ld.shared.b32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+    pdl_wait();               // everything above touched only shared memory, TMEM and kernel parameters (common.cuh)
+    pdl_trigger();
     const int64_t tiles_per_img = (int64_t)p.tiles_x * p.tiles_y;
 
     if (warp == 0) {
@@ -1214,7 +1220,7 @@ int conv_wgrad_tc(const msx_conv_desc* d, const void* x, const void* dy, float* 
     const double Ms = (double)p.N * p.H * p.W, Mb = (double)p.N * Hb * Wb;
     {
         ProfScope ps__(K_WGRAD_TC, st, (Ms * A + Mb * B) * 2.0, 2.0 * Ms * A * B * taps);
-        wgrad_tc_kernel<<<grid, kThreads, smem, st>>>(tmS, tmG, static_cast<float*>(ws), p);
+        launch_pdl(wgrad_tc_kernel, dim3(grid), dim3(kThreads), smem, st, tmS, tmG, static_cast<float*>(ws), p);
     }
     MSX_LAUNCH_CHECK();
     return wgrad_reduce_launch(static_cast<const float*>(ws), p.splits, taps, A, B, p.Apad, p.Bpad, dw, st);
@@ -1344,7 +1350,7 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     MSX_TRY(ensure_big_smem(reinterpret_cast<const void*>(kern)));     // > 48 KB dynamic smem: once per device and instantiation
     {
         ProfScope ps__(K_CONV_TC, st, M * (K + Nc) * 2.0, 2.0 * M * Nc * K * taps);
-        kern<<<grid, kHaloThreads2, smem, st>>>(tmA, tmB, tmAt, tmBt, static_cast<bf16*>(dst), ep, p);
+        launch_pdl(kern, dim3(grid), dim3(kHaloThreads2), smem, st, tmA, tmB, tmAt, tmBt, static_cast<bf16*>(dst), ep, p);
     }
     MSX_LAUNCH_CHECK();
     if (ep.stats && !ep.bnf.ticket) MSX_TRY(bn_finalize_launch(ep.bnf, grid, st));
@@ -1513,7 +1519,7 @@ int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const
         const double Mg = (double)p.N * p.H * p.W, Ms = (double)p.N * Hs * Ws / nphase;
         {
             ProfScope ps__(K_CONV_TC, st, (Mg * Nc + Ms * K) * 2.0, 2.0 * Mg * Nc * K * p.taps.n);
-            conv_tc_kernel<<<grid, kHaloThreads, smem, st>>>(maps, tmB, maps_tail, tmB_tail, static_cast<bf16*>(dst), ep, p);
+            launch_pdl(conv_tc_kernel, dim3(grid), dim3(kHaloThreads), smem, st, maps, tmB, maps_tail, tmB_tail, static_cast<bf16*>(dst), ep, p);
         }
         MSX_LAUNCH_CHECK();
         if (ep.stats && !ep.bnf.ticket) MSX_TRY(bn_finalize_launch(ep.bnf, grid, st));

@@ -168,6 +168,8 @@ __device__ inline void fold_partials_block(const double* partials, int nblk, int
 // so the in-kernel path is only taken up to ticket_max_cp() channels (default 0: never).
 __global__ void __launch_bounds__(128) bn_finalize_kernel(int nblk, const BnFinalize f) {
     __shared__ double sh[8];
+    pdl_wait();
+    pdl_trigger();
     const int c = blockIdx.x;
     const int lane = threadIdx.x;
     if (c == 0 && lane == 0 && f.nbt && !f.sums) *f.nbt += 1;
@@ -302,6 +304,8 @@ __device__ inline void bn_bwd_finalize_all(const BnBwdFinalize& f, const double*
 
 __global__ void __launch_bounds__(128) bn_bwd_finalize_kernel(const double* partials, int nblk, const BnBwdFinalize f) {
     __shared__ double sh[8];
+    pdl_wait();
+    pdl_trigger();
     const int c = blockIdx.x;
     const int lane = threadIdx.x;
     if (c >= f.cp) return;
@@ -497,6 +501,8 @@ __global__ void __launch_bounds__(256, 3) bn_bwd_reduce_bf16_kernel(const bf16* 
                                                                     int relu, double* partials, const BnBwdFinalize fin) {
     __shared__ double shm[8 * 256];
     __shared__ int last_flag;
+    pdl_wait();
+    pdl_trigger();
     const ChanThread t = chan_thread<8>(cp, vch);
     float mu[8], sc[8], be[8], fs[8], fq[8];          // sc = invstd * gamma; fq = sum g * (x - mean), scaled by invstd at the end
 #pragma unroll
@@ -561,6 +567,8 @@ __global__ void __launch_bounds__(256, 3) bn_bwd_apply_bf16_kernel(const bf16* _
                                                                    const float* __restrict__ mean, const float* __restrict__ invstd,
                                                                    const float* __restrict__ gamma, const float* __restrict__ beta,
                                                                    const float* __restrict__ c1, const float* __restrict__ c2, int relu) {
+    pdl_wait();
+    pdl_trigger();
     const ChanThread t = chan_thread<8>(cp, vch);
     if (!t.active) return;
     float mu[8], sc[8], be[8], e[8], f[8];
@@ -608,6 +616,8 @@ __global__ void __launch_bounds__(256, 4) bn_apply_bf16_kernel(const bf16* __res
                                                                int64_t pixels, int cp, int vch, int channels,
                                                                const float* __restrict__ mean, const float* __restrict__ invstd,
                                                                const float* __restrict__ gamma, const float* __restrict__ beta, int relu) {
+    pdl_wait();
+    pdl_trigger();
     const ChanThread t = chan_thread<8>(cp, vch);
     if (!t.active) return;
     float mu[8], sc[8], sh[8];
@@ -799,6 +809,8 @@ __global__ void __launch_bounds__(256, 3) sum_bf16_kernel(SumArgs a, int up2x, i
                                                           const float* __restrict__ shift, int relu, const BnFinalize fin) {
     __shared__ double sh[STATS ? 8 * 256 : 1];
     __shared__ int last_flag;
+    pdl_wait();
+    pdl_trigger();
     const ChanThread t = chan_thread<8>(cp, vch);
     float asc[8], ash[8], fs[8], fq[8];
     const bool affine = !STATS && scale != nullptr;
@@ -1014,7 +1026,7 @@ int sum_launch_bf16(const SumArgs& a, int up2x, int h, int w, void* s, int lds, 
     const int per_iter = a.n <= 2 ? 4 : (a.n <= 4 ? 2 : 1);
     const int g = wave_grid(reinterpret_cast<const void*>(sum_bf16_kernel<STATS>), pixels, c.lanes, per_iter * 2, STATS ? kMaxPartialBlocks : (1 << 30));
     { ProfScope ps__(K_SUM, st, (double)pixels * channels * 2.0 * (a.n + 1.0), 0);
-      sum_bf16_kernel<STATS><<<dim3(g, c.nchunk), 256, 0, st>>>(a, up2x, h, w, static_cast<bf16*>(s), lds, pixels, c.cp, c.vch, partials, scale, shift, relu, fin); }
+      launch_pdl(sum_bf16_kernel<STATS>, dim3(dim3(g, c.nchunk)), dim3(256), 0, st, a, up2x, h, w, static_cast<bf16*>(s), lds, pixels, c.cp, c.vch, partials, scale, shift, relu, fin); }
     if (nblk_out) *nblk_out = g;
     MSX_LAUNCH_CHECK();
     return MSX_OK;
@@ -1034,7 +1046,7 @@ int ticket_max_cp() {
 
 // fold nblk partial rows and finalize, as its own launch (what every reduction uses when its BnFinalize has no ticket)
 int bn_finalize_launch(const BnFinalize& f, int nblk, cudaStream_t st) {
-    { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_finalize_kernel<<<f.cp, 128, 0, st>>>(nblk, f); }
+    { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); launch_pdl(bn_finalize_kernel, dim3(f.cp), dim3(128), 0, st, nblk, f); }
     MSX_LAUNCH_CHECK();
     return MSX_OK;
 }
@@ -1102,7 +1114,7 @@ int bn_apply_launch(int dtype, const void* x, int ldx, void* z, int ldz, int64_t
     if (dtype == MSX_BF16) {
         const ChanCfg c = chan_cfg<8>(channels);
         const int g = wave_grid(reinterpret_cast<const void*>(bn_apply_bf16_kernel), pixels, c.lanes, 4);
-        { ProfScope ps__(K_BN_APPLY, st, 2.0 * (double)pixels * channels * 2.0, 0); bn_apply_bf16_kernel<<<dim3(g, c.nchunk), 256, 0, st>>>(
+        { ProfScope ps__(K_BN_APPLY, st, 2.0 * (double)pixels * channels * 2.0, 0); launch_pdl(bn_apply_bf16_kernel, dim3(dim3(g, c.nchunk)), dim3(256), 0, st, 
             static_cast<const bf16*>(x), ldx, static_cast<bf16*>(z), ldz, pixels, c.cp, c.vch, channels, mean, invstd, gamma, beta, relu); }
         MSX_LAUNCH_CHECK();
         return MSX_OK;
@@ -1135,9 +1147,9 @@ int bn_bwd_reduce_launch(int dtype, const void* x, int ldx, const void* dz, int 
     if (dtype == MSX_BF16) {
         const ChanCfg c = chan_cfg<8>(channels);
         const int g = wave_grid(reinterpret_cast<const void*>(bn_bwd_reduce_bf16_kernel), pixels, c.lanes, 8, kMaxPartialBlocks);
-        { ProfScope ps__(K_BN_BWD_REDUCE, st, 2.0 * (double)pixels * channels * 2.0, 0); bn_bwd_reduce_bf16_kernel<<<dim3(g, c.nchunk), 256, 0, st>>>(
+        { ProfScope ps__(K_BN_BWD_REDUCE, st, 2.0 * (double)pixels * channels * 2.0, 0); launch_pdl(bn_bwd_reduce_bf16_kernel, dim3(dim3(g, c.nchunk)), dim3(256), 0, st, 
             static_cast<const bf16*>(x), ldx, static_cast<const bf16*>(dz), lddz, pixels, c.cp, c.vch, channels, mean, invstd, gamma, beta, relu, partials, f); }
-        if (!f.ticket) { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_bwd_finalize_kernel<<<f.cp, 128, 0, st>>>(partials, g, f); }
+        if (!f.ticket) { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); launch_pdl(bn_bwd_finalize_kernel, dim3(f.cp), dim3(128), 0, st, partials, g, f); }
         MSX_LAUNCH_CHECK();
         return MSX_OK;
     }
@@ -1146,7 +1158,7 @@ int bn_bwd_reduce_launch(int dtype, const void* x, int ldx, const void* dz, int 
         const int g = reduce_grid(pixels, c.lanes);
         { ProfScope ps__(K_BN_BWD_REDUCE, st, 2.0 * (double)pixels * channels * (double)sizeof(T), 0); bn_bwd_reduce_kernel<T><<<dim3(g, c.nchunk), 256, 0, st>>>(static_cast<const T*>(x), ldx, static_cast<const T*>(dz), lddz,
                                                                  pixels, c.cp, c.vch, channels, mean, invstd, gamma, beta, relu, partials, f); }
-        if (!f.ticket) { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); bn_bwd_finalize_kernel<<<f.cp, 128, 0, st>>>(partials, g, f); }
+        if (!f.ticket) { ProfScope ps__(K_BN_FINALIZE, st, 0, 0); launch_pdl(bn_bwd_finalize_kernel, dim3(f.cp), dim3(128), 0, st, partials, g, f); }
     });
     MSX_LAUNCH_CHECK();
     return MSX_OK;
@@ -1160,7 +1172,7 @@ int bn_bwd_apply_launch(int dtype, const void* x, int ldx, const void* dz, int l
     if (dtype == MSX_BF16) {
         const ChanCfg c = chan_cfg<8>(channels);
         const int g = wave_grid(reinterpret_cast<const void*>(bn_bwd_apply_bf16_kernel), pixels, c.lanes, 4);
-        { ProfScope ps__(K_BN_BWD_APPLY, st, 3.0 * (double)pixels * channels * 2.0, 0); bn_bwd_apply_bf16_kernel<<<dim3(g, c.nchunk), 256, 0, st>>>(
+        { ProfScope ps__(K_BN_BWD_APPLY, st, 3.0 * (double)pixels * channels * 2.0, 0); launch_pdl(bn_bwd_apply_bf16_kernel, dim3(dim3(g, c.nchunk)), dim3(256), 0, st, 
             static_cast<const bf16*>(x), ldx, static_cast<const bf16*>(dz), lddz, static_cast<bf16*>(dx), lddx, pixels, c.cp, c.vch, channels,
             mean, invstd, gamma, beta, c1, c2, relu); }
         MSX_LAUNCH_CHECK();
