@@ -36,10 +36,27 @@ void note_conv_engine(int engine);
 // may become resident while this one drains and runs its prologue (shared-memory carve-up, mbarrier init, TMEM allocation)
 // up to pdl_wait(), which returns once every kernel before it has completed and its writes are visible.  A kernel launched
 // this way must not touch global memory before pdl_wait() - neither read a predecessor's output nor write a buffer a
-// predecessor may still read.  pdl_trigger() lets the successor's launch start; a kernel that never calls it triggers at exit.
+// predecessor may still read.  griddepcontrol.launch_dependents releases the successor's launch; a kernel that never issues it
+// releases it at exit.
 // MSX_PDL=0 launches the same kernels without the attribute (pdl_wait / pdl_trigger are then no-ops).
-__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
-__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+// Where the successor's launch is released (MSX_PDL_MODE, measured on the whole step, DUCKNet-17 batch 16):
+//   2 (default)  never explicitly - at this kernel's exit: 409.4 img/s.  The gain is the pre-staged launch itself.
+//   0            right after the wait: 404.0;   1  before the wait: 401.5 - successors that become resident early only sit
+//                on registers and CTA slots that kernels of the sibling streams would have used.
+//   3            pdl_trigger_late(): when a CTA has issued its last loads (producer warp) / finished its main loop
+#ifndef MSX_PDL_MODE
+#define MSX_PDL_MODE 2
+#endif
+__device__ __forceinline__ void pdl_wait() {
+    if (MSX_PDL_MODE == 1) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_trigger() {
+    if (MSX_PDL_MODE == 0) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_trigger_late() {
+    if (MSX_PDL_MODE == 3) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
 int pdl_enabled();
 template <typename... KArgs, typename... Args>
 inline void launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {

@@ -342,6 +342,7 @@ conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CU
                     }
                 }
             }
+            pdl_trigger_late();
         }
     } else if (warp == 1) {
         // ================= MMA issuer =================
@@ -545,6 +546,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 }
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
+            pdl_trigger_late();
         }
     } else if (warp == 1 || warp == 10) {
         // Two issuers (p.issuers == 2) take alternate tiles: the per-tile barrier round trips of one overlap the
@@ -854,6 +856,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
                     }
                 }
             }
+            pdl_trigger_late();
         }
     } else if (warp == 1) {
         if (lane == 0) {

@@ -542,6 +542,7 @@ __global__ void __launch_bounds__(256, 3) bn_bwd_reduce_bf16_kernel(const bf16* 
         }
         for (; p < pixels; p += step) body(ldg16(x + p * ldx + t.c0), ldg16(dz + p * lddz + t.c0));
     }
+    pdl_trigger_late();
     double acc[16];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -840,6 +841,7 @@ __global__ void __launch_bounds__(256, 3) sum_bf16_kernel(SumArgs a, int up2x, i
         }
     }
     if (!STATS) return;
+    pdl_trigger_late();
     double acc[16];
 #pragma unroll
     for (int j = 0; j < 8; ++j) { acc[j] = (double)fs[j]; acc[8 + j] = (double)fq[j]; }
