@@ -459,6 +459,9 @@ struct HaloParams {
     uint32_t a_tail_off, a_bytes_tail, b_tail_bytes, b_tail_base;
     uint32_t rb;                   // bytes of one pixel row in shared memory: 128 (64-channel box, SWIZZLE_128B) or, for K <= 32
                                    // channels, 64 (32-channel box, SWIZZLE_64B): the TMA unit's time per row follows the bytes it writes
+    int flat;                      // 1x1, no padding: the activation is walked as one row of N*H*W pixels, a tile = 128 consecutive
+                                   // pixels = ONE contiguous run for the TMA unit instead of 16 runs of 8 pixels (tma_rate.cu: the unit
+                                   // pays ~20-35 cycles per run on top of ~1.2-1.5 per row)
     int issuers;                   // 1 or 2 MMA-issuing warps
     int tw, boxes_x, total_boxes;  // tw == 2 (pair mode): one TMA box covers two tiles side by side; issuer / epilogue group j takes tile j
 #ifdef MSX_ABLATION
@@ -536,7 +539,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             for (int t = blockIdx.x; t < total_units; t += gridDim.x) {
                 const int img = t / tiles_per_img, rem = t - img * tiles_per_img;
                 const int ty = rem / units_x;
-                const int y0 = ty * 16, x0 = (rem - ty * units_x) * unit_w;
+                const int y0 = ty * 16, x0 = p.flat ? rem * 128 : (rem - ty * units_x) * unit_w;
                 mbar_wait(bar_empty + 8 * stage, phase ^ 1);
                 if (MSX_DBG(p, 4)) mbar_arrive(bar_full + 8 * stage);
                 else {
@@ -622,7 +625,8 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         for (int t = pair ? blockIdx.x : blockIdx.x + grp * gridDim.x; t < total_units; t += (pair ? 1 : 2) * gridDim.x, it += 2) {
             const int img = t / tiles_per_img, rem = t - img * tiles_per_img;
             const int ty = rem / units_x;
-            const int y = ty * 16 + dy, x = (rem - ty * units_x) * unit_w + (pair ? grp * 8 : 0) + dx;
+            const int y = p.flat ? 0 : ty * 16 + dy;
+            const int x = p.flat ? rem * 128 + m : (rem - ty * units_x) * unit_w + (pair ? grp * 8 : 0) + dx;
             const bool valid = y < p.H && x < p.W && !MSX_DBG(p, 1);
             bf16* out = dst + ((int64_t)(img * p.H + y) * p.W + x) * p.ldd;
             const int as = it % p.nacc;
@@ -1182,7 +1186,20 @@ bool conv_tc_gather_supported(const msx_conv_desc* d, bool fwd_pass) {
     return d->h % 2 == 0 && d->w % 2 == 0 && d->h == 2 * d->oh && d->w == 2 * d->ow;
 }
 
+// 1x1 without padding: the weight gradient does not care where a pixel sits - walk the activations as ONE row of N*H*W pixels,
+// so that a 128-pixel tile is one contiguous run for the TMA unit (see HaloParams::flat)
+static const msx_conv_desc* flat_1x1(const msx_conv_desc* d, msx_conv_desc* tmp) {
+    static const int on = [] { const char* e = getenv("MSX_FLAT_1X1"); return e ? atoi(e) : 1; }();
+    const int64_t pixels = (int64_t)d->n * d->h * d->w;
+    if (!on || d->kh != 1 || d->kw != 1 || d->stride != 1 || d->transposed || d->pad_h || d->pad_w || pixels >= (1ll << 31) - 128) return d;
+    *tmp = *d;
+    tmp->n = 1; tmp->h = tmp->oh = 1; tmp->w = tmp->ow = (int)pixels;
+    return tmp;
+}
+
 size_t conv_wgrad_tc_ws_bytes(const msx_conv_desc* d) {
+    msx_conv_desc flat_d;
+    d = flat_1x1(d, &flat_d);
     WgParams p;
     wgrad_plan(d, p);
     return (size_t)p.splits * p.kh * p.kw * p.Apad * (size_t)p.Bpad * sizeof(float);
@@ -1196,6 +1213,8 @@ static int make_src_maps(PhaseMaps& maps, const void* src, int Kp, int N, int Hs
 static unsigned build_taps(const msx_conv_desc* d, bool f_form, int pa, int pb, TapTable& t);
 
 int conv_wgrad_tc(const msx_conv_desc* d, const void* x, const void* dy, float* dw, void* ws, size_t ws_bytes, cudaStream_t st) {
+    msx_conv_desc flat_d;
+    d = flat_1x1(d, &flat_d);
     WgParams p;
     wgrad_plan(d, p);
     const size_t need = conv_wgrad_tc_ws_bytes(d);
@@ -1248,7 +1267,11 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     HaloParams p;
     p.N = d->n; p.H = d->h; p.W = d->w;
     p.tiles_x = (p.W + 7) / 8; p.tiles_y = (p.H + 15) / 16;
-    const double eff = (double)p.W * p.H / ((double)p.tiles_x * p.tiles_y * 128.0);
+    static const int flat_on = [] { const char* e = getenv("MSX_FLAT_1X1"); return e ? atoi(e) : 1; }();
+    const int64_t pixels = (int64_t)d->n * d->h * d->w;
+    p.flat = (flat_on && taps == 1 && d->pad_h == 0 && d->pad_w == 0 && pixels < (1ll << 31) - 128) ? 1 : 0;
+    if (p.flat) { p.N = 1; p.H = 1; p.W = (int)pixels; p.tiles_x = (int)((pixels + 127) / 128); p.tiles_y = 1; }
+    const double eff = p.flat ? 1.0 : (double)p.W * p.H / ((double)p.tiles_x * p.tiles_y * 128.0);
     if (eff < 0.75) return MSX_OK;
     p.total_tiles = p.tiles_x * p.tiles_y * p.N;
     p.kh = d->kh; p.kw = d->kw;
@@ -1282,7 +1305,7 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     // so the per-box cost of the TMA unit is not what bounds these layers.  Kept for the next round's layout work.
     p.boxes_x = (p.tiles_x + 1) / 2;
     p.total_boxes = p.boxes_x * p.tiles_y * p.N;
-    p.tw = (want_pair && !tail && tight && p.issuers == 2 && (p.tiles_x % 2 == 0 || p.tiles_x >= 9)) ? 2 : 1;
+    p.tw = (want_pair && !p.flat && !tail && tight && p.issuers == 2 && (p.tiles_x % 2 == 0 || p.tiles_x >= 9)) ? 2 : 1;
     for (;;) {
         p.Wh = p.tw == 2 ? 16 + span_w : (tight ? 8 + span_w : (span_w > 0 ? 16 : 8));
         p.a_bytes = (uint32_t)p.Hh * p.Wh * p.rb;
@@ -1316,11 +1339,12 @@ static int conv_gather_tc_halo(const msx_conv_desc* d, bool fwd_pass, const void
     {
         cuuint64_t dims[4] = {(cuuint64_t)Kp, (cuuint64_t)p.W, (cuuint64_t)p.H, (cuuint64_t)p.N};
         cuuint64_t strides[3] = {(cuuint64_t)lds * 2, (cuuint64_t)lds * 2 * p.W, (cuuint64_t)lds * 2 * p.W * p.H};
-        cuuint32_t box[4] = {p.rb / 2, (cuuint32_t)p.Wh, (cuuint32_t)p.Hh, 1};
+        const cuuint32_t bw = p.flat ? 128u : (cuuint32_t)p.Wh, bh = p.flat ? 1u : (cuuint32_t)p.Hh;      // flat: Wh x Hh = 8 x 16 rows as one run
+        cuuint32_t box[4] = {p.rb / 2, bw, bh, 1};
         MSX_TRY(make_map(&tmA, 4, src, dims, strides, box, p.rb == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B));
         tmAt = tmA;
         if (tail) {
-            cuuint32_t boxt[4] = {16, (cuuint32_t)p.Wh, (cuuint32_t)p.Hh, 1};
+            cuuint32_t boxt[4] = {16, bw, bh, 1};
             MSX_TRY(make_map(&tmAt, 4, src, dims, strides, boxt, CU_TENSOR_MAP_SWIZZLE_32B));
         }
     }
