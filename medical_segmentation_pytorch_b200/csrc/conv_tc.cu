@@ -242,6 +242,43 @@ __device__ __forceinline__ void umma_bf16_lhr(uint32_t tmem_d, uint32_t a_lo, ui
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
+// Warp-uniform issue: ALL lanes of the issuing warp run the loop (barrier waits, descriptor arithmetic) with identical values
+// and one elected lane issues the instruction.  In a block entered by `if (lane == 0)` the compiler cannot know that the
+// descriptors are warp-uniform and moves every one of them to the uniform registers UTCHMMA wants through an
+// ELECT / R2UR.BROADCAST / BRA.U.ANY loop - four such moves per MMA.
+template <int ACC>
+__device__ __forceinline__ void umma_bf16_lh_e(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi, uint32_t idesc) {
+    asm volatile(
+        "{\n"
+        ".reg .b64 da, db;\n"
+        ".reg .pred p, e;\n"
+        "mov.b64 da, {%1, %2};\n"
+        "mov.b64 db, {%3, %4};\n"
+        "setp.ne.b32 p, %6, 0;\n"
+        "elect.sync _|e, 0xffffffff;\n"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n"
+        "}\n" ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "n"(ACC));
+}
+__device__ __forceinline__ void umma_bf16_lhr_e(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n"
+        ".reg .b64 da, db;\n"
+        ".reg .pred p, e;\n"
+        "mov.b64 da, {%1, %2};\n"
+        "mov.b64 db, {%3, %4};\n"
+        "setp.ne.b32 p, %6, 0;\n"
+        "elect.sync _|e, 0xffffffff;\n"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n"
+        "}\n" ::"r"(tmem_d), "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(acc));
+}
+__device__ __forceinline__ void umma_commit_e(uint32_t bar) {
+    asm volatile(
+        "{\n"
+        ".reg .pred e;\n"
+        "elect.sync _|e, 0xffffffff;\n"
+        "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n"
+        "}\n" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
@@ -863,7 +900,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
             pdl_trigger_late();
         }
     } else if (warp == 1) {
-        if (lane == 0) {
+        {   // all 32 lanes, one elected lane issues (umma_*_e)
             // c=F32, a=b=BF16, A and B MN-major (bits 15, 16), N>>3 @17, M>>4 @24
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) |
                                    ((uint32_t)(p.TN >> 3) << 17) | ((128u >> 4) << 24);
@@ -906,14 +943,14 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
                     for (int q = 0; q < kMaxAccQ; ++q) {
                         if (q < nq) {
                             const uint32_t tmem_d = tmem_base + q * TNa;
-                            umma_bf16_lhr(tmem_d, x_lo + x_off[q], hi_x, y_lo, hi_y, idesc2, first);
+                            umma_bf16_lhr_e(tmem_d, x_lo + x_off[q], hi_x, y_lo, hi_y, idesc2, first);
 #pragma unroll
                             for (int kk = 1; kk < 8; ++kk)
-                                umma_bf16_lh<1>(tmem_d, x_lo + x_off[q] + kk * x_kk, hi_x, y_lo + kk * y_kk, hi_y, idesc2);
+                                umma_bf16_lh_e<1>(tmem_d, x_lo + x_off[q] + kk * x_kk, hi_x, y_lo + kk * y_kk, hi_y, idesc2);
                         }
                     }
-                    umma_commit(barB_empty + 8 * stB);
-                    umma_commit(barA_empty + 8 * stA);
+                    umma_commit_e(barB_empty + 8 * stB);
+                    umma_commit_e(barA_empty + 8 * stA);
                     if (++stB == stagesB) { stB = 0; phB ^= 1; }
                     if (++stA == SA) { stA = 0; phA ^= 1; }
                 }
@@ -945,14 +982,14 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
                     for (int k = 0; k < kMaxTaps; ++k) {
                         if (k < ntap) {
                             const uint32_t tmem_d = tmem_base + k * TN;
-                            umma_bf16_lhr(tmem_d, a_lo, hi_a, b_lo + b_off[k], hi_b, idesc, first);
+                            umma_bf16_lhr_e(tmem_d, a_lo, hi_a, b_lo + b_off[k], hi_b, idesc, first);
 #pragma unroll
                             for (int kk = 1; kk < 8; ++kk)
-                                umma_bf16_lh<1>(tmem_d, a_lo + kk * a_kk, hi_a, b_lo + b_off[k] + kk * b_kk, hi_b, idesc);
+                                umma_bf16_lh_e<1>(tmem_d, a_lo + kk * a_kk, hi_a, b_lo + b_off[k] + kk * b_kk, hi_b, idesc);
                         }
                     }
-                    umma_commit(barB_empty + 8 * stB);
-                    umma_commit(barA_empty + 8 * stA);
+                    umma_commit_e(barB_empty + 8 * stB);
+                    umma_commit_e(barA_empty + 8 * stA);
                     if (++stB == stagesB) { stB = 0; phB ^= 1; }
                     if (++stA == SA) { stA = 0; phA ^= 1; }
                 }
@@ -970,17 +1007,17 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
                     const uint32_t b_lo = ((baddr & 0x3FFFFu) >> 4) | ((((128 * rbB) >> 4) & 0x3FFFu) << 16);
                     const uint32_t hi_a = ((8 * rbA) >> 4) | (1u << 14) | ((rbA == 128 ? 2u : 4u) << 29);
                     const uint32_t hi_b = ((8 * rbB) >> 4) | (1u << 14) | ((rbB == 128 ? 2u : 4u) << 29);
-                    umma_bf16_lhr(tmem_d, a_lo, hi_a, b_lo, hi_b, idesc, t > t_beg ? 1u : 0u);
+                    umma_bf16_lhr_e(tmem_d, a_lo, hi_a, b_lo, hi_b, idesc, t > t_beg ? 1u : 0u);
 #pragma unroll
                     for (int kk = 1; kk < 8; ++kk)                         // 128 pixels = 8 x K16
-                        umma_bf16_lh<1>(tmem_d, a_lo + kk * ((16 * rbA) >> 4), hi_a, b_lo + kk * ((16 * rbB) >> 4), hi_b, idesc);
-                    umma_commit(barB_empty + 8 * stB);
+                        umma_bf16_lh_e<1>(tmem_d, a_lo + kk * ((16 * rbA) >> 4), hi_a, b_lo + kk * ((16 * rbB) >> 4), hi_b, idesc);
+                    umma_commit_e(barB_empty + 8 * stB);
                     if (++stB == p.stagesB) { stB = 0; phB ^= 1; }
                 }
-                umma_commit(barA_empty + 8 * stA);
+                umma_commit_e(barA_empty + 8 * stA);
                 if (++stA == SA) { stA = 0; phA ^= 1; }
             }
-            umma_commit(bar_done);
+            umma_commit_e(bar_done);
         }
     } else {
         const int quad = warp & 3, row = quad * 32 + lane;
