@@ -383,7 +383,7 @@ conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CU
         }
     } else if (warp == 1) {
         // ================= MMA issuer =================
-        if (lane == 0) {
+        {   // all 32 lanes run the loop, one elected lane issues (umma_*_e)
             // cute::UMMA::InstrDescriptor: c=F32 (bit 4), a=b=BF16 (bits 7, 10), K-major A and B, N>>3 @17, M>>4 @24
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((128u >> 4) << 24);
             const uint32_t row_bytes = p.chunk * 2;
@@ -415,12 +415,12 @@ conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CU
                         const uint32_t da = a_lo0 + stage * a_step, db = b_lo0 + stage * b_step;
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
-                            if (k < ksteps) { umma_bf16_lhr(tmem_d, da + 2 * k, hik, db + 2 * k, hik, idesc, acc); acc = 1; }   // +32 B per K=16 step
-                        umma_commit(bar_empty + 8 * stage);                  // frees the smem stage when the MMAs retire
+                            if (k < ksteps) { umma_bf16_lhr_e(tmem_d, da + 2 * k, hik, db + 2 * k, hik, idesc, acc); acc = 1; }   // +32 B per K=16 step
+                        umma_commit_e(bar_empty + 8 * stage);                  // frees the smem stage when the MMAs retire
                         if (++stage == stages) { stage = 0; phase ^= 1; }
                     }
                 }
-                umma_commit(bar_tfull + 8 * as);                             // accumulator complete -> epilogue
+                umma_commit_e(bar_tfull + 8 * as);                             // accumulator complete -> epilogue
             }
         }
     } else {
@@ -592,7 +592,7 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         // Two issuers (p.issuers == 2) take alternate tiles: the per-tile barrier round trips of one overlap the
         // tensor-pipe back-pressure of the other.  Accumulators and stages are per tile, so no ordering between them.
         const int me = warp == 1 ? 0 : 1;
-        if (lane == 0 && me < p.issuers) {
+        if (me < p.issuers) {   // all 32 lanes run the loop, one elected lane issues (umma_*_e)
             const uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(p.BN >> 3) << 17) | ((128u >> 4) << 24);
             // The issuing thread is latency bound on its own instruction stream (measured: the issue loop, not
             // TMA, MMA or the epilogue, set the tile rate), so TAPS / KSTEPS are template constants, the loops
@@ -633,16 +633,16 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 for (int tap = 0; tap < TAPS; ++tap) {
 #pragma unroll
                     for (int k = 0; k < KSTEPS; ++k) {
-                        if (tap == 0 && k == 0) umma_bf16_lh<0>(tmem_d, a_lo + a_off[tap], hi_a, b_lo[tap], hi_b, idesc);
-                        else umma_bf16_lh<1>(tmem_d, a_lo + a_off[tap] + 2 * k, hi_a, b_lo[tap] + 2 * k, hi_b, idesc);
+                        if (tap == 0 && k == 0) umma_bf16_lh_e<0>(tmem_d, a_lo + a_off[tap], hi_a, b_lo[tap], hi_b, idesc);
+                        else umma_bf16_lh_e<1>(tmem_d, a_lo + a_off[tap] + 2 * k, hi_a, b_lo[tap] + 2 * k, hi_b, idesc);
                     }
-                    if (TAIL) umma_bf16_lh<1>(tmem_d, a_lo + (p.a_tail_off >> 4) + a_off_t[tap], hi_a_t, b_lo_t[tap], hi_b_t, idesc);
+                    if (TAIL) umma_bf16_lh_e<1>(tmem_d, a_lo + (p.a_tail_off >> 4) + a_off_t[tap], hi_a_t, b_lo_t[tap], hi_b_t, idesc);
                 }
                 }
-                if (MSX_DBG(p, 16)) { mbar_arrive(bar_empty + 8 * stage); mbar_arrive(bar_tfull + 8 * as); }
+                if (MSX_DBG(p, 16)) { if (lane == 0) { mbar_arrive(bar_empty + 8 * stage); mbar_arrive(bar_tfull + 8 * as); } }
                 else {
-                    umma_commit(bar_empty + 8 * stage);
-                    umma_commit(bar_tfull + 8 * as);
+                    umma_commit_e(bar_empty + 8 * stage);
+                    umma_commit_e(bar_tfull + 8 * as);
                 }
                 stage += step;
                 if (stage >= stages) { stage -= stages; phase ^= 1; }
