@@ -242,6 +242,24 @@ __device__ __forceinline__ void umma_bf16_lhr(uint32_t tmem_d, uint32_t a_lo, ui
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
+// Elected-lane forms of the producer's instructions (see "Warp-uniform issue" below: UTMALDG takes its tensor-map address
+// and coordinates from uniform registers too).
+__device__ __forceinline__ void mbar_expect_tx_e(uint32_t bar, uint32_t bytes) {
+    asm volatile("{\n.reg .pred e;\nelect.sync _|e, 0xffffffff;\n@e mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n}\n" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_e(uint32_t bar) {
+    asm volatile("{\n.reg .pred e;\nelect.sync _|e, 0xffffffff;\n@e mbarrier.arrive.shared::cta.b64 _, [%0];\n}\n" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tma_load_4d_e(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2, int c3) {
+    asm volatile("{\n.reg .pred e;\nelect.sync _|e, 0xffffffff;\n"
+                 "@e cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];\n}\n"
+                 ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_load_3d_e(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2) {
+    asm volatile("{\n.reg .pred e;\nelect.sync _|e, 0xffffffff;\n"
+                 "@e cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];\n}\n"
+                 ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
 // Warp-uniform issue: ALL lanes of the issuing warp run the loop (barrier waits, descriptor arithmetic) with identical values
 // and one elected lane issues the instruction.  In a block entered by `if (lane == 0)` the compiler cannot know that the
 // descriptors are warp-uniform and moves every one of them to the uniform registers UTCHMMA wants through an
@@ -349,7 +367,7 @@ conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CU
 
     if (warp == 0) {
         // ================= TMA producer =================
-        if (lane == 0) {
+        {   // all 32 lanes run the loop, one elected lane issues (*_e)
             int stage = 0;
             uint32_t phase = 0;
             for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
@@ -367,13 +385,13 @@ conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CU
                         if (p.tail && kc == p.kchunks - 1) {
                             // short channel tail (72 = 64 + 8, 136 = 128 + 8, ...): a 16- or 32-channel box with the
                             // matching narrower swizzle instead of a zero-filled 64-channel one - a quarter / half of the fill
-                            mbar_expect_tx(bar_full + 8 * stage, p.a_bytes_tail + p.b_bytes_tail);
-                            tma_load_4d(sA + stage * p.a_stage, mapAt, bar_full + 8 * stage, kc * p.chunk, sx, sy, img);
-                            tma_load_3d(sB + stage * p.b_stage, &tmB_tail, bar_full + 8 * stage, kc * p.chunk, nt * p.BN, wtap);
+                            mbar_expect_tx_e(bar_full + 8 * stage, p.a_bytes_tail + p.b_bytes_tail);
+                            tma_load_4d_e(sA + stage * p.a_stage, mapAt, bar_full + 8 * stage, kc * p.chunk, sx, sy, img);
+                            tma_load_3d_e(sB + stage * p.b_stage, &tmB_tail, bar_full + 8 * stage, kc * p.chunk, nt * p.BN, wtap);
                         } else {
-                            mbar_expect_tx(bar_full + 8 * stage, p.a_bytes + p.b_bytes);
-                            tma_load_4d(sA + stage * p.a_stage, mapA, bar_full + 8 * stage, kc * p.chunk, sx, sy, img);
-                            tma_load_3d(sB + stage * p.b_stage, &tmB, bar_full + 8 * stage, kc * p.chunk, nt * p.BN, wtap);
+                            mbar_expect_tx_e(bar_full + 8 * stage, p.a_bytes + p.b_bytes);
+                            tma_load_4d_e(sA + stage * p.a_stage, mapA, bar_full + 8 * stage, kc * p.chunk, sx, sy, img);
+                            tma_load_3d_e(sB + stage * p.b_stage, &tmB, bar_full + 8 * stage, kc * p.chunk, nt * p.BN, wtap);
                         }
                         if (++stage == p.stages) { stage = 0; phase ^= 1; }
                     }
@@ -566,11 +584,11 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
     if (warp == 0) {
         // (a second TMA-issuing warp on alternate tiles was measured: no gain - the per-box cost is in the TMA unit)
-        if (lane == 0) {
-            mbar_expect_tx(bar_w, taps * (p.b_tap_bytes + (TAIL ? p.b_tail_bytes : 0u)));      // resident weights, once per CTA
-            for (int tap = 0; tap < taps; ++tap) tma_load_3d(sB + tap * p.b_tap_bytes, &tmB, bar_w, 0, 0, tap);
+        {   // all 32 lanes run the loop, one elected lane issues (*_e)
+            mbar_expect_tx_e(bar_w, taps * (p.b_tap_bytes + (TAIL ? p.b_tail_bytes : 0u)));      // resident weights, once per CTA
+            for (int tap = 0; tap < taps; ++tap) tma_load_3d_e(sB + tap * p.b_tap_bytes, &tmB, bar_w, 0, 0, tap);
             if (TAIL)
-                for (int tap = 0; tap < taps; ++tap) tma_load_3d(sBt + tap * p.b_tail_bytes, &tmBt, bar_w, 64, 0, tap);
+                for (int tap = 0; tap < taps; ++tap) tma_load_3d_e(sBt + tap * p.b_tail_bytes, &tmBt, bar_w, 64, 0, tap);
             int stage = 0;
             uint32_t phase = 0;
             for (int t = blockIdx.x; t < total_units; t += gridDim.x) {
@@ -578,11 +596,11 @@ conv_tc_halo_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 const int ty = rem / units_x;
                 const int y0 = ty * 16, x0 = p.flat ? rem * 128 : (rem - ty * units_x) * unit_w;
                 mbar_wait(bar_empty + 8 * stage, phase ^ 1);
-                if (MSX_DBG(p, 4)) mbar_arrive(bar_full + 8 * stage);
+                if (MSX_DBG(p, 4)) mbar_arrive_e(bar_full + 8 * stage);
                 else {
-                    mbar_expect_tx(bar_full + 8 * stage, p.a_bytes + (TAIL ? p.a_bytes_tail : 0u));
-                    tma_load_4d(sA + stage * p.a_stage, &tmA, bar_full + 8 * stage, 0, x0 + p.ox_min, y0 + p.oy_min, img);
-                    if (TAIL) tma_load_4d(sA + stage * p.a_stage + p.a_tail_off, &tmAt, bar_full + 8 * stage, 64, x0 + p.ox_min, y0 + p.oy_min, img);
+                    mbar_expect_tx_e(bar_full + 8 * stage, p.a_bytes + (TAIL ? p.a_bytes_tail : 0u));
+                    tma_load_4d_e(sA + stage * p.a_stage, &tmA, bar_full + 8 * stage, 0, x0 + p.ox_min, y0 + p.oy_min, img);
+                    if (TAIL) tma_load_4d_e(sA + stage * p.a_stage + p.a_tail_off, &tmAt, bar_full + 8 * stage, 64, x0 + p.ox_min, y0 + p.oy_min, img);
                 }
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
@@ -867,7 +885,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
     const int64_t tiles_per_img = (int64_t)p.tiles_x * p.tiles_y;
 
     if (warp == 0) {
-        if (lane == 0) {
+        {   // all 32 lanes run the loop, one elected lane issues (*_e)
             int stA = 0, stB = 0;
             uint32_t phA = 0, phB = 0;
             for (int64_t t = t_beg; t < t_end; ++t) {
@@ -875,23 +893,23 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
                 const int y0 = (rem / p.tiles_x) * p.th, x0 = (rem % p.tiles_x) * p.tw;
                 const int ya = p.rowN ? y0 - (p.kh - 1) * p.dil + p.pad_h : y0;        // rows stacked on N: dy patch with the y halo
                 mbar_wait(barA_empty + 8 * stA, phA ^ 1);
-                mbar_expect_tx(barA_full + 8 * stA, groupsA * p.a_box_bytes);
+                mbar_expect_tx_e(barA_full + 8 * stA, groupsA * p.a_box_bytes);
                 for (int g = 0; g < groupsA; ++g)
-                    tma_load_4d(sA + stA * p.a_stage + g * 128 * rbA, &tmS, barA_full + 8 * stA, a0 + g * p.chunkA, x0, ya, img);
+                    tma_load_4d_e(sA + stA * p.a_stage + g * 128 * rbA, &tmS, barA_full + 8 * stA, a0 + g * p.chunkA, x0, ya, img);
                 if (++stA == SA) { stA = 0; phA ^= 1; }
                 if (p.halo) {
                     mbar_wait(barB_empty + 8 * stB, phB ^ 1);
-                    mbar_expect_tx(barB_full + 8 * stB, (uint32_t)p.Hh * p.Wh * rbB);
-                    tma_load_4d(sB + stB * p.b_stage, &tmG.m[0], barB_full + 8 * stB, b0, x0 - p.pad_w, p.rowN ? y0 : y0 - p.pad_h, img);
+                    mbar_expect_tx_e(barB_full + 8 * stB, (uint32_t)p.Hh * p.Wh * rbB);
+                    tma_load_4d_e(sB + stB * p.b_stage, &tmG.m[0], barB_full + 8 * stB, b0, x0 - p.pad_w, p.rowN ? y0 : y0 - p.pad_h, img);
                     if (++stB == p.stagesB) { stB = 0; phB ^= 1; }
                 } else {
                     for (int k = 0; k < ntap; ++k) {
                         const int tap = tap0 + k;
                         const CUtensorMap* mapG = &tmG.m[p.taps.map[tap]];
                         mbar_wait(barB_empty + 8 * stB, phB ^ 1);
-                        mbar_expect_tx(barB_full + 8 * stB, p.groupsB * 128 * rbB);
+                        mbar_expect_tx_e(barB_full + 8 * stB, p.groupsB * 128 * rbB);
                         for (int g = 0; g < p.groupsB; ++g)
-                            tma_load_4d(sB + stB * p.b_stage + g * 128 * rbB, mapG, barB_full + 8 * stB, b0 + g * p.chunkB,
+                            tma_load_4d_e(sB + stB * p.b_stage + g * 128 * rbB, mapG, barB_full + 8 * stB, b0 + g * p.chunkB,
                                         x0 + p.taps.dx[tap], y0 + p.taps.dy[tap], img);
                         if (++stB == p.stagesB) { stB = 0; phB ^= 1; }
                     }
