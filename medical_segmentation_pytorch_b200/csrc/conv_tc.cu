@@ -829,7 +829,14 @@ struct WgParams {
     // each - are dil image rows apart (block j <-> filter row kh-1-j).  One MMA covers G x kh taps: a 3x3 at <= 32
     // channels needs 8 MMAs per 128-pixel tile instead of 24.
     int rowN, HhA;
+    // halo == 2 with wide > 0: 16 x 8-pixel tiles instead of 8 x 16.  The TMA unit pays per contiguous run of a box (~20-35
+    // cycles, tools/micro/tma_rate.cu) and a box has one run per image row: half as many rows, twice as long.  For the MN-major
+    // operands only the K order changes - one K = 16 step is one image row of the tile (two dense 8-pixel groups) instead of two.
+    int wide;
     uint32_t a_box_bytes;             // bytes of one dy TMA box
+#ifdef MSX_ABLATION
+    int dbg;                          // MSX_DBG_WGRAD ablations of the stacked (halo == 2) mode, results are wrong: 2 no MMAs, 4 no TMA loads
+#endif
 };
 
 // MN-major operand descriptor: MN groups `lbo` bytes apart, 8-row (K) groups 8*row_bytes apart.
@@ -893,14 +900,20 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
                 const int y0 = (rem / p.tiles_x) * p.th, x0 = (rem % p.tiles_x) * p.tw;
                 const int ya = p.rowN ? y0 - (p.kh - 1) * p.dil + p.pad_h : y0;        // rows stacked on N: dy patch with the y halo
                 mbar_wait(barA_empty + 8 * stA, phA ^ 1);
-                mbar_expect_tx_e(barA_full + 8 * stA, groupsA * p.a_box_bytes);
-                for (int g = 0; g < groupsA; ++g)
-                    tma_load_4d_e(sA + stA * p.a_stage + g * 128 * rbA, &tmS, barA_full + 8 * stA, a0 + g * p.chunkA, x0, ya, img);
+                if (MSX_DBG(p, 4)) mbar_arrive_e(barA_full + 8 * stA);
+                else {
+                    mbar_expect_tx_e(barA_full + 8 * stA, groupsA * p.a_box_bytes);
+                    for (int g = 0; g < groupsA; ++g)
+                        tma_load_4d_e(sA + stA * p.a_stage + g * 128 * rbA, &tmS, barA_full + 8 * stA, a0 + g * p.chunkA, x0, ya, img);
+                }
                 if (++stA == SA) { stA = 0; phA ^= 1; }
                 if (p.halo) {
                     mbar_wait(barB_empty + 8 * stB, phB ^ 1);
-                    mbar_expect_tx_e(barB_full + 8 * stB, (uint32_t)p.Hh * p.Wh * rbB);
-                    tma_load_4d_e(sB + stB * p.b_stage, &tmG.m[0], barB_full + 8 * stB, b0, x0 - p.pad_w, p.rowN ? y0 : y0 - p.pad_h, img);
+                    if (MSX_DBG(p, 4)) mbar_arrive_e(barB_full + 8 * stB);
+                    else {
+                        mbar_expect_tx_e(barB_full + 8 * stB, (uint32_t)p.Hh * p.Wh * rbB);
+                        tma_load_4d_e(sB + stB * p.b_stage, &tmG.m[0], barB_full + 8 * stB, b0, x0 - p.pad_w, p.rowN ? y0 : y0 - p.pad_h, img);
+                    }
                     if (++stB == p.stagesB) { stB = 0; phB ^= 1; }
                 } else {
                     for (int k = 0; k < ntap; ++k) {
@@ -940,14 +953,14 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
                     const int r = p.rowN ? 0 : q / p.ncg, cg = p.rowN ? q : q - r * p.ncg;
                     x_off[q] = (uint32_t)((r * p.dil * p.Wh + cg * p.G * p.gs) * (int)rbB) >> 4;
                 }
-                const uint32_t hi_x = (uint32_t)((p.Wh * rbB) >> 4) | (1u << 14) | ((rbB == 128 ? 2u : 4u) << 29);
+                const uint32_t hi_x = (uint32_t)(((p.wide ? 8 : p.Wh) * rbB) >> 4) | (1u << 14) | ((rbB == 128 ? 2u : 4u) << 29);
                 const uint32_t hi_y = ((8 * rbA) >> 4) | (1u << 14) | ((rbA == 128 ? 2u : 4u) << 29);
                 const uint32_t x_lo0 = ((sB & 0x3FFFFu) >> 4) | ((((uint32_t)p.gs * rbB) >> 4) << 16);
                 // dy operand: N groups 128 pixel rows apart (several channel groups of one tile), or - rows stacked on N -
                 // dil image rows (8 pixels each) apart: the same channels seen through kh shifted windows
-                const uint32_t y_lbo = p.rowN ? (uint32_t)p.dil * 8u * rbA : 128u * rbA;
+                const uint32_t y_lbo = p.rowN ? (uint32_t)(p.dil * p.tw) * rbA : 128u * rbA;
                 const uint32_t y_lo0 = ((sA & 0x3FFFFu) >> 4) | (((y_lbo >> 4) & 0x3FFFu) << 16);
-                const uint32_t x_kk = (uint32_t)(2 * p.Wh * rbB) >> 4, y_kk = (16 * rbA) >> 4;
+                const uint32_t x_kk = (uint32_t)((p.wide ? 1 : 2) * p.Wh * rbB) >> 4, y_kk = (16 * rbA) >> 4;
                 const uint32_t a_st = p.a_stage >> 4, b_st = p.b_stage >> 4;
                 const int stagesB = p.stagesB, TNa = accN;
                 for (int64_t t = t_beg; t < t_end; ++t) {
@@ -957,6 +970,10 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
                     const uint32_t y_lo = y_lo0 + stA * a_st;
                     const uint32_t x_lo = x_lo0 + stB * b_st;
                     const uint32_t first = t > t_beg ? 1u : 0u;
+                    if (MSX_DBG(p, 2)) {
+                        mbar_arrive_e(barB_empty + 8 * stB);
+                        mbar_arrive_e(barA_empty + 8 * stA);
+                    } else {
 #pragma unroll
                     for (int q = 0; q < kMaxAccQ; ++q) {
                         if (q < nq) {
@@ -969,6 +986,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
                     }
                     umma_commit_e(barB_empty + 8 * stB);
                     umma_commit_e(barA_empty + 8 * stA);
+                    }
                     if (++stB == stagesB) { stB = 0; phB ^= 1; }
                     if (++stA == SA) { stA = 0; phA ^= 1; }
                 }
@@ -1168,7 +1186,7 @@ void wgrad_plan(const msx_conv_desc* d, WgParams& p) {
             p.b_stage = ((uint32_t)p.Hh * p.Wh * 128u + 1023u) & ~1023u;
         }
     }
-    p.TNa = 0; p.G = 0; p.ncg = 0; p.rowN = 0; p.HhA = 0; p.gs = p.dil;
+    p.TNa = 0; p.G = 0; p.ncg = 0; p.rowN = 0; p.HhA = 0; p.gs = p.dil; p.wide = 0;
     if (p.halo == 1 && p.Ap <= 128 && halo_mode() != 3) {
         // tap-stacked variant: see the halo == 2 branch of wgrad_tc_kernel
         const int chunkB = p.Bp <= 32 ? 32 : 64, G = 128 / chunkB, ncg = (p.kw + G - 1) / G;
@@ -1178,6 +1196,19 @@ void wgrad_plan(const msx_conv_desc* d, WgParams& p) {
         if (Wh2 <= 24 && p.kh * ncg * TNa <= 512 && p.kh * ncg <= 9) {
             p.halo = 2;
             p.chunkB = chunkB; p.G = G; p.ncg = ncg; p.TNa = TNa; p.gs = gs; p.Wh = Wh2;
+            {
+                static const int wide_on = [] { const char* e = getenv("MSX_WGRAD_WIDE"); return e ? atoi(e) : 1; }();
+                const int txw = (p.W + 15) / 16, tyw = (p.H + 7) / 8;
+                const double eff_t = (double)p.W * p.H / ((double)p.tiles_x * p.tiles_y * 128.0);
+                const double eff_w = (double)p.W * p.H / ((double)txw * tyw * 128.0);
+                if (wide_on && eff_w >= eff_t - 0.02) {
+                    p.wide = 1;
+                    p.tw = 16; p.th = 8; p.tiles_x = txw; p.tiles_y = tyw;
+                    p.pix_tiles = (int64_t)txw * tyw * p.N;
+                    p.Wh = Wh2 + 8;
+                    p.Hh = 8 + (p.kh - 1) * p.dil;
+                }
+            }
             p.b_stage = ((uint32_t)p.Hh * p.Wh * (chunkB * 2) + 1023u) & ~1023u;
             p.a_tiles = 1; p.b_tiles = 1; p.tap_groups = 1; p.tg = taps;
             int64_t sp = kNumSMs < p.pix_tiles ? kNumSMs : p.pix_tiles;
@@ -1191,8 +1222,8 @@ void wgrad_plan(const msx_conv_desc* d, WgParams& p) {
             if (rows_on_n && p.kh >= 2 && p.Ap <= rowN && p.kh * rowN <= 256 && ncg * p.kh * rowN <= 512) {
                 p.rowN = rowN;
                 p.chunkA = rowN;
-                p.HhA = 16 + (p.kh - 1) * p.dil;
-                p.Hh = 16;                                              // x patch: x halo only
+                p.HhA = p.th + (p.kh - 1) * p.dil;
+                p.Hh = p.th;                                            // x patch: x halo only
                 p.b_stage = ((uint32_t)p.Hh * p.Wh * (chunkB * 2) + 1023u) & ~1023u;
                 int cols3 = 32;
                 while (cols3 < ncg * p.kh * rowN) cols3 <<= 1;
@@ -1209,13 +1240,16 @@ void wgrad_plan(const msx_conv_desc* d, WgParams& p) {
         if (p.SA == 4) p.a_stage = (need + 1023u) & ~1023u;
         p.a_box_bytes = 128u * (p.chunkA * 2);
         if (p.rowN) {                                                   // one dy box of HhA x 8 pixels
-            p.a_box_bytes = (uint32_t)p.HhA * 8u * (p.chunkA * 2);
+            p.a_box_bytes = (uint32_t)p.HhA * (uint32_t)p.tw * (p.chunkA * 2);
             p.a_stage = (p.a_box_bytes + 1023u) & ~1023u;
             p.SA = p.a_stage <= 24 * 1024 ? 4 : 2;
         }
     }
     int sb = (int)((kSmemBudget - p.SA * p.a_stage) / p.b_stage);
     p.stagesB = sb > kMaxStages ? kMaxStages : (sb < 2 ? 2 : sb);
+#ifdef MSX_ABLATION
+    { static const int dbg = [] { const char* e = getenv("MSX_DBG_WGRAD"); return e ? atoi(e) : 0; }(); p.dbg = dbg; }
+#endif
 }
 
 }  // namespace
