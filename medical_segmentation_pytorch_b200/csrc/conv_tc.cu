@@ -895,9 +895,15 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__
         {   // all 32 lanes run the loop, one elected lane issues (*_e)
             int stA = 0, stB = 0;
             uint32_t phA = 0, phB = 0;
+            // tile coordinates by increments: the 64-bit divisions of t cost more than the rest of an iteration
+            int img_i = (int)(t_beg / tiles_per_img), tyi, txi;
+            {
+                const int rem0 = (int)(t_beg % tiles_per_img);
+                tyi = rem0 / p.tiles_x; txi = rem0 - tyi * p.tiles_x;
+            }
             for (int64_t t = t_beg; t < t_end; ++t) {
-                const int img = (int)(t / tiles_per_img), rem = (int)(t % tiles_per_img);
-                const int y0 = (rem / p.tiles_x) * p.th, x0 = (rem % p.tiles_x) * p.tw;
+                const int img = img_i, y0 = tyi * p.th, x0 = txi * p.tw;
+                if (++txi == p.tiles_x) { txi = 0; if (++tyi == p.tiles_y) { tyi = 0; ++img_i; } }
                 const int ya = p.rowN ? y0 - (p.kh - 1) * p.dil + p.pad_h : y0;        // rows stacked on N: dy patch with the y halo
                 mbar_wait(barA_empty + 8 * stA, phA ^ 1);
                 if (MSX_DBG(p, 4)) mbar_arrive_e(barA_full + 8 * stA);
