@@ -459,7 +459,7 @@ conv_tc_kernel(const __grid_constant__ PhaseMaps tmA, const __grid_constant__ CU
             bf16* out = dst + ((int64_t)(img * p.Hd + y * p.dmul + p.da) * p.Wd + x * p.dmul + p.db) * p.ldd + n0;
             mbar_wait(bar_tfull + 8 * grp, (it >> 1) & 1);
             tc_fence_after();
-            double* ws_s = sstat + ((warp - 2) * 2 + 0) * nca + n0;       // stats need n_tiles == 1 (n0 == 0): the launcher guarantees it
+            double* ws_s = sstat + ((warp - 2) * 2 + 0) * nca + n0;       // rows cover every output column, whichever n tiles this CTA visits
             double* ws_q = sstat + ((warp - 2) * 2 + 1) * nca + n0;
             int c0 = 0;
             for (; c0 < ncols && ncols - c0 > 16; c0 += 32) {
@@ -1599,7 +1599,10 @@ int conv_gather_tc(const msx_conv_desc* d, bool fwd_pass, const void* src, const
     p.a_stage = 128 * row_bytes;                                 // full 128-row operand tile
     p.b_stage = (p.b_bytes + 1023u) & ~1023u;
     const int nphase = (!f_form && d->stride == 2) ? 4 : 1;      // b-form stride 2: one launch per destination phase
-    if (p.n_tiles != 1 || nphase != 1) ep.stats = 0;
+    // several tiles of output channels: a CTA's statistics rows cover ALL columns (it may visit several n tiles; the columns it
+    // never sees stay zero), which costs shared memory - up to 72 KB (544 channels) are traded for the stand-alone pass
+    static const int stats_ntiles = [] { const char* e = getenv("MSX_STATS_NTILES"); return e ? atoi(e) : 1; }();
+    if (nphase != 1 || (p.n_tiles != 1 && (!stats_ntiles || stat_smem_bytes(p.ncp) > 72u * 1024u))) ep.stats = 0;
     const uint32_t stat_bytes = ep.stats ? stat_smem_bytes(p.ncp) : 0;
     int stages = (int)((kSmemBudget - stat_bytes) / (p.a_stage + p.b_stage));
     p.stages = stages > kMaxStages ? kMaxStages : (stages < 2 ? 2 : stages);

@@ -218,7 +218,7 @@ BN_FUSED_CASES = [
     (272, 136, 3, 1, 1, 11, 11, 2),
     (17, 34, 3, 2, 1, 32, 48, 2),       # stride 2 (streaming kernel over phase views)
     (3, 34, 2, 2, 1, 32, 32, 2),
-    (272, 544, 3, 1, 1, 11, 11, 2),     # > 256 output channels: two n tiles -> stand-alone statistics pass
+    (272, 544, 3, 1, 1, 11, 11, 2),     # several tiles of output channels: every CTA's statistics rows cover all 544 columns
 ]
 
 
