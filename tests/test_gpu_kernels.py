@@ -94,6 +94,9 @@ TC_CASES = [
     (68, 68, 1, 1, 1, 24, 24, 3),
     (34, 34, 3, 3, 3, 48, 48, 2),       # wgrad: two x-tap groups of two, windows 3 pixels apart (17-pixel-wide patch)
     (3, 17, 7, 1, 1, 64, 32, 2),        # wgrad: one-column filter, the stacked windows coincide
+    (17, 17, 1, 1, 1, 33, 47, 3),       # 1x1 walked as one row of 4 653 pixels: the last 128-pixel tile hangs over the end
+    (17, 17, 3, 3, 1, 35, 45, 2),       # wgrad on 16 x 8 tiles with ragged right / bottom tiles
+    (34, 17, 3, 3, 2, 24, 40, 2),       # wgrad 16 x 8 tiles, two x-tap groups, dilation 2
 ]
 
 
