@@ -494,6 +494,39 @@ __device__ inline void lane_reduce_2x8(double (&v)[16], double* sh, int vch, int
     }
 }
 
+// 16 floats per thread summed over the threads of the CTA that hold the same channel vector (threadIdx.x % vch, vch <= 32):
+// inside a warp by shuffles between threads vch * 2^k apart, across the 8 warps through shared memory - two block barriers
+// instead of the fourteen of the double-precision tree above, which was a quarter of the kernel at 88 x 88 (ncu, round 2).
+// The per-thread fp32 sums cover a few dozen pixels; 85 lanes more in a pairwise fp32 tree add ~1e-6 relative error, and the
+// fold over CTAs stays in double.  Result in the threads with threadIdx.x < vch.
+__device__ inline void lane_reduce_f32(float (&v)[16], float* sh, int vch) {
+    const int i = threadIdx.x & 31, w = threadIdx.x >> 5;
+    int smax = vch;
+    while (smax < 16) smax <<= 1;
+    for (int s = smax; s >= vch; s >>= 1) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const float o = __shfl_down_sync(0xffffffffu, v[j], s & 31);
+            if (i + s < 32) v[j] += o;
+        }
+    }
+    if (i < vch) {
+        const int c = (32 * w + i) % vch;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) sh[(w * 16 + j) * 32 + c] = v[j];
+    }
+    __syncthreads();
+    if (threadIdx.x < vch) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            float t = 0.f;
+#pragma unroll
+            for (int ww = 0; ww < 8; ++ww) t += sh[(ww * 16 + j) * 32 + threadIdx.x];
+            v[j] = t;
+        }
+    }
+}
+
 __global__ void __launch_bounds__(256, 3) bn_bwd_reduce_bf16_kernel(const bf16* __restrict__ x, int ldx, const bf16* __restrict__ dz, int lddz,
                                                                     int64_t pixels, int cp, int vch, int channels,
                                                                     const float* __restrict__ mean, const float* __restrict__ invstd,
@@ -544,13 +577,26 @@ __global__ void __launch_bounds__(256, 3) bn_bwd_reduce_bf16_kernel(const bf16* 
     }
     pdl_trigger_late();
     double acc[16];
+    if (vch <= 32) {
+        float v16[16];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        const int c = t.c0 + j;
-        acc[j] = (double)fs[j];
-        acc[8 + j] = (t.active && c < channels) ? (double)fq[j] * (double)invstd[c] : 0.0;
+        for (int j = 0; j < 8; ++j) { v16[j] = fs[j]; v16[8 + j] = fq[j]; }
+        lane_reduce_f32(v16, reinterpret_cast<float*>(shm), vch);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int c = t.c0 + j;
+            acc[j] = (double)v16[j];
+            acc[8 + j] = (t.active && c < channels) ? (double)v16[8 + j] * (double)invstd[c] : 0.0;
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int c = t.c0 + j;
+            acc[j] = (double)fs[j];
+            acc[8 + j] = (t.active && c < channels) ? (double)fq[j] * (double)invstd[c] : 0.0;
+        }
+        lane_reduce_2x8(acc, shm, vch, t.lane, t.lanes);
     }
-    lane_reduce_2x8(acc, shm, vch, t.lane, t.lanes);
     if (t.active && t.lane == 0) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
