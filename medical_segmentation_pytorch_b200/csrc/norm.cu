@@ -889,9 +889,18 @@ __global__ void __launch_bounds__(256, 3) sum_bf16_kernel(SumArgs a, int up2x, i
     if (!STATS) return;
     pdl_trigger_late();
     double acc[16];
+    if (vch <= 32) {
+        float v16[16];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) { acc[j] = (double)fs[j]; acc[8 + j] = (double)fq[j]; }
-    lane_reduce_2x8(acc, sh, vch, t.lane, t.lanes);
+        for (int j = 0; j < 8; ++j) { v16[j] = fs[j]; v16[8 + j] = fq[j]; }
+        lane_reduce_f32(v16, reinterpret_cast<float*>(sh), vch);
+#pragma unroll
+        for (int j = 0; j < 16; ++j) acc[j] = (double)v16[j];
+    } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { acc[j] = (double)fs[j]; acc[8 + j] = (double)fq[j]; }
+        lane_reduce_2x8(acc, sh, vch, t.lane, t.lanes);
+    }
     if (t.active && t.lane == 0 && partials) {
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
