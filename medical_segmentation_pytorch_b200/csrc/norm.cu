@@ -147,9 +147,21 @@ __global__ void __launch_bounds__(256, MSX_BN_MINBLOCKS) bn_stats_kernel(const T
 // instead of the four to five a single warp needs - these kernels are pure latency on the step's critical path.
 __device__ inline void fold_partials_block(const double* partials, int nblk, int cp, int c, double& s, double& q, double* sh) {
     double a = 0.0, b = 0.0;
-    for (int r = threadIdx.x; r < nblk; r += 128) {
-        a += __ldcg(partials + ((int64_t)r * 2 + 0) * cp + c);
-        b += __ldcg(partials + ((int64_t)r * 2 + 1) * cp + c);
+    if (nblk <= 5 * 128) {                       // kMaxPartialBlocks = 592: all ten loads of a thread in flight at once
+        double va[5], vb[5];
+#pragma unroll
+        for (int u = 0; u < 5; ++u) {
+            const int r = threadIdx.x + u * 128;
+            va[u] = r < nblk ? __ldcg(partials + ((int64_t)r * 2 + 0) * cp + c) : 0.0;
+            vb[u] = r < nblk ? __ldcg(partials + ((int64_t)r * 2 + 1) * cp + c) : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < 5; ++u) { a += va[u]; b += vb[u]; }
+    } else {
+        for (int r = threadIdx.x; r < nblk; r += 128) {
+            a += __ldcg(partials + ((int64_t)r * 2 + 0) * cp + c);
+            b += __ldcg(partials + ((int64_t)r * 2 + 1) * cp + c);
+        }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
